@@ -1,0 +1,470 @@
+/*
+ * cfd_b200.h -- C-ABI of libcfd_b200.so, the B200-native (sm_100a) backend for the
+ * shaia/CFD projection-method time step.
+ *
+ * Part 1 mirrors, field for field, the reference's own ABI types that cross the
+ *        boundary (so this header is usable without the reference tree).
+ * Part 2 declares the drop-in entry points: the very symbols that the reference's
+ *        solver registry and Poisson dispatcher bind at link time
+ *        (lib/src/api/solver_registry.c:83-95, lib/src/solvers/linear/linear_solver.c:165-229).
+ * Part 3 is the backend-private extension surface (cfd_b200_*): Poisson-method
+ *        selection (the reference has no public knob), device-resident sessions for
+ *        multi-step / multi-GPU runs, and measurement hooks.
+ *
+ * All signatures are plain C: pointers, sizes, doubles and ints. No C++/torch types.
+ * When the real reference headers were already included, Part 1 is skipped.
+ */
+#ifndef CFD_B200_H
+#define CFD_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include <stdbool.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define CFD_B200_API __attribute__((visibility("default")))
+#else
+#define CFD_B200_API
+#endif
+
+/* ======================================================================
+ * Part 1 -- ABI mirror of the reference types
+ * ====================================================================== */
+#ifndef CFD_NAVIER_STOKES_SOLVER_H /* reference: lib/include/cfd/solvers/navier_stokes_solver.h */
+
+/* lib/include/cfd/core/cfd_status.h:13-24 */
+typedef enum {
+    CFD_SUCCESS = 0,
+    CFD_ERROR = -1,
+    CFD_ERROR_NOMEM = -2,
+    CFD_ERROR_INVALID = -3,
+    CFD_ERROR_IO = -4,
+    CFD_ERROR_UNSUPPORTED = -5,
+    CFD_ERROR_DIVERGED = -6,
+    CFD_ERROR_MAX_ITER = -7,
+    CFD_ERROR_LIMIT_EXCEEDED = -8,
+    CFD_ERROR_NOT_FOUND = -9
+} cfd_status_t;
+
+/* lib/include/cfd/core/grid.h:18-40 */
+typedef struct {
+    double* x;
+    double* y;
+    double* dx;
+    double* dy;
+    size_t nx;
+    size_t ny;
+    double xmin, xmax, ymin, ymax;
+    double* z;
+    double* dz;
+    size_t nz;
+    double zmin, zmax;
+    size_t stride_z;
+    double inv_dz2;
+    size_t k_start;
+    size_t k_end;
+} grid;
+
+/* lib/include/cfd/boundary/boundary_conditions.h:19-27 */
+typedef enum {
+    BC_TYPE_PERIODIC,
+    BC_TYPE_NEUMANN,
+    BC_TYPE_DIRICHLET,
+    BC_TYPE_NOSLIP,
+    BC_TYPE_INLET,
+    BC_TYPE_OUTLET,
+    BC_TYPE_SYMMETRY
+} bc_type_t;
+
+/* lib/include/cfd/boundary/boundary_conditions.h:50-57 */
+typedef struct {
+    double left, right, top, bottom, front, back;
+} bc_dirichlet_values_t;
+
+/* lib/include/cfd/solvers/navier_stokes_solver.h:54-64 */
+typedef struct {
+    double* u;
+    double* v;
+    double* w;
+    double* p;
+    double* rho;
+    double* T;
+    size_t nx, ny, nz;
+} flow_field;
+
+/* navier_stokes_solver.h:77-92 */
+typedef void (*ns_source_func_t)(double x, double y, double z, double t, void* context,
+                                 double* source_u, double* source_v, double* source_w);
+typedef double (*ns_heat_source_func_t)(double x, double y, double z, double t, void* context);
+
+/* navier_stokes_solver.h:108-116 */
+typedef struct {
+    bc_type_t left, right, bottom, top, front, back;
+    bc_dirichlet_values_t dirichlet_values;
+} ns_thermal_bc_config_t;
+
+/* navier_stokes_solver.h:121-158 */
+typedef struct {
+    double dt, cfl, gamma, mu, k;
+    int max_iter;
+    double tolerance;
+    double source_amplitude_u, source_amplitude_v, source_decay_rate, pressure_coupling;
+    ns_source_func_t source_func;
+    void* source_context;
+    double alpha, beta, T_ref;
+    double gravity[3];
+    ns_heat_source_func_t heat_source_func;
+    void* heat_source_context;
+    ns_thermal_bc_config_t thermal_bc;
+} ns_solver_params_t;
+
+/* navier_stokes_solver.h:172-207 */
+typedef enum {
+    NS_SOLVER_BACKEND_SCALAR = 0,
+    NS_SOLVER_BACKEND_SIMD = 1,
+    NS_SOLVER_BACKEND_OMP = 2,
+    NS_SOLVER_BACKEND_CUDA = 3
+} ns_solver_backend_t;
+
+typedef enum {
+    NS_SOLVER_CAP_NONE = 0,
+    NS_SOLVER_CAP_INCOMPRESSIBLE = (1 << 0),
+    NS_SOLVER_CAP_COMPRESSIBLE = (1 << 1),
+    NS_SOLVER_CAP_STEADY_STATE = (1 << 2),
+    NS_SOLVER_CAP_TRANSIENT = (1 << 3),
+    NS_SOLVER_CAP_SIMD = (1 << 4),
+    NS_SOLVER_CAP_PARALLEL = (1 << 5),
+    NS_SOLVER_CAP_GPU = (1 << 6)
+} ns_solver_capabilities_t;
+
+typedef struct {
+    int iterations;
+    double residual;
+    double max_velocity;
+    double max_pressure;
+    double max_temperature;
+    double cfl_number;
+    double elapsed_time_ms;
+    cfd_status_t status;
+} ns_solver_stats_t;
+
+/* navier_stokes_solver.h:213-277 -- the solver vtable a registry factory returns */
+typedef struct NSSolver ns_solver_t;
+typedef void* ns_solver_context_t;
+typedef cfd_status_t (*ns_solver_init_func)(ns_solver_t*, const grid*, const ns_solver_params_t*);
+typedef void (*ns_solver_destroy_func)(ns_solver_t*);
+typedef cfd_status_t (*ns_solver_step_func)(ns_solver_t*, flow_field*, const grid*,
+                                            const ns_solver_params_t*, ns_solver_stats_t*);
+typedef cfd_status_t (*ns_solver_solve_func)(ns_solver_t*, flow_field*, const grid*,
+                                             const ns_solver_params_t*, ns_solver_stats_t*);
+typedef void (*ns_solver_boundary_func)(ns_solver_t*, flow_field*, const grid*);
+typedef double (*ns_solver_compute_dt_func)(ns_solver_t*, const flow_field*, const grid*,
+                                            const ns_solver_params_t*);
+typedef const char* (*ns_solver_get_name_func)(const ns_solver_t*);
+typedef const char* (*ns_solver_get_description_func)(const ns_solver_t*);
+typedef ns_solver_capabilities_t (*ns_solver_get_capabilities_func)(const ns_solver_t*);
+
+struct NSSolver {
+    const char* name;
+    const char* description;
+    const char* version;
+    ns_solver_capabilities_t capabilities;
+    ns_solver_backend_t backend;
+    ns_solver_context_t context;
+    ns_solver_init_func init;
+    ns_solver_destroy_func destroy;
+    ns_solver_step_func step;
+    ns_solver_solve_func solve;
+    ns_solver_boundary_func apply_boundary;
+    ns_solver_compute_dt_func compute_dt;
+    ns_solver_get_name_func get_name;
+    ns_solver_get_description_func get_description;
+    ns_solver_get_capabilities_func get_capabilities;
+};
+
+typedef ns_solver_t* (*ns_solver_factory_func)(void);
+
+#endif /* CFD_NAVIER_STOKES_SOLVER_H */
+
+#ifndef CFD_POISSON_SOLVER_H /* reference: lib/include/cfd/solvers/poisson_solver.h */
+
+/* poisson_solver.h:53-108 */
+typedef enum {
+    POISSON_METHOD_JACOBI,
+    POISSON_METHOD_GAUSS_SEIDEL,
+    POISSON_METHOD_SOR,
+    POISSON_METHOD_REDBLACK_SOR,
+    POISSON_METHOD_CG,
+    POISSON_METHOD_BICGSTAB,
+    POISSON_METHOD_MULTIGRID
+} poisson_solver_method_t;
+
+typedef enum {
+    POISSON_BACKEND_AUTO,
+    POISSON_BACKEND_SCALAR,
+    POISSON_BACKEND_OMP,
+    POISSON_BACKEND_SIMD,
+    POISSON_BACKEND_GPU
+} poisson_solver_backend_t;
+
+typedef enum {
+    POISSON_CONVERGED = 0,
+    POISSON_MAX_ITER = 1,
+    POISSON_DIVERGED = 2,
+    POISSON_STAGNATED = 3,
+    POISSON_ERROR = -1
+} poisson_solver_status_t;
+
+typedef enum { POISSON_PRECOND_NONE = 0, POISSON_PRECOND_JACOBI = 1 } poisson_precond_type_t;
+
+typedef struct {
+    double tolerance;
+    double absolute_tolerance;
+    int max_iterations;
+    double omega;
+    int check_interval;
+    bool verbose;
+    poisson_precond_type_t preconditioner;
+} poisson_solver_params_t;
+
+typedef struct {
+    poisson_solver_status_t status;
+    int iterations;
+    double initial_residual;
+    double final_residual;
+    double elapsed_time_ms;
+} poisson_solver_stats_t;
+
+/* poisson_solver.h:163-233 -- the Poisson vtable a factory returns */
+typedef struct poisson_solver poisson_solver_t;
+typedef void* poisson_solver_context_t;
+typedef cfd_status_t (*poisson_solver_init_func)(poisson_solver_t*, size_t nx, size_t ny, size_t nz,
+                                                 double dx, double dy, double dz,
+                                                 const poisson_solver_params_t*);
+typedef void (*poisson_solver_destroy_func)(poisson_solver_t*);
+typedef cfd_status_t (*poisson_solver_solve_func)(poisson_solver_t*, double* x, double* x_temp,
+                                                  const double* rhs, poisson_solver_stats_t*);
+typedef cfd_status_t (*poisson_solver_iterate_func)(poisson_solver_t*, double* x, double* x_temp,
+                                                    const double* rhs, double* residual);
+typedef void (*poisson_solver_apply_bc_func)(poisson_solver_t*, double* x);
+
+struct poisson_solver {
+    const char* name;
+    const char* description;
+    poisson_solver_method_t method;
+    poisson_solver_backend_t backend;
+    size_t nx, ny, nz;
+    double dx, dy, dz;
+    poisson_solver_params_t params;
+    poisson_solver_context_t context;
+    poisson_solver_init_func init;
+    poisson_solver_destroy_func destroy;
+    poisson_solver_solve_func solve;
+    poisson_solver_iterate_func iterate;
+    poisson_solver_apply_bc_func apply_bc;
+};
+
+#endif /* CFD_POISSON_SOLVER_H */
+
+#ifndef CFD_GPU_DEVICE_H /* reference: lib/include/cfd/core/gpu_device.h */
+
+/* gpu_device.h:32-53 */
+typedef struct {
+    int enable_gpu;
+    size_t min_grid_size;
+    int min_steps;
+    int block_size_x;
+    int block_size_y;
+    int poisson_max_iter;
+    double poisson_tolerance;
+    int persistent_memory;
+    int async_transfers;
+    int sync_after_kernel;
+    int verbose;
+} gpu_config_t;
+
+/* gpu_device.h:58-69 */
+typedef struct {
+    int device_id;
+    char name[256];
+    size_t total_memory;
+    size_t free_memory;
+    int compute_capability_major;
+    int compute_capability_minor;
+    int multiprocessor_count;
+    int max_threads_per_block;
+    int warp_size;
+    int is_available;
+} gpu_device_info_t;
+
+/* gpu_device.h:74-82 */
+typedef struct {
+    double kernel_time_ms;
+    double transfer_time_ms;
+    double poisson_time_ms;
+    int poisson_iterations;
+    double poisson_residual;
+    size_t memory_allocated;
+    int kernels_launched;
+} gpu_solver_stats_t;
+
+typedef struct gpu_solver_context_t gpu_solver_context_t; /* gpu_device.h:88, opaque */
+
+#endif /* CFD_GPU_DEVICE_H */
+
+/* ======================================================================
+ * Part 2 -- drop-in entry points (reference names, reference signatures)
+ * ====================================================================== */
+
+/* The ten symbols libcfd_api.a needs from the GPU library. */
+CFD_B200_API int gpu_is_available(void);                        /* gpu_device.h:103 */
+CFD_B200_API gpu_config_t gpu_config_default(void);             /* gpu_device.h:97  */
+CFD_B200_API cfd_status_t solve_projection_method_gpu(          /* gpu_device.h:221 */
+    flow_field* field, const grid* grid, const ns_solver_params_t* params, const gpu_config_t* config);
+CFD_B200_API cfd_status_t solve_rk2_method_gpu(                 /* gpu_device.h:234 */
+    flow_field* field, const grid* grid, const ns_solver_params_t* params, const gpu_config_t* config);
+CFD_B200_API cfd_status_t solve_rk4_method_gpu(                 /* gpu_device.h:247 */
+    flow_field* field, const grid* grid, const ns_solver_params_t* params, const gpu_config_t* config);
+CFD_B200_API cfd_status_t solve_explicit_euler_method_gpu(      /* solver_registry.c:86-88 */
+    flow_field* field, const grid* grid, const ns_solver_params_t* params, const gpu_config_t* config);
+CFD_B200_API poisson_solver_t* create_jacobi_gpu_solver(void);   /* linear_solver.c:165-168 */
+CFD_B200_API poisson_solver_t* create_redblack_gpu_solver(void); /* linear_solver.c:194-197 */
+CFD_B200_API poisson_solver_t* create_cg_gpu_solver(void);       /* linear_solver.c:212-215 */
+CFD_B200_API poisson_solver_t* create_bicgstab_gpu_solver(void); /* linear_solver.c:226-229 */
+
+/* Remaining public GPU device surface used by the reference's tests/examples. */
+CFD_B200_API int gpu_get_device_info(gpu_device_info_t* info, int max_devices); /* gpu_device.h:111 */
+CFD_B200_API cfd_status_t gpu_select_device(int device_id);                     /* gpu_device.h:118 */
+CFD_B200_API int gpu_should_use(const gpu_config_t* config, size_t nx, size_t ny, size_t nz,
+                                int num_steps);                                 /* gpu_device.h:129 */
+CFD_B200_API cfd_status_t solve_navier_stokes_gpu(                              /* gpu_device.h:209 */
+    flow_field* field, const grid* grid, const ns_solver_params_t* params, const gpu_config_t* config);
+
+/* Legacy persistent-context API (gpu_device.h:145-194). step() advances one projection step. */
+CFD_B200_API gpu_solver_context_t* gpu_solver_create(size_t nx, size_t ny, size_t nz,
+                                                     const gpu_config_t* config);
+CFD_B200_API void gpu_solver_destroy(gpu_solver_context_t* ctx);
+CFD_B200_API cfd_status_t gpu_solver_upload(gpu_solver_context_t* ctx, const flow_field* field);
+CFD_B200_API cfd_status_t gpu_solver_download(gpu_solver_context_t* ctx, flow_field* field);
+CFD_B200_API cfd_status_t gpu_solver_step(gpu_solver_context_t* ctx, const grid* grid,
+                                          const ns_solver_params_t* params, gpu_solver_stats_t* stats);
+CFD_B200_API gpu_solver_stats_t gpu_solver_get_stats(const gpu_solver_context_t* ctx);
+CFD_B200_API void gpu_solver_reset_stats(gpu_solver_context_t* ctx);
+
+/* Run-time registration path (navier_stokes_solver.h:333-337): factories returning a heap
+ * ns_solver_t with real init/destroy (persistent device context) and fully filled stats. */
+CFD_B200_API ns_solver_t* cfd_b200_create_projection_gpu_solver(void);
+CFD_B200_API ns_solver_t* cfd_b200_create_rk2_gpu_solver(void);
+CFD_B200_API ns_solver_t* cfd_b200_create_rk4_gpu_solver(void);
+
+/* ======================================================================
+ * Part 3 -- backend-private extensions
+ * ====================================================================== */
+
+/* What to do when the Poisson solve hits its iteration cap. */
+typedef enum {
+    CFD_B200_NONCONV_ERROR = 0,   /* reference CPU behaviour: CFD_ERROR_MAX_ITER (solver_projection.c:220-224) */
+    CFD_B200_NONCONV_CONTINUE = 1 /* reference GPU behaviour / fixed-iteration timing mode: proceed */
+} cfd_b200_nonconv_t;
+
+/* Poisson configuration of the projection step. The reference hard-codes CG with
+ * poisson_solver_params_default() (solver_projection.c:217-218, linear_solver.c:37-47). */
+typedef struct {
+    poisson_solver_method_t method;  /* JACOBI, REDBLACK_SOR, CG, BICGSTAB */
+    poisson_solver_params_t params;  /* tolerance, absolute_tolerance, max_iterations, omega,
+                                        check_interval, preconditioner (CG only) */
+    cfd_b200_nonconv_t on_nonconvergence;
+} cfd_b200_poisson_config_t;
+
+CFD_B200_API cfd_b200_poisson_config_t cfd_b200_poisson_config_default(void);
+/* Process-wide configuration used by solve_projection_method_gpu and the factories.
+ * Also settable with env CFD_B200_POISSON={jacobi,rbsor,cg,pcg,bicgstab}. */
+CFD_B200_API cfd_status_t cfd_b200_set_poisson_config(const cfd_b200_poisson_config_t* cfg);
+CFD_B200_API cfd_b200_poisson_config_t cfd_b200_get_poisson_config(void);
+
+/* Thread-local human-readable error of the last failing cfd_b200 / drop-in call. */
+CFD_B200_API const char* cfd_b200_last_error(void);
+CFD_B200_API const char* cfd_b200_version(void);
+/* Number of kernels this library has launched since load (all streams, all sessions). */
+CFD_B200_API unsigned long long cfd_b200_kernel_launch_count(void);
+
+/* Pinned host memory helpers (for callers that want async H2D/D2H of their flow_field). */
+CFD_B200_API void* cfd_b200_host_alloc(size_t bytes);
+CFD_B200_API void cfd_b200_host_free(void* p);
+
+/* ---- Device-resident session: one slab of the (possibly decomposed) grid on one GPU ---- */
+
+typedef struct cfd_b200_session cfd_b200_session_t;
+
+typedef struct {
+    /* Local slab extents INCLUDING the one-cell boundary/halo layer on every side. */
+    size_t nx, ny, nz;            /* nz == 1 for 2-D */
+    double dx, dy, dz;            /* uniform spacing (dz ignored when nz == 1) */
+    double xmin, ymin, zmin;      /* coordinate of local index 0 (source term uses x_i, y_j) */
+    /* Slab decomposition along z (along y when nz == 1). rank 0 holds the low physical
+     * boundary, rank nranks-1 the high one; interior ranks have halos on both sides. */
+    int rank, nranks;
+    int device;                   /* CUDA device ordinal, -1 = current */
+} cfd_b200_session_desc_t;
+
+CFD_B200_API cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* desc);
+CFD_B200_API void cfd_b200_session_destroy(cfd_b200_session_t* s);
+
+/* Attach an initialised NCCL communicator (ncclComm_t passed as void*) for halo exchange and
+ * Krylov all-reduces. nccl_lib is the path of the libnccl.so.2 that created it. */
+CFD_B200_API cfd_status_t cfd_b200_session_set_comm(cfd_b200_session_t* s, void* nccl_comm,
+                                                    const char* nccl_lib);
+
+/* Host<->device movement of the local slab (host arrays sized nx*ny*nz, reference layout).
+ * rho: only rho[0] is used by the projection; RK uses the full field. */
+CFD_B200_API cfd_status_t cfd_b200_session_upload(cfd_b200_session_t* s, const flow_field* host);
+CFD_B200_API cfd_status_t cfd_b200_session_download(cfd_b200_session_t* s, flow_field* host);
+/* Fill the device fields with the deterministic synthetic state of SURVEY 8(d) config C5
+ * (sinusoidal velocity + splitmix64 perturbation); no host traffic. */
+CFD_B200_API cfd_status_t cfd_b200_session_init_synthetic(cfd_b200_session_t* s, uint64_t seed,
+                                                          size_t global_k0);
+
+/* Advance nsteps projection steps (solver_projection.c:111-290) fully on the device. */
+CFD_B200_API cfd_status_t cfd_b200_session_projection(cfd_b200_session_t* s,
+                                                      const ns_solver_params_t* params,
+                                                      const cfd_b200_poisson_config_t* poisson,
+                                                      int nsteps, ns_solver_stats_t* stats);
+/* Advance nsteps explicit RK steps, order in {1,2,4} (solver_rk2.c, solver_rk4.c). */
+CFD_B200_API cfd_status_t cfd_b200_session_rk(cfd_b200_session_t* s, int order,
+                                              const ns_solver_params_t* params, int nsteps,
+                                              ns_solver_stats_t* stats);
+/* Stand-alone Poisson solve on device-resident x (the session's pressure) and rhs. */
+CFD_B200_API cfd_status_t cfd_b200_session_poisson(cfd_b200_session_t* s,
+                                                   const cfd_b200_poisson_config_t* poisson,
+                                                   poisson_solver_stats_t* stats);
+CFD_B200_API cfd_status_t cfd_b200_session_upload_poisson(cfd_b200_session_t* s, const double* x,
+                                                          const double* rhs);
+CFD_B200_API cfd_status_t cfd_b200_session_download_poisson(cfd_b200_session_t* s, double* x);
+
+/* Poisson statistics of the most recent projection step / Poisson solve. */
+CFD_B200_API poisson_solver_stats_t cfd_b200_session_last_poisson_stats(const cfd_b200_session_t* s);
+
+/* ---- Measurement hooks (bench.py): per-kernel CUDA-event timing on the session stream ---- */
+#define CFD_B200_MAX_KERNEL_KINDS 48
+typedef struct {
+    const char* name;            /* kernel family name */
+    unsigned long long launches; /* launches since reset */
+    double total_ms;             /* summed CUDA-event time (only when profiling enabled) */
+    double bytes_per_cell;       /* algorithmic bytes per interior cell per launch */
+} cfd_b200_kernel_stat_t;
+CFD_B200_API void cfd_b200_session_profile(cfd_b200_session_t* s, int enable);
+CFD_B200_API int cfd_b200_session_kernel_stats(const cfd_b200_session_t* s,
+                                               cfd_b200_kernel_stat_t* out, int max);
+CFD_B200_API void cfd_b200_session_reset_kernel_stats(cfd_b200_session_t* s);
+/* cudaStream_t of the session as void* (so callers can record their own events on it). */
+CFD_B200_API void* cfd_b200_session_stream(cfd_b200_session_t* s);
+CFD_B200_API cfd_status_t cfd_b200_session_sync(cfd_b200_session_t* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CFD_B200_H */
