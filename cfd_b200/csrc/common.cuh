@@ -1,0 +1,167 @@
+// common.cuh -- shared device/host definitions of libcfd_b200 (sm_100a, FP64).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <math.h>
+
+#include "../../include/cfd_b200.h"
+
+namespace cfdb {
+
+// ---------------------------------------------------------------------------------------
+// Geometry of one slab resident on one GPU.  Layout is the reference's: SoA, x fastest,
+// idx = k*nx*ny + j*nx + i (cfd/core/indexing.h:17-20); the outermost layer of cells on every
+// side is either a physical boundary (ghost) layer or, along the decomposed axis, a halo
+// plane owned by the neighbouring rank.
+// ---------------------------------------------------------------------------------------
+struct Geom {
+    int nx, ny, nz;          // local extents including boundary / halo layers
+    long long sy, sz;        // strides in doubles: sy = nx, sz = nx*ny (0 when nz == 1)
+    int k0, k1;              // updated k range [k0,k1): 1..nz-1 in 3-D, 0..1 in 2-D
+    int dim3;                // nz > 1
+    double inv_2dx, inv_2dy, inv_2dz, inv_dx2, inv_dy2, inv_dz2;
+    double factor, inv_factor;  // 2(1/dx2+1/dy2+1/dz2) and its reciprocal (linear_solver_jacobi.c:62-63)
+    // physical-boundary flags: glo[a]/ghi[a] == 1 when the low/high side of axis a (0=x,1=y,2=z)
+    // is a true domain boundary (Neumann ghost / BC applies); 0 when it is a halo.
+    int glo[3], ghi[3];
+    // global index of local (0,0,0) -- for coordinate tables and red/black colouring
+    long long gi0, gj0, gk0;
+    long long ncell;         // nx*ny*nz
+};
+
+// One reduction "slot" : up to 4 simultaneous sums (or maxes) finished by the last block.
+struct RedBuf {
+    double* partials;   // [max_blocks][4]
+    unsigned* ticket;   // zero-initialised, self-resetting
+};
+
+// Device-resident control block of an iterative solve: kernels read/derive everything they
+// need from here, so the host never synchronises inside an iteration.
+struct Ctl {
+    double dot[32];       // raw reduced values; slot meaning is solver specific (see poisson.cuh)
+    double tol;           // max(rel*r0, abs)
+    double r0;            // initial residual norm
+    double res;           // last residual norm the reference would report
+    int done_seq;         // kernels launched with seq > done_seq are no-ops; INT_MAX while running
+    int status;           // poisson_solver_status_t
+    int iterations;       // as the reference reports them
+    int result_buf;       // which ping-pong buffer holds x (Jacobi)
+    int skip_final_bc;    // reference returned before its final Neumann BC (stagnation paths)
+    int nonfinite;        // NaN/Inf flag of the time step (solver_projection.c:281-289)
+    int pad[2];
+    double stat[4];       // max |vel|, max |p|, max T, spare (solver_registry.c:31-62)
+};
+
+// Per-launch arguments of the Poisson kernels (everything the host knows at launch time).
+struct KArgs {
+    int seq;              // launch sequence number inside this solve (monotone)
+    int it;               // iteration (or sweep) index
+    int check;            // check_interval
+    int max_iter;
+    double rel_tol, abs_tol;
+    double omega;         // SOR relaxation factor
+    double dinv;          // Jacobi preconditioner 1/diag (linear_solver_cg.c:216)
+    int zchunk;           // planes marched per block
+};
+
+#define CFDB_CUDA_OK(expr)                                                                  \
+    do {                                                                                    \
+        cudaError_t e_ = (expr);                                                            \
+        if (e_ != cudaSuccess) {                                                            \
+            cfdb::set_error(CFD_ERROR, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), \
+                            __FILE__, __LINE__);                                            \
+            return CFD_ERROR;                                                               \
+        }                                                                                   \
+    } while (0)
+
+void set_error(cfd_status_t st, const char* fmt, ...);
+extern unsigned long long g_launches;  // kernels launched by this library
+
+// ---------------------------------------------------------------------------------------
+// Device helpers
+// ---------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ double clamp100(double v) { return fmax(-100.0, fmin(100.0, v)); }
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Block-wide reduction of NV values followed by the deterministic "last block finishes"
+// pattern: every block stores its partial, the block that draws the last ticket adds all
+// partials in a fixed order and writes out[0..NV).  No atomics on doubles, no host sync.
+// IS_MAX selects max instead of sum.  All threads of the block must call it.
+template <int NV, bool IS_MAX>
+__device__ __forceinline__ void block_reduce_finish(double (&v)[NV], const RedBuf rb, double* out) {
+    __shared__ double sh[NV][32];
+    __shared__ bool last;
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+    const int nthr = blockDim.x * blockDim.y;
+    const int lane = tid & 31, wid = tid >> 5, nw = (nthr + 31) >> 5;
+#pragma unroll
+    for (int q = 0; q < NV; q++) {
+        double r = IS_MAX ? warp_max(v[q]) : warp_sum(v[q]);
+        if (lane == 0) sh[q][wid] = r;
+    }
+    __syncthreads();
+    const unsigned nblocks = gridDim.x * gridDim.y * gridDim.z;
+    const unsigned bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    if (wid == 0) {
+#pragma unroll
+        for (int q = 0; q < NV; q++) {
+            double r = (lane < nw) ? sh[q][lane] : (IS_MAX ? -INFINITY : 0.0);
+            r = IS_MAX ? warp_max(r) : warp_sum(r);
+            if (lane == 0) rb.partials[(size_t)bid * 4 + q] = r;
+        }
+        if (lane == 0) {
+            __threadfence();
+            unsigned t = atomicAdd(rb.ticket, 1u);
+            last = (t == nblocks - 1);
+        }
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    double acc[NV];
+#pragma unroll
+    for (int q = 0; q < NV; q++) acc[q] = IS_MAX ? -INFINITY : 0.0;
+    for (unsigned b = tid; b < nblocks; b += nthr) {
+#pragma unroll
+        for (int q = 0; q < NV; q++) {
+            double pv = __ldcg(&rb.partials[(size_t)b * 4 + q]);
+            acc[q] = IS_MAX ? fmax(acc[q], pv) : acc[q] + pv;
+        }
+    }
+    __syncthreads();  // sh reuse
+#pragma unroll
+    for (int q = 0; q < NV; q++) {
+        double r = IS_MAX ? warp_max(acc[q]) : warp_sum(acc[q]);
+        if (lane == 0) sh[q][wid] = r;
+    }
+    __syncthreads();
+    if (wid == 0) {
+#pragma unroll
+        for (int q = 0; q < NV; q++) {
+            double r = (lane < nw) ? sh[q][lane] : (IS_MAX ? -INFINITY : 0.0);
+            r = IS_MAX ? warp_max(r) : warp_sum(r);
+            if (lane == 0) out[q] = r;
+        }
+        if (lane == 0) {
+            *rb.ticket = 0u;
+            __threadfence();
+        }
+    }
+}
+
+#endif  // __CUDACC__
+
+}  // namespace cfdb

@@ -1,0 +1,18 @@
+// ns_args.h -- small by-value argument bundles of the RK stage kernel.
+#pragma once
+namespace cfdb {
+struct P4 {
+    const double* a[4];
+};
+struct W4 {
+    double* a[4];
+};
+struct RkArgs {
+    double fac_next;   // Q_{s+1} = Q0 + fac_next * k           (not last stage)
+    double w_k;        // acc += w_k * k  (first stage initialises acc instead)
+    double w_final;    // Q = Q0 + w_final * (acc + k)         (last stage)
+    int first, last;
+    int wrap_y, wrap_z;  // wrap neighbour indices locally (axis not decomposed over ranks)
+    double src_decay;    // exp(-lambda * iter * dt)
+};
+}  // namespace cfdb

@@ -1,0 +1,226 @@
+// ns_kernels2.cu -- RK2/RK4 stage kernel, periodic / thermal boundary conditions, field
+// statistics, synthetic initial state, small utilities.  See ns_kernels.cu for the citations.
+#include "common.cuh"
+#include "kernels.h"
+#include "ns_args.h"
+
+#include <limits.h>
+
+namespace cfdb {
+
+constexpr int TX = 32, TY = 8;
+
+struct March2 {
+    double m, c, p;
+};
+
+__device__ __forceinline__ double clampv(double lim, double v) { return fmax(-lim, fmin(lim, v)); }
+
+// ---------------------------------------------------------------------------------------
+// RK2 / RK4 stage, fused: k = RHS(Q_s) (ns_momentum_rhs_scalar.h:49-190, periodic-wrapped
+// neighbours, clamps), running weighted sum acc (same association order as the reference's
+// k1 + 2 k2 + 2 k3 + k4, solver_rk4.c:211-214), next stage state Q0 + f k or the final
+// combine (velocity clamp +-100).  Boundary cells are never read by the RHS (wrapped indices)
+// and are overwritten by the periodic BC after the step, so only interior cells are touched.
+// ---------------------------------------------------------------------------------------
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 qout,
+           const double* __restrict__ rho, const double* __restrict__ T,
+           const double* __restrict__ su_tab, const double* __restrict__ sv_tab, Ctl* ctl) {
+    const int i = blockIdx.x * TX + threadIdx.x, j = blockIdx.y * TY + threadIdx.y;
+    const int kb = g.k0 + blockIdx.z * zchunk, ke = min(kb + zchunk, g.k1);
+    if (!(i >= 1 && i < g.nx - 1 && j >= 1 && j < g.ny - 1)) return;
+    long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+    const long long oxm = (i > 1) ? -1 : (g.nx - 3), oxp = (i < g.nx - 2) ? 1 : -(g.nx - 3);
+    const long long oym = (j > 1 || !ra.wrap_y) ? -g.sy : (g.ny - 3) * g.sy;
+    const long long oyp = (j < g.ny - 2 || !ra.wrap_y) ? g.sy : -(g.ny - 3) * g.sy;
+    const double su = c.src_on ? su_tab[j] * ra.src_decay : 0.0;
+    const double sv = c.src_on ? sv_tab[i] * ra.src_decay : 0.0;
+    March2 F[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const long long zm = (kb > 1 || !ra.wrap_z) ? n - g.sz : n + (long long)(g.nz - 3) * g.sz;
+        F[q].m = D3 ? qin.a[q][zm] : 0.0;
+        F[q].c = qin.a[q][n];
+        F[q].p = 0.0;
+    }
+    bool bad = false;
+    for (int k = kb; k < ke; k++, n += g.sz) {
+        double d1[4][3], d2[3][3];  // first derivatives of u,v,w,p; second derivatives of u,v,w
+        const long long zp = (k < g.nz - 2 || !ra.wrap_z) ? n + g.sz : n - (long long)(g.nz - 3) * g.sz;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const double* f = qin.a[q];
+            if (D3) F[q].p = f[zp];
+            const double e = f[n + oxp], w_ = f[n + oxm], nn = f[n + oyp], s_ = f[n + oym], cc = F[q].c;
+            d1[q][0] = clampv(100.0, (e - w_) * g.inv_2dx);
+            d1[q][1] = clampv(100.0, (nn - s_) * g.inv_2dy);
+            d1[q][2] = clampv(100.0, (F[q].p - F[q].m) * g.inv_2dz);
+            if (q < 3) {
+                d2[q][0] = clampv(1000.0, (e - 2.0 * cc + w_) * g.inv_dx2);
+                d2[q][1] = clampv(1000.0, (nn - 2.0 * cc + s_) * g.inv_dy2);
+                d2[q][2] = clampv(1000.0, (F[q].p - 2.0 * cc + F[q].m) * g.inv_dz2);
+            }
+        }
+        const double rh = __ldg(rho + n);
+        double kq[4] = {0.0, 0.0, 0.0, 0.0};
+        if (rh > 1e-10) {
+            const double nu = fmin(c.mu / fmax(rh, 1e-10), 1.0);
+            double fu = su, fv = sv, fw = 0.0;
+            if (c.beta != 0.0) {
+                const double dT = __ldg(T + n) - c.T_ref;
+                fu += -c.beta * dT * c.gx;
+                fv += -c.beta * dT * c.gy;
+                fw += -c.beta * dT * c.gz;
+            }
+            const double uc = F[0].c, vc = F[1].c, wc = F[2].c, rinv = 1.0 / rh;
+            const double src[3] = {fu, fv, fw};
+#pragma unroll
+            for (int q = 0; q < 3; q++)
+                kq[q] = -uc * d1[q][0] - vc * d1[q][1] - wc * d1[q][2] - d1[3][q] * rinv +
+                        nu * (d2[q][0] + d2[q][1] + d2[q][2]) + src[q];
+            const double div = clampv(10.0, d1[0][0] + d1[1][1] + d1[2][2]);
+            kq[3] = -0.1 * rh * div;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const double base = ra.first ? F[q].c : __ldg(q0.a[q] + n);
+            double out;
+            if (ra.last) {
+                const double a_ = ra.first ? 0.0 : acc.a[q][n];
+                out = base + ra.w_final * (a_ + kq[q]);
+            } else {
+                acc.a[q][n] = ra.first ? kq[q] : acc.a[q][n] + ra.w_k * kq[q];
+                out = base + ra.fac_next * kq[q];
+            }
+            if (q < 3) out = clamp100(out);
+            qout.a[q][n] = out;
+            bad |= !isfinite(out);
+            F[q].m = F[q].c;
+            F[q].c = F[q].p;
+        }
+    }
+    if (bad && ra.last) ctl->nonfinite = 1;
+}
+
+// Periodic wrap of one field on every physical boundary (solver_explicit_euler.c:231-314):
+// x faces, then y faces, then z faces  ==>  closed form: boundary cell = wrapped interior cell.
+__global__ void k_periodic_bc(Geom g, double* f, int wrap_y, int wrap_z) {
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= g.ncell) return;
+    const int i = (int)(t % g.nx), j = (int)((t / g.nx) % g.ny), k = (int)(t / ((long long)g.nx * g.ny));
+    int ci = i, cj = j, ck = k;
+    if (i == 0) ci = g.nx - 2;
+    if (i == g.nx - 1) ci = 1;
+    if (wrap_y) {
+        if (j == 0) cj = g.ny - 2;
+        if (j == g.ny - 1) cj = 1;
+    }
+    if (g.dim3 && wrap_z) {
+        if (k == 0) ck = g.nz - 2;
+        if (k == g.nz - 1) ck = 1;
+    }
+    if (ci == i && cj == j && ck == k) return;
+    f[t] = f[(long long)ck * g.nx * g.ny + (long long)cj * g.nx + ci];
+}
+
+// Thermal BCs, one launch per axis, in the reference's order left/right, bottom/top, back/front
+// (energy_solver.c:246-331): later faces read cells already finalised by earlier ones.
+__global__ void k_thermal_bc(Geom g, double* T, int axis, int type_lo, int type_hi, double val_lo,
+                             double val_hi, int do_lo, int do_hi) {
+    // face extents: axis 0 -> (j,k), axis 1 -> (i,k), axis 2 -> (i,j)
+    const long long na = (axis == 0) ? g.ny : g.nx;
+    const long long nb = (axis == 2) ? g.ny : g.nz;
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= na * nb) return;
+    const long long a = t % na, b = t / na;
+    const long long plane = (long long)g.nx * g.ny;
+    const int n_ax = (axis == 0) ? g.nx : (axis == 1 ? g.ny : g.nz);
+    const long long st = (axis == 0) ? 1 : (axis == 1 ? g.nx : plane);
+    long long base;
+    if (axis == 0) base = b * plane + a * g.nx;
+    else if (axis == 1) base = b * plane + a;
+    else base = b * g.nx + a;
+    if (do_lo) {
+        double* c = T + base;
+        if (type_lo == BC_TYPE_DIRICHLET) *c = val_lo;
+        else if (type_lo == BC_TYPE_NEUMANN) *c = c[st];
+        else *c = c[(long long)(n_ax - 2) * st];
+    }
+    if (do_hi) {
+        double* c = T + base + (long long)(n_ax - 1) * st;
+        if (type_hi == BC_TYPE_DIRICHLET) *c = val_hi;
+        else if (type_hi == BC_TYPE_NEUMANN) *c = c[-st];
+        else *c = T[base + st];
+    }
+}
+
+// max sqrt(u^2+v^2+w^2), max |p|, max T over ALL cells (solver_registry.c:31-62).
+__global__ void __launch_bounds__(256)
+k_field_stats(Geom g, const double* __restrict__ u, const double* __restrict__ v,
+              const double* __restrict__ w, const double* __restrict__ p, const double* __restrict__ T,
+              Ctl* ctl, RedBuf rb) {
+    double m[3] = {0.0, 0.0, -INFINITY};
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < g.ncell; t += stride) {
+        const double a = u[t], b = v[t], c = w[t];
+        m[0] = fmax(m[0], sqrt(a * a + b * b + c * c));
+        m[1] = fmax(m[1], fabs(p[t]));
+        m[2] = fmax(m[2], T[t]);
+    }
+    block_reduce_finish<3, true>(m, rb, &ctl->stat[0]);
+}
+
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+// Synthetic state of SURVEY 8(d) C5: u = 0.1 sin2pix cos2piy cos2piz, v = -0.1 cos2pix sin2piy cos2piz,
+// w = 0, each + 1e-3 * splitmix64(seed, global idx) in [-1,1); p = 0, rho = 1, T = 300.
+__global__ void k_synth_init(Geom g, uint64_t seed, long long gk0, long long gnz, double* u, double* v,
+                             double* w, double* p, double* T, double* rho) {
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= g.ncell) return;
+    const int i = (int)(t % g.nx), j = (int)((t / g.nx) % g.ny);
+    const long long k = t / ((long long)g.nx * g.ny) + gk0;
+    const double tp = 6.283185307179586;
+    const double x = (double)i / (g.nx - 1), y = (double)j / (g.ny - 1);
+    const double z = gnz > 1 ? (double)k / (double)(gnz - 1) : 0.0;
+    const uint64_t gid = (uint64_t)((k * g.ny + j) * (long long)g.nx + i);
+    auto rnd = [&](uint64_t c) {
+        const uint64_t h = splitmix64(seed ^ (gid * 3ull + c));
+        return ((double)(h >> 11) * (1.0 / 9007199254740992.0)) * 2.0 - 1.0;
+    };
+    const double cz = g.dim3 ? cos(tp * z) : 1.0;
+    u[t] = 0.1 * sin(tp * x) * cos(tp * y) * cz + 1e-3 * rnd(0);
+    v[t] = -0.1 * cos(tp * x) * sin(tp * y) * cz + 1e-3 * rnd(1);
+    w[t] = g.dim3 ? 1e-3 * rnd(2) : 0.0;
+    p[t] = 0.0;
+    T[t] = 300.0;
+    if (rho) rho[t] = 1.0;
+}
+
+__global__ void k_copy(double* __restrict__ dst, const double* __restrict__ src, size_t n) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += stride) dst[t] = src[t];
+}
+
+__global__ void k_zero_ctl(Ctl* ctl) {
+    const int t = threadIdx.x;
+    if (t < 32) ctl->dot[t] = 0.0;
+    if (t == 0) {
+        ctl->tol = ctl->r0 = ctl->res = 0.0;
+        ctl->done_seq = INT_MAX;
+        ctl->status = POISSON_ERROR;
+        ctl->iterations = 0;
+        ctl->result_buf = 0;
+        ctl->skip_final_bc = 0;
+    }
+}
+
+#include "ns_launch2.inc"
+
+}  // namespace cfdb

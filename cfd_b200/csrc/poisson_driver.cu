@@ -1,0 +1,254 @@
+// poisson_driver.cu -- host drivers of the four Poisson methods.  The host only enqueues
+// kernels: batches of iterations are launched back to back, the device control block decides
+// convergence, and the host looks at a pinned copy of it one batch late (so the GPU never
+// waits for the CPU).  Launches after convergence are no-ops.
+#include "session.h"
+
+#include <limits.h>
+#include <math.h>
+
+namespace cfdb {
+
+namespace {
+
+struct Poll {
+    cfd_b200_session* s;
+    int batch = 0;
+    // enqueue a copy of the control block; returns true when an OLDER copy already shows "done"
+    bool step() {
+        const int cur = batch & 1;
+        cudaMemcpyAsync(&s->h_ctl[cur], s->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s->st);
+        cudaEventRecord(s->ev[cur], s->st);
+        bool done = false;
+        if (batch >= 1) {
+            cudaEventSynchronize(s->ev[cur ^ 1]);
+            done = s->h_ctl[cur ^ 1].done_seq != INT_MAX;
+        }
+        batch++;
+        return done;
+    }
+    // final: wait for everything and return the latest control block
+    const Ctl& final_state() {
+        cudaMemcpyAsync(&s->h_ctl[0], s->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s->st);
+        cudaStreamSynchronize(s->st);
+        return s->h_ctl[0];
+    }
+};
+
+int batch_size(const cfd_b200_session* s) {
+    // small grids: launch-bound, poll rarely; big grids: each iteration is milliseconds
+    const double cells = (double)s->N;
+    if (cells < 1e5) return 64;
+    if (cells < 4e6) return 32;
+    if (cells < 1e8) return 8;
+    return 4;
+}
+
+double optimal_omega(const cfd_b200_session_desc_t& d, size_t gnx, size_t gny, size_t gnz) {
+    // linear_solver_internal.h:184-220 (global extents)
+    const double ix = 1.0 / (d.dx * d.dx), iy = 1.0 / (d.dy * d.dy);
+    const double iz = (d.dz > 0.0) ? 1.0 / (d.dz * d.dz) : 0.0;
+    double num = cos(M_PI / (double)(gnx - 1)) * ix + cos(M_PI / (double)(gny - 1)) * iy;
+    double den = ix + iy;
+    if (gnz > 1 && iz > 0.0) {
+        num += cos(M_PI / (double)(gnz - 1)) * iz;
+        den += iz;
+    }
+    const double rj = num / den;
+    return 2.0 / (1.0 + sqrt(1.0 - (rj * rj)));
+}
+
+}  // namespace
+
+cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double** px,
+                           double** pxt, const double* rhs, poisson_solver_stats_t* out) {
+    const poisson_solver_params_t& pp = cfg->params;
+    const LaunchCtx L = s->L();
+    const int R = s->desc.nranks;
+    KArgs a;
+    a.seq = 0;
+    a.it = 0;
+    a.check = pp.check_interval > 0 ? pp.check_interval : 1;
+    a.max_iter = pp.max_iterations;
+    a.rel_tol = pp.tolerance;
+    a.abs_tol = pp.absolute_tolerance;
+    a.dinv = 1.0 / (2.0 * s->g.inv_dx2 + 2.0 * s->g.inv_dy2 + 2.0 * s->g.inv_dz2);
+    a.zchunk = s->zchunk;
+    {
+        // global extents along the decomposed axis (every rank owns n-2 interior layers)
+        size_t gnx = s->desc.nx, gny = s->desc.ny, gnz = s->desc.nz;
+        // NOTE: uniform slabs assumed for the omega formula; set via session extension if not
+        if (R > 1) {
+            if (s->g.dim3) gnz = (s->desc.nz - 2) * (size_t)R + 2;
+            else gny = (s->desc.ny - 2) * (size_t)R + 2;
+        }
+        a.omega = pp.omega > 0.0 ? pp.omega : optimal_omega(s->desc, gnx, gny, gnz);
+    }
+    launch_zero_ctl(L);
+    Poll poll{s};
+    const int B = batch_size(s);
+    double* x = *px;
+    int seq = 1;
+    const int method = cfg->method;
+    cfd_status_t rc = CFD_SUCCESS;
+
+    if (method == POISSON_METHOD_JACOBI) {
+        if (!pxt || !*pxt) return CFD_ERROR_INVALID;
+        double* buf[2] = {x, *pxt};
+        // sweeps q = 0..max_iter (sweep q computes res(x_q)); then the final decision
+        for (int q = 0; q <= a.max_iter;) {
+            for (int b = 0; b < B && q <= a.max_iter; b++, q++) {
+                a.seq = seq++;
+                a.it = q;
+                launch_jacobi(L, a, buf[q & 1], buf[(q + 1) & 1], rhs);
+                if (R > 1) {
+                    double* f[1] = {buf[(q + 1) & 1]};
+                    halo_exchange(s, f, 1, false);
+                    allreduce(s, &s->ctl->dot[q & 1], 1, true);
+                }
+            }
+            if (poll.step()) break;
+        }
+        a.seq = seq++;
+        a.it = a.max_iter;
+        launch_stationary_final(L, a);
+        const Ctl& c = poll.final_state();
+        if (c.result_buf == 1) {  // x lives in the ping-pong partner: swap the caller's pointers
+            *px = buf[1];
+            *pxt = buf[0];
+        }
+    } else if (method == POISSON_METHOD_REDBLACK_SOR) {
+        a.seq = seq++;
+        launch_linf_residual(L, a, x, rhs, 0);
+        if (R > 1) allreduce(s, &s->ctl->dot[0], 1, true);
+        for (int it = 0; it < a.max_iter;) {
+            for (int b = 0; b < B && it < a.max_iter; b++, it++) {
+                a.it = it;
+                double* f[1] = {x};
+                a.seq = seq++;
+                launch_redblack(L, a, x, rhs, 0, 1);
+                if (R > 1) halo_exchange(s, f, 1, false);
+                a.seq = seq++;
+                launch_redblack(L, a, x, rhs, 1, 0);
+                if (R > 1) halo_exchange(s, f, 1, false);
+                if (it % a.check == 0) {
+                    a.seq = seq++;
+                    launch_linf_residual(L, a, x, rhs, (it + 1) & 1);
+                    if (R > 1) allreduce(s, &s->ctl->dot[(it + 1) & 1], 1, true);
+                }
+            }
+            if (poll.step()) break;
+        }
+        a.seq = seq++;
+        a.it = a.max_iter;
+        launch_stationary_final(L, a);
+        (void)poll.final_state();
+    } else if (method == POISSON_METHOD_CG) {
+        const int pre = (pp.preconditioner == POISSON_PRECOND_JACOBI);
+        for (int q = 0; q < 4; q++)
+            if ((rc = dalloc(s, &s->kv[q])) != CFD_SUCCESS) return rc;
+        double *r = s->kv[0], *Ap = s->kv[1], *pb[2] = {s->kv[2], s->kv[3]};
+        launch_neumann_fill(L, x, 0, 0, false);
+        a.seq = seq++;
+        launch_krylov_init(L, a, x, rhs, r, pb[0], nullptr, pre);
+        if (R > 1) {
+            double* f[2] = {r, pb[0]};
+            halo_exchange(s, f, 2, false);
+            allreduce(s, &s->ctl->dot[0], 2, false);
+        }
+        for (int it = 0; it < a.max_iter;) {
+            for (int b = 0; b < B && it < a.max_iter; b++, it++) {
+                a.it = it;
+                a.seq = seq++;
+                // iteration it: p_it lives in pb[it&1]; it == 0 only applies A to p_0
+                double* pold = (it == 0) ? pb[0] : pb[(it - 1) & 1];
+                double* pnew = pb[it & 1];
+                launch_cg_dir(L, a, r, pold, pnew, Ap, pre, 0);
+                if (R > 1) allreduce(s, &s->ctl->dot[4 + (it & 1)], 1, false);
+                a.seq = seq++;
+                launch_cg_update(L, a, x, r, pnew, Ap, pre);
+                if (R > 1) {
+                    double* f[1] = {r};
+                    halo_exchange(s, f, 1, false);
+                    allreduce(s, &s->ctl->dot[2 * ((it + 1) & 1)], 2, false);
+                }
+            }
+            if (poll.step()) break;
+        }
+        a.seq = seq++;
+        a.it = a.max_iter;
+        launch_cg_dir(L, a, r, pb[0], pb[1], Ap, pre, 1);
+        launch_neumann_fill(L, x, 0, 1, true);
+        (void)poll.final_state();
+    } else if (method == POISSON_METHOD_BICGSTAB) {
+        for (int q = 0; q < 8; q++)
+            if ((rc = dalloc(s, &s->kv[q])) != CFD_SUCCESS) return rc;
+        double *r = s->kv[0], *rh = s->kv[1], *sv = s->kv[2], *tv = s->kv[3];
+        double *pb[2] = {s->kv[4], s->kv[5]}, *vb[2] = {s->kv[6], s->kv[7]};
+        launch_neumann_fill(L, x, 0, 0, false);
+        a.seq = seq++;
+        launch_krylov_init(L, a, x, rhs, r, nullptr, rh, 0);
+        if (R > 1) {
+            double* f[1] = {r};
+            halo_exchange(s, f, 1, false);
+            allreduce(s, &s->ctl->dot[0], 2, false);
+        }
+        for (int it = 0; it < a.max_iter;) {
+            for (int b = 0; b < B && it < a.max_iter; b++, it++) {
+                a.it = it;
+                a.seq = seq++;
+                double *pold = pb[(it + 1) & 1], *pnew = pb[it & 1];
+                double *vold = vb[(it + 1) & 1], *vnew = vb[it & 1];
+                launch_bicg_dir(L, a, r, pold, vold, rh, pnew, vnew, it == 0, 0);
+                if (R > 1) {
+                    double* f[1] = {vnew};
+                    halo_exchange(s, f, 1, false);
+                    allreduce(s, &s->ctl->dot[4 + (it & 1)], 1, false);
+                }
+                a.seq = seq++;
+                launch_bicg_s(L, a, r, vnew, sv, tv);
+                if (R > 1) allreduce(s, &s->ctl->dot[8 + 4 * (it & 1)], 3, false);
+                a.seq = seq++;
+                launch_bicg_update(L, a, x, r, pnew, sv, tv, rh);
+                if (R > 1) {
+                    double* f[1] = {r};
+                    halo_exchange(s, f, 1, false);
+                    allreduce(s, &s->ctl->dot[2 * ((it + 1) & 1)], 2, false);
+                }
+            }
+            if (poll.step()) break;
+        }
+        a.seq = seq++;
+        a.it = a.max_iter;
+        launch_bicg_dir(L, a, r, pb[0], vb[0], rh, pb[1], vb[1], 0, 1);
+        launch_neumann_fill(L, x, 0, 1, true);
+        (void)poll.final_state();
+    } else {
+        set_error(CFD_ERROR_UNSUPPORTED, "Poisson method %d has no GPU implementation", method);
+        return CFD_ERROR_UNSUPPORTED;
+    }
+
+    cudaError_t ce = cudaGetLastError();
+    if (ce != cudaSuccess) {
+        set_error(CFD_ERROR, "CUDA failure in Poisson solve: %s", cudaGetErrorString(ce));
+        return CFD_ERROR;
+    }
+    const Ctl& c = s->h_ctl[0];
+    poisson_solver_stats_t st;
+    st.status = (poisson_solver_status_t)c.status;
+    st.iterations = c.iterations;
+    st.initial_residual = c.r0;
+    st.final_residual = c.res;
+    st.elapsed_time_ms = 0.0;
+    if (c.done_seq == INT_MAX) st.status = POISSON_ERROR;
+    s->last_ps = st;
+    if (out) *out = st;
+    if (R > 1) {  // make the halo of the solution current for the caller
+        double* f[1] = {*px};
+        halo_exchange(s, f, 1, false);
+    }
+    return st.status == POISSON_CONVERGED ? CFD_SUCCESS
+                                          : (st.status == POISSON_ERROR ? CFD_ERROR : CFD_ERROR_MAX_ITER);
+}
+
+}  // namespace cfdb

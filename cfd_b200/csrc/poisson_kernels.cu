@@ -1,0 +1,630 @@
+// poisson_kernels.cu -- pressure-Poisson kernels: Jacobi, Red-Black SOR, CG/PCG, BiCGSTAB.
+//
+// Reference semantics followed (file:line under /root/reference/lib/src/solvers/linear):
+//   linear_solver.c:304-346 (L-inf residual), :348-392 (Neumann BC), :397-485 (stationary driver)
+//   cpu/linear_solver_jacobi.c:76-129, cpu/linear_solver_redblack.c:79-146,
+//   cpu/linear_solver_cg.c:290-461, cpu/linear_solver_bicgstab.c:265-495.
+//
+// Design (B200): every kernel is a 2.5-D sweep -- a block owns an x-y tile and marches a chunk
+// of z planes keeping the z-1/z/z+1 values of each stencil operand in registers; in-plane
+// neighbours come through L1.  All solver scalars (dots, alpha/beta/omega, tolerances, the
+// convergence decision) live in a device control block (Ctl); reductions are finished by the
+// last block with a fixed summation order, so there is no host synchronisation and no
+// floating-point atomics anywhere inside an iteration.
+#include "common.cuh"
+#include "kernels.h"
+
+#include <limits.h>
+
+namespace cfdb {
+
+constexpr int TX = 32, TY = 8;  // thread tile (x fastest): 256 threads, 8 warps
+
+__device__ __forceinline__ bool leader() {
+    return (blockIdx.x | blockIdx.y | blockIdx.z | threadIdx.x | threadIdx.y) == 0;
+}
+
+// Column owned by this thread and the z chunk of this block.  Returns whether (i,j) is an
+// interior column (the only ones that are updated).
+__device__ __forceinline__ bool column(const Geom& g, int zchunk, int& i, int& j, int& kb, int& ke) {
+    i = blockIdx.x * TX + threadIdx.x;
+    j = blockIdx.y * TY + threadIdx.y;
+    kb = g.k0 + blockIdx.z * zchunk;
+    ke = min(kb + zchunk, g.k1);
+    return i >= 1 && i < g.nx - 1 && j >= 1 && j < g.ny - 1;
+}
+
+// Store v at interior cell n=(i,j,k) and at every physical ghost cell whose nearest interior
+// cell it is.  This is the closed form of the reference's sequential Neumann pass
+// (linear_solver.c:367-391 + boundary_conditions_core_impl.h:46-69): ghost = clamped interior.
+template <bool D3>
+__device__ __forceinline__ void store_with_ghosts(const Geom& g, double* x, int i, int j, int k,
+                                                  long long n, double v) {
+    x[n] = v;
+    const bool ex = (i == 1) | (i == g.nx - 2), ey = (j == 1) | (j == g.ny - 2);
+    const bool ez = D3 && ((k == 1) | (k == g.nz - 2));
+    if (!(ex | ey | ez)) return;
+    long long ox[3] = {0, 0, 0}, oy[3] = {0, 0, 0}, oz[3] = {0, 0, 0};
+    int cx = 1, cy = 1, cz = 1;
+    if (i == 1 && g.glo[0]) ox[cx++] = -1;
+    if (i == g.nx - 2 && g.ghi[0]) ox[cx++] = 1;
+    if (j == 1 && g.glo[1]) oy[cy++] = -g.sy;
+    if (j == g.ny - 2 && g.ghi[1]) oy[cy++] = g.sy;
+    if (D3) {
+        if (k == 1 && g.glo[2]) oz[cz++] = -g.sz;
+        if (k == g.nz - 2 && g.ghi[2]) oz[cz++] = g.sz;
+    }
+    for (int c = 0; c < cz; c++)
+        for (int b = 0; b < cy; b++)
+            for (int a = 0; a < cx; a++)
+                if (a | b | c) x[n + ox[a] + oy[b] + oz[c]] = v;
+}
+
+// ---------------------------------------------------------------------------------------
+// Neumann ghost fill as a stand-alone pass ("apply BC" at the start/end of the Krylov solves).
+// One thread per cell of the local slab; ghost cells read their clamped interior source.
+// Halo planes (non-physical sides) are left untouched.
+// ---------------------------------------------------------------------------------------
+__global__ void k_neumann_fill(Geom g, double* x, const Ctl* ctl, int seq, int honour_skip) {
+    if (ctl && seq > ctl->done_seq && !honour_skip) return;
+    if (ctl && honour_skip && ctl->skip_final_bc) return;
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= g.ncell) return;
+    int i = (int)(t % g.nx);
+    int j = (int)((t / g.nx) % g.ny);
+    int k = (int)(t / ((long long)g.nx * g.ny));
+    int ci = i, cj = j, ck = k;
+    if (i == 0 && g.glo[0]) ci = 1;
+    if (i == g.nx - 1 && g.ghi[0]) ci = g.nx - 2;
+    if (j == 0 && g.glo[1]) cj = 1;
+    if (j == g.ny - 1 && g.ghi[1]) cj = g.ny - 2;
+    if (g.dim3) {
+        if (k == 0 && g.glo[2]) ck = 1;
+        if (k == g.nz - 1 && g.ghi[2]) ck = g.nz - 2;
+    }
+    if (ci == i && cj == j && ck == k) return;
+    // a ghost cell on a halo plane/row mirrors a cell of that same halo plane: leave it to the exchange
+    if (g.dim3 ? ((k == 0 && !g.glo[2]) || (k == g.nz - 1 && !g.ghi[2]))
+               : ((j == 0 && !g.glo[1]) || (j == g.ny - 1 && !g.ghi[1])))
+        return;
+    x[t] = x[(long long)ck * g.nx * g.ny + (long long)cj * g.nx + ci];
+}
+
+// ---------------------------------------------------------------------------------------
+// Stationary methods: shared convergence decision (linear_solver.c:415-484).
+// Called by every thread at the start of the kernel that would begin iteration s, when the
+// L-inf residual of x_s sits in dot[s&1].  Returns true when the kernel must not run.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ bool stationary_decide(Ctl* ctl, const KArgs& a) {
+    if (a.seq > ctl->done_seq) return true;
+    const int s = a.it;
+    const double res = ctl->dot[s & 1];
+    bool fin = false, checked = true;
+    int status = POISSON_CONVERGED, iters = 0;
+    double tol;
+    if (s == 0) {
+        tol = fmax(a.rel_tol * res, a.abs_tol);
+        if (res < a.abs_tol) fin = true;
+    } else {
+        tol = ctl->tol;
+        checked = ((s - 1) % a.check) == 0;
+        if (checked && (res < tol || res < a.abs_tol)) {
+            fin = true;
+            iters = s;
+        } else if (s >= a.max_iter) {
+            fin = true;
+            status = POISSON_MAX_ITER;
+            iters = a.max_iter + 1;  // reference reports iter+1 after the loop ran out (:478)
+        }
+    }
+    if (leader()) {
+        if (s == 0) {
+            ctl->r0 = res;
+            ctl->tol = tol;
+        }
+        if (checked) ctl->res = res;
+        if (fin) {
+            ctl->status = status;
+            ctl->iterations = iters;
+            ctl->result_buf = s & 1;
+            ctl->skip_final_bc = 0;
+            ctl->done_seq = a.seq - 1;
+        }
+    }
+    return fin;
+}
+
+__global__ void k_stationary_final(Ctl* ctl, KArgs a) { (void)stationary_decide(ctl, a); }
+
+// Jacobi sweep s: reads x_s (ghosts valid), writes x_{s+1} with its Neumann ghosts, and gets
+// the L-inf residual of x_s for free from the same loads.  24 B/cell: x in, rhs in, x out.
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_jacobi(Geom g, const double* __restrict__ xin, double* __restrict__ xout,
+         const double* __restrict__ rhs, Ctl* ctl, RedBuf rb, KArgs a) {
+    // sweep q decides about x_{q-1}, whose residual sweep q-1 left in dot[(q-1)&1]
+    if (a.it > 0) {
+        KArgs d = a;
+        d.it = a.it - 1;
+        if (stationary_decide(ctl, d)) return;
+    } else if (a.seq > ctl->done_seq) {
+        return;
+    }
+    int i, j, kb, ke;
+    const bool act = column(g, a.zchunk, i, j, kb, ke);
+    double rmax[1] = {0.0};
+    if (act) {
+        long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+        double zm = D3 ? xin[n - g.sz] : 0.0, zc = xin[n], zp = 0.0;
+        for (int k = kb; k < ke; k++, n += g.sz) {
+            if (D3) zp = xin[n + g.sz];
+            const double xe = xin[n + 1], xw = xin[n - 1], yn = xin[n + g.sy], ys = xin[n - g.sy];
+            const double f = __ldg(rhs + n);
+            const double lap = (xe - 2.0 * zc + xw) * g.inv_dx2 + (yn - 2.0 * zc + ys) * g.inv_dy2 +
+                               (zp + zm - 2.0 * zc) * g.inv_dz2;
+            rmax[0] = fmax(rmax[0], fabs(lap - f));
+            const double v = -(f - (xe + xw) * g.inv_dx2 - (yn + ys) * g.inv_dy2 -
+                               (zp + zm) * g.inv_dz2) * g.inv_factor;
+            store_with_ghosts<D3>(g, xout, i, j, k, n, v);
+            zm = zc;
+            zc = zp;
+        }
+    }
+    block_reduce_finish<1, true>(rmax, rb, &ctl->dot[a.it & 1]);
+}
+
+// One colour of Red-Black SOR, in place.  colour 0 = (i+j+k) even (global indices).
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_redblack(Geom g, double* x, const double* __restrict__ rhs, Ctl* ctl, KArgs a, int colour,
+           int decide) {
+    if (decide ? stationary_decide(ctl, a) : (a.seq > ctl->done_seq)) return;
+    int i, j, kb, ke;
+    if (!column(g, a.zchunk, i, j, kb, ke)) return;
+    long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+    const int par0 = (int)((g.gi0 + i + g.gj0 + j + g.gk0) & 1);
+    for (int k = kb; k < ke; k++, n += g.sz) {
+        if (((par0 + k) & 1) != colour) continue;
+        const double zp = D3 ? x[n + g.sz] : 0.0, zm = D3 ? x[n - g.sz] : 0.0;
+        const double pn = -(__ldg(rhs + n) - (x[n + 1] + x[n - 1]) * g.inv_dx2 -
+                            (x[n + g.sy] + x[n - g.sy]) * g.inv_dy2 - (zp + zm) * g.inv_dz2) *
+                          g.inv_factor;
+        const double xc = x[n];
+        store_with_ghosts<D3>(g, x, i, j, k, n, xc + a.omega * (pn - xc));
+    }
+}
+
+// L-inf residual of x (after BC) into dot[slot] -- linear_solver.c:304-346.
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_linf_residual(Geom g, const double* __restrict__ x, const double* __restrict__ rhs, Ctl* ctl,
+                RedBuf rb, KArgs a, int slot) {
+    if (a.seq > ctl->done_seq) return;
+    int i, j, kb, ke;
+    const bool act = column(g, a.zchunk, i, j, kb, ke);
+    double rmax[1] = {0.0};
+    if (act) {
+        long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+        double zm = D3 ? x[n - g.sz] : 0.0, zc = x[n], zp = 0.0;
+        for (int k = kb; k < ke; k++, n += g.sz) {
+            if (D3) zp = x[n + g.sz];
+            const double lap = (x[n + 1] - 2.0 * zc + x[n - 1]) * g.inv_dx2 +
+                               (x[n + g.sy] - 2.0 * zc + x[n - g.sy]) * g.inv_dy2 +
+                               (zp + zm - 2.0 * zc) * g.inv_dz2;
+            rmax[0] = fmax(rmax[0], fabs(lap - __ldg(rhs + n)));
+            zm = zc;
+            zc = zp;
+        }
+    }
+    block_reduce_finish<1, true>(rmax, rb, &ctl->dot[slot]);
+}
+
+
+// =======================================================================================
+// Krylov solvers.  A = -lap on interior cells; r, p, v, s, t keep ZERO on physical boundary
+// cells (never written), exactly as the reference's calloc'ed work vectors.
+// Dot slots in Ctl::dot  (par = iteration parity, so a kernel never overwrites a value that
+// late-starting blocks of the same launch still have to read):
+//   CG      : [2*par+0]=r.r  [2*par+1]=r.z   [4+par]=p.Ap
+//   BiCGSTAB: [2*par+0]=r.r  [2*par+1]=rhat.r  [4+par]=rhat.v  [8+4*par+{0,1,2}]=s.s, t.s, t.t
+// =======================================================================================
+
+__device__ __forceinline__ void finish(Ctl* ctl, const KArgs& a, int status, int iters, double res,
+                                       int skip_bc, int after_this_kernel) {
+    if (!leader()) return;
+    ctl->status = status;
+    ctl->iterations = iters;
+    ctl->res = res;
+    ctl->skip_final_bc = skip_bc;
+    ctl->done_seq = after_this_kernel ? a.seq : a.seq - 1;
+}
+
+// r = -rhs + lap(x) (linear_solver_cg.c:134-158), d0 = r or dinv*r into p (CG), rhat = r (BiCGSTAB).
+// Dots: r.r and r.z (CG) / r.r twice (BiCGSTAB: rhat.r == r.r at start).
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_krylov_init(Geom g, const double* __restrict__ x, const double* __restrict__ rhs,
+              double* __restrict__ r, double* __restrict__ p0, double* __restrict__ rhat, Ctl* ctl,
+              RedBuf rb, KArgs a, int precond) {
+    int i, j, kb, ke;
+    const bool act = column(g, a.zchunk, i, j, kb, ke);
+    double acc[2] = {0.0, 0.0};
+    if (act) {
+        long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+        double zm = D3 ? x[n - g.sz] : 0.0, zc = x[n], zp = 0.0;
+        for (int k = kb; k < ke; k++, n += g.sz) {
+            if (D3) zp = x[n + g.sz];
+            const double lap = (x[n + 1] - 2.0 * zc + x[n - 1]) * g.inv_dx2 +
+                               (x[n + g.sy] - 2.0 * zc + x[n - g.sy]) * g.inv_dy2 +
+                               (zp + zm - 2.0 * zc) * g.inv_dz2;
+            const double rv = -__ldg(rhs + n) + lap;
+            r[n] = rv;
+            const double zv = precond ? a.dinv * rv : rv;
+            if (p0) p0[n] = zv;
+            if (rhat) rhat[n] = rv;
+            acc[0] += rv * rv;
+            acc[1] += rv * zv;
+            zm = zc;
+            zc = zp;
+        }
+    }
+    block_reduce_finish<2, false>(acc, rb, &ctl->dot[0]);
+}
+
+// Generic fused "direction update + mat-vec + dots" sweep:
+//   c(n)   = Op::comb(n)              (a linear combination of up to three vectors)
+//   cout   = c                        (written on owned cells and on halo planes)
+//   aout   = A c = -lap(c)
+//   dots   = Op::dots(...)
+// c is re-evaluated at the four in-plane neighbours (their operands come through L1) and
+// carried in registers along z, so each operand is read once from HBM.
+template <bool D3, class Op>
+__device__ __forceinline__ void comb_matvec(const Geom& g, const KArgs& a, const Op& op,
+                                            double* __restrict__ cout, double* __restrict__ aout,
+                                            double (&acc)[Op::NV]) {
+    int i, j, kb, ke;
+    if (!column(g, a.zchunk, i, j, kb, ke)) return;
+    long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+    double cm = D3 ? op.comb(n - g.sz) : 0.0, cc = op.comb(n), cp = 0.0;
+    if (D3 && kb == 1 && !g.glo[2]) cout[n - g.sz] = cm;  // keep the low halo plane of c current
+    for (int k = kb; k < ke; k++, n += g.sz) {
+        if (D3) cp = op.comb(n + g.sz);
+        const double ce = op.comb(n + 1), cw = op.comb(n - 1);
+        const double cn = op.comb(n + g.sy), cs = op.comb(n - g.sy);
+        const double Ac = -((ce - 2.0 * cc + cw) * g.inv_dx2 + (cn - 2.0 * cc + cs) * g.inv_dy2 +
+                            (cp + cm - 2.0 * cc) * g.inv_dz2);
+        cout[n] = cc;
+        aout[n] = Ac;
+        op.dots(n, cc, Ac, acc);
+        cm = cc;
+        cc = cp;
+    }
+    if (D3 && ke == g.nz - 1 && !g.ghi[2]) cout[n] = cc;  // high halo plane (n == plane nz-1 now)
+}
+
+// ---- CG -------------------------------------------------------------------------------
+struct CgDirOp {
+    static constexpr int NV = 1;
+    const double* r;
+    const double* pold;
+    double beta, dinv;
+    int first, precond;
+    __device__ __forceinline__ double comb(long long n) const {
+        const double po = __ldg(pold + n);
+        if (first) return po;
+        const double rv = __ldg(r + n);
+        return (precond ? dinv * rv : rv) + beta * po;
+    }
+    __device__ __forceinline__ void dots(long long, double c, double Ac, double (&acc)[1]) const {
+        acc[0] += c * Ac;
+    }
+};
+
+// Start of CG iteration `it`: convergence / breakdown decisions of iteration it-1
+// (linear_solver_cg.c:397-415), then p = z + beta p, Ap = A p, p.Ap.
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_cg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold,
+         double* __restrict__ pnew, double* __restrict__ Ap, Ctl* ctl, RedBuf rb, KArgs a,
+         int precond, int decide_only) {
+    if (a.seq > ctl->done_seq) return;
+    const int it = a.it, par = it & 1;
+    const double rr = ctl->dot[2 * par], rho_new = ctl->dot[2 * par + precond];
+    const double res = sqrt(rr);
+    double beta = 0.0;
+    if (it == 0) {
+        const double tol = fmax(a.rel_tol * res, a.abs_tol);
+        if (leader()) {
+            ctl->r0 = res;
+            ctl->tol = tol;
+        }
+        if (res < a.abs_tol) {
+            finish(ctl, a, POISSON_CONVERGED, 0, res, 1, 0);
+            return;
+        }
+    } else {
+        const double tol = ctl->tol;
+        const double rho_old = ctl->dot[2 * (par ^ 1) + precond];
+        const bool conv = (res < tol || res < a.abs_tol);
+        if (((it - 1) % a.check) == 0 && conv) {
+            finish(ctl, a, POISSON_CONVERGED, it, res, 0, 0);
+            return;
+        }
+        if (fabs(rho_old) < 1e-30) {
+            finish(ctl, a, POISSON_STAGNATED, it, res, 1, 0);
+            return;
+        }
+        if (it >= a.max_iter) {
+            finish(ctl, a, conv ? POISSON_CONVERGED : POISSON_MAX_ITER, a.max_iter, res, 0, 0);
+            return;
+        }
+        beta = rho_new / rho_old;
+    }
+    if (decide_only) return;
+    CgDirOp op{r, pold, beta, a.dinv, it == 0, precond};
+    double acc[1] = {0.0};
+    comb_matvec<D3>(g, a, op, pnew, Ap, acc);
+    block_reduce_finish<1, false>(acc, rb, &ctl->dot[4 + par]);
+}
+
+// alpha = rho / p.Ap ; x += alpha p ; r -= alpha Ap ; r.r and r.z  (linear_solver_cg.c:372-397)
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_cg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
+            const double* __restrict__ Ap, Ctl* ctl, RedBuf rb, KArgs a, int precond) {
+    if (a.seq > ctl->done_seq) return;
+    const int par = a.it & 1;
+    const double pAp = ctl->dot[4 + par];
+    if (fabs(pAp) < 1e-30) {
+        finish(ctl, a, POISSON_STAGNATED, a.it + 1, a.it == 0 ? ctl->r0 : sqrt(ctl->dot[2 * par]), 1, 0);
+        return;
+    }
+    const double alpha = ctl->dot[2 * par + precond] / pAp;
+    int i, j, kb, ke;
+    const bool act = column(g, a.zchunk, i, j, kb, ke);
+    double acc[2] = {0.0, 0.0};
+    if (act) {
+        long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+        for (int k = kb; k < ke; k++, n += g.sz) {
+            x[n] += alpha * __ldg(p + n);
+            const double rv = r[n] - alpha * __ldg(Ap + n);
+            r[n] = rv;
+            acc[0] += rv * rv;
+            acc[1] += rv * (a.dinv * rv);
+        }
+    }
+    block_reduce_finish<2, false>(acc, rb, &ctl->dot[2 * (par ^ 1)]);
+}
+
+// ---- BiCGSTAB -------------------------------------------------------------------------
+struct BiDirOp {  // p = r + beta (p - omega v) ; v = A p ; rhat.v
+    static constexpr int NV = 1;
+    const double *r, *pold, *vold, *rhat;
+    double beta, omega;
+    int first;  // iteration 0: p = v = 0 (linear_solver_bicgstab.c:307-308) without reading them
+    __device__ __forceinline__ double comb(long long n) const {
+        const double rv = __ldg(r + n);
+        if (first) return rv;
+        return rv + beta * (__ldg(pold + n) - omega * __ldg(vold + n));
+    }
+    __device__ __forceinline__ void dots(long long n, double, double Ac, double (&acc)[1]) const {
+        acc[0] += __ldg(rhat + n) * Ac;
+    }
+};
+struct BiSOp {  // s = r - alpha v ; t = A s ; s.s, t.s, t.t
+    static constexpr int NV = 3;
+    const double *r, *v;
+    double alpha;
+    __device__ __forceinline__ double comb(long long n) const {
+        return __ldg(r + n) - alpha * __ldg(v + n);
+    }
+    __device__ __forceinline__ void dots(long long, double c, double Ac, double (&acc)[3]) const {
+        acc[0] += c * c;
+        acc[1] += Ac * c;
+        acc[2] += Ac * Ac;
+    }
+};
+
+// Scalars of BiCGSTAB iteration `it` recomputed from the raw dots (cheap, avoids a control kernel).
+__device__ __forceinline__ double bi_alpha(const Ctl* ctl, int it) {
+    return ctl->dot[2 * (it & 1) + 1] / ctl->dot[4 + (it & 1)];
+}
+__device__ __forceinline__ double bi_omega(const Ctl* ctl, int it) {
+    return ctl->dot[8 + 4 * (it & 1) + 1] / ctl->dot[8 + 4 * (it & 1) + 2];
+}
+
+// Start of iteration `it` (linear_solver_bicgstab.c:338-370 preceded by the tail checks :451-474
+// of iteration it-1).
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_bicg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold,
+           const double* __restrict__ vold, const double* __restrict__ rhat,
+           double* __restrict__ pnew, double* __restrict__ vnew, Ctl* ctl, RedBuf rb, KArgs a,
+           int decide_only) {
+    if (a.seq > ctl->done_seq) return;
+    const int it = a.it, par = it & 1;
+    const double res = sqrt(ctl->dot[2 * par]);
+    const double rho_new = ctl->dot[2 * par + 1];
+    double beta, omega_old = 1.0;
+    if (it == 0) {
+        const double tol = fmax(a.rel_tol * res, a.abs_tol);
+        if (leader()) {
+            ctl->r0 = res;
+            ctl->tol = tol;
+        }
+        if (res < a.abs_tol) {
+            finish(ctl, a, POISSON_CONVERGED, 0, res, 1, 0);
+            return;
+        }
+        if (fabs(rho_new) < 1e-30) {
+            finish(ctl, a, POISSON_STAGNATED, 1, res, 1, 0);
+            return;
+        }
+        beta = rho_new;  // (rho_new / 1) * (1 / 1)
+    } else {
+        const double tol = ctl->tol;
+        const bool conv = (res < tol || res < a.abs_tol);
+        if (((it - 1) % a.check) == 0 && conv) {
+            finish(ctl, a, POISSON_CONVERGED, it, res, 0, 0);
+            return;
+        }
+        omega_old = bi_omega(ctl, it - 1);
+        if (fabs(omega_old) < 1e-30) {
+            finish(ctl, a, POISSON_STAGNATED, it, res, 1, 0);
+            return;
+        }
+        if (it >= a.max_iter) {
+            finish(ctl, a, conv ? POISSON_CONVERGED : POISSON_MAX_ITER, a.max_iter, res, 0, 0);
+            return;
+        }
+        if (fabs(rho_new) < 1e-30) {
+            finish(ctl, a, POISSON_STAGNATED, it + 1, res, 1, 0);
+            return;
+        }
+        const double rho_old = ctl->dot[2 * (par ^ 1) + 1];
+        beta = (rho_new / rho_old) * (bi_alpha(ctl, it - 1) / omega_old);
+    }
+    if (decide_only) return;
+    BiDirOp op{r, pold, vold, rhat, beta, omega_old, it == 0};
+    double acc[1] = {0.0};
+    comb_matvec<D3>(g, a, op, pnew, vnew, acc);
+    block_reduce_finish<1, false>(acc, rb, &ctl->dot[4 + par]);
+}
+
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_bicg_s(Geom g, const double* __restrict__ r, const double* __restrict__ v,
+         double* __restrict__ s, double* __restrict__ t, Ctl* ctl, RedBuf rb, KArgs a) {
+    if (a.seq > ctl->done_seq) return;
+    const int par = a.it & 1;
+    const double rhv = ctl->dot[4 + par];
+    if (fabs(rhv) < 1e-30) {
+        finish(ctl, a, POISSON_STAGNATED, a.it + 1, a.it == 0 ? ctl->r0 : sqrt(ctl->dot[2 * par]), 1, 0);
+        return;
+    }
+    BiSOp op{r, v, ctl->dot[2 * par + 1] / rhv};
+    double acc[3] = {0.0, 0.0, 0.0};
+    comb_matvec<D3>(g, a, op, s, t, acc);
+    block_reduce_finish<3, false>(acc, rb, &ctl->dot[8 + 4 * par]);
+}
+
+// Tail of the iteration (:396-451): early exit on ||s||, omega, x and r updates, r.r and rhat.r.
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_bicg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
+              const double* __restrict__ s, const double* __restrict__ t,
+              const double* __restrict__ rhat, Ctl* ctl, RedBuf rb, KArgs a) {
+    if (a.seq > ctl->done_seq) return;
+    const int par = a.it & 1;
+    const double alpha = bi_alpha(ctl, a.it);
+    const double sn = sqrt(ctl->dot[8 + 4 * par]);
+    const double tt = ctl->dot[8 + 4 * par + 2];
+    const double tol = ctl->tol;
+    int mode = 0;  // 0 full update, 1 x += alpha p only (then stop)
+    if (sn < tol || sn < a.abs_tol) {
+        mode = 1;
+        finish(ctl, a, POISSON_CONVERGED, a.it + 1, sn, 0, 1);
+    } else if (fabs(tt) < 1e-30) {
+        mode = 1;
+        finish(ctl, a, POISSON_STAGNATED, a.it + 1, sn, 1, 1);
+    }
+    const double omega = (mode == 0) ? ctl->dot[8 + 4 * par + 1] / tt : 0.0;
+    int i, j, kb, ke;
+    const bool act = column(g, a.zchunk, i, j, kb, ke);
+    double acc[2] = {0.0, 0.0};
+    if (act) {
+        long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+        for (int k = kb; k < ke; k++, n += g.sz) {
+            if (mode == 1) {
+                x[n] += alpha * __ldg(p + n);
+            } else {
+                const double sv = __ldg(s + n);
+                x[n] += alpha * __ldg(p + n) + omega * sv;
+                const double rv = sv - omega * __ldg(t + n);
+                r[n] = rv;
+                acc[0] += rv * rv;
+                acc[1] += __ldg(rhat + n) * rv;
+            }
+        }
+    }
+    if (mode == 0) block_reduce_finish<2, false>(acc, rb, &ctl->dot[2 * (par ^ 1)]);
+}
+
+
+// =======================================================================================
+// Host launchers
+// =======================================================================================
+dim3 LaunchCtx::grid() const {
+    const int nzi = g.k1 - g.k0;
+    return dim3((g.nx + TX - 1) / TX, (g.ny + TY - 1) / TY, (nzi + zchunk - 1) / zchunk);
+}
+static inline dim3 blk() { return dim3(TX, TY); }
+static inline KArgs with_chunk(const LaunchCtx& L, KArgs a) {
+    a.zchunk = L.zchunk;
+    return a;
+}
+
+void launch_neumann_fill(const LaunchCtx& L, double* x, int seq, int honour_skip, bool use_ctl) {
+    const int nb = (int)((L.g.ncell + 255) / 256);
+    CFDB_LAUNCH(KK_NEUMANN, L.st,
+                k_neumann_fill<<<nb, 256, 0, L.st>>>(L.g, x, use_ctl ? L.ctl : nullptr, seq, honour_skip));
+}
+void launch_jacobi(const LaunchCtx& L, const KArgs& a0, const double* xin, double* xout, const double* rhs) {
+    const KArgs a = with_chunk(L, a0);
+    if (L.g.dim3) CFDB_LAUNCH(KK_JACOBI, L.st, k_jacobi<true><<<L.grid(), blk(), 0, L.st>>>(L.g, xin, xout, rhs, L.ctl, L.rb, a));
+    else CFDB_LAUNCH(KK_JACOBI, L.st, k_jacobi<false><<<L.grid(), blk(), 0, L.st>>>(L.g, xin, xout, rhs, L.ctl, L.rb, a));
+}
+void launch_redblack(const LaunchCtx& L, const KArgs& a0, double* x, const double* rhs, int colour, int decide) {
+    const KArgs a = with_chunk(L, a0);
+    if (L.g.dim3) CFDB_LAUNCH(KK_REDBLACK, L.st, k_redblack<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, a, colour, decide));
+    else CFDB_LAUNCH(KK_REDBLACK, L.st, k_redblack<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, a, colour, decide));
+}
+void launch_linf_residual(const LaunchCtx& L, const KArgs& a0, const double* x, const double* rhs, int slot) {
+    const KArgs a = with_chunk(L, a0);
+    if (L.g.dim3) CFDB_LAUNCH(KK_LINF, L.st, k_linf_residual<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, L.rb, a, slot));
+    else CFDB_LAUNCH(KK_LINF, L.st, k_linf_residual<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, L.rb, a, slot));
+}
+void launch_stationary_final(const LaunchCtx& L, const KArgs& a) {
+    CFDB_LAUNCH(KK_STAT_FINAL, L.st, k_stationary_final<<<1, 32, 0, L.st>>>(L.ctl, a));
+}
+void launch_krylov_init(const LaunchCtx& L, const KArgs& a0, const double* x, const double* rhs, double* r,
+                        double* p0, double* rhat, int precond) {
+    const KArgs a = with_chunk(L, a0);
+    if (L.g.dim3) CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, k_krylov_init<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, r, p0, rhat, L.ctl, L.rb, a, precond));
+    else CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, k_krylov_init<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, r, p0, rhat, L.ctl, L.rb, a, precond));
+}
+void launch_cg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const double* pold, double* pnew,
+                   double* Ap, int precond, int decide_only) {
+    const KArgs a = with_chunk(L, a0);
+    const dim3 gr = decide_only ? dim3(1, 1, 1) : L.grid();
+    if (L.g.dim3) CFDB_LAUNCH(KK_CG_DIR, L.st, k_cg_dir<true><<<gr, blk(), 0, L.st>>>(L.g, r, pold, pnew, Ap, L.ctl, L.rb, a, precond, decide_only));
+    else CFDB_LAUNCH(KK_CG_DIR, L.st, k_cg_dir<false><<<gr, blk(), 0, L.st>>>(L.g, r, pold, pnew, Ap, L.ctl, L.rb, a, precond, decide_only));
+}
+void launch_cg_update(const LaunchCtx& L, const KArgs& a0, double* x, double* r, const double* p,
+                      const double* Ap, int precond) {
+    const KArgs a = with_chunk(L, a0);
+    if (L.g.dim3) CFDB_LAUNCH(KK_CG_UPDATE, L.st, k_cg_update<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, Ap, L.ctl, L.rb, a, precond));
+    else CFDB_LAUNCH(KK_CG_UPDATE, L.st, k_cg_update<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, Ap, L.ctl, L.rb, a, precond));
+}
+void launch_bicg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const double* pold,
+                     const double* vold, const double* rhat, double* pnew, double* vnew, int first,
+                     int decide_only) {
+    (void)first;
+    const KArgs a = with_chunk(L, a0);
+    const dim3 gr = decide_only ? dim3(1, 1, 1) : L.grid();
+    if (L.g.dim3) CFDB_LAUNCH(KK_BICG_DIR, L.st, k_bicg_dir<true><<<gr, blk(), 0, L.st>>>(L.g, r, pold, vold, rhat, pnew, vnew, L.ctl, L.rb, a, decide_only));
+    else CFDB_LAUNCH(KK_BICG_DIR, L.st, k_bicg_dir<false><<<gr, blk(), 0, L.st>>>(L.g, r, pold, vold, rhat, pnew, vnew, L.ctl, L.rb, a, decide_only));
+}
+void launch_bicg_s(const LaunchCtx& L, const KArgs& a0, const double* r, const double* v, double* s, double* t) {
+    const KArgs a = with_chunk(L, a0);
+    if (L.g.dim3) CFDB_LAUNCH(KK_BICG_S, L.st, k_bicg_s<true><<<L.grid(), blk(), 0, L.st>>>(L.g, r, v, s, t, L.ctl, L.rb, a));
+    else CFDB_LAUNCH(KK_BICG_S, L.st, k_bicg_s<false><<<L.grid(), blk(), 0, L.st>>>(L.g, r, v, s, t, L.ctl, L.rb, a));
+}
+void launch_bicg_update(const LaunchCtx& L, const KArgs& a0, double* x, double* r, const double* p,
+                        const double* s, const double* t, const double* rhat) {
+    const KArgs a = with_chunk(L, a0);
+    if (L.g.dim3) CFDB_LAUNCH(KK_BICG_UPDATE, L.st, k_bicg_update<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, s, t, rhat, L.ctl, L.rb, a));
+    else CFDB_LAUNCH(KK_BICG_UPDATE, L.st, k_bicg_update<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, s, t, rhat, L.ctl, L.rb, a));
+}
+
+}  // namespace cfdb

@@ -1,0 +1,247 @@
+// session.cu -- session lifecycle, host<->device movement, NCCL plumbing, globals.
+#include "session.h"
+
+#include <dlfcn.h>
+#include <limits.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+namespace cfdb {
+
+unsigned long long g_launches = 0;
+thread_local Profiler* t_prof = nullptr;
+static thread_local char t_err[512] = "";
+
+const char* const kKernelNames[KK_COUNT] = {
+    "neumann_fill", "jacobi_sweep", "redblack_half_sweep", "linf_residual", "stationary_final",
+    "krylov_init", "cg_dir_matvec", "cg_update", "bicg_dir_matvec", "bicg_s_matvec", "bicg_update",
+    "predictor", "divergence_rhs", "corrector", "thermal_bc", "periodic_bc", "rk_stage",
+    "field_stats", "synth_init", "copy", "euler"};
+// Algorithmic bytes per interior cell per launch.
+const double kKernelBytesPerCell[KK_COUNT] = {0, 24, 16, 16, 0, 32, 32, 48, 48, 32, 56,
+                                              48, 32, 56, 0, 0, 136, 40, 0, 16, 0};
+
+// The reference keeps a thread-local error string (cfd/core/cfd_status.h:31-43).  When its core
+// library is loaded in the process we forward to it; otherwise we keep our own.
+extern "C" void cfd_set_error(cfd_status_t, const char*) __attribute__((weak));
+
+void set_error(cfd_status_t st, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_err, sizeof(t_err), fmt, ap);
+    va_end(ap);
+    if (cfd_set_error) cfd_set_error(st, t_err);
+}
+const char* last_error() { return t_err; }
+
+void Profiler::begin(cudaStream_t st) {
+    if (!e0) {
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+    }
+    cudaEventRecord(e0, st);
+}
+void Profiler::end(cudaStream_t st, int kind) {
+    launches[kind]++;
+    if (!on) return;
+    cudaEventRecord(e1, st);
+    cudaEventSynchronize(e1);
+    float ms_ = 0.f;
+    cudaEventElapsedTime(&ms_, e0, e1);
+    ms[kind] += ms_;
+}
+
+cfd_status_t dalloc(cfd_b200_session* s, double** p) {
+    if (*p) return CFD_SUCCESS;
+    cudaError_t e = cudaMalloc((void**)p, s->N * sizeof(double));
+    if (e != cudaSuccess) {
+        *p = nullptr;
+        cudaGetLastError();
+        set_error(CFD_ERROR_NOMEM, "cudaMalloc of %zu bytes failed: %s", s->N * sizeof(double),
+                  cudaGetErrorString(e));
+        return CFD_ERROR_NOMEM;
+    }
+    s->bytes_allocated += s->N * sizeof(double);
+    CFDB_CUDA_OK(cudaMemsetAsync(*p, 0, s->N * sizeof(double), s->st));
+    return CFD_SUCCESS;
+}
+
+static void fill_geom(cfd_b200_session* s) {
+    const cfd_b200_session_desc_t& d = s->desc;
+    Geom& g = s->g;
+    memset(&g, 0, sizeof(g));
+    g.nx = (int)d.nx;
+    g.ny = (int)d.ny;
+    g.nz = (int)d.nz;
+    g.dim3 = d.nz > 1;
+    g.sy = (long long)d.nx;
+    g.sz = g.dim3 ? (long long)d.nx * d.ny : 0;
+    g.k0 = g.dim3 ? 1 : 0;
+    g.k1 = g.dim3 ? g.nz - 1 : 1;
+    g.inv_2dx = 1.0 / (2.0 * d.dx);
+    g.inv_2dy = 1.0 / (2.0 * d.dy);
+    g.inv_dx2 = 1.0 / (d.dx * d.dx);
+    g.inv_dy2 = 1.0 / (d.dy * d.dy);
+    g.inv_2dz = (g.dim3 && d.dz > 0.0) ? 1.0 / (2.0 * d.dz) : 0.0;
+    g.inv_dz2 = (g.dim3 && d.dz > 0.0) ? 1.0 / (d.dz * d.dz) : 0.0;
+    g.factor = 2.0 * (g.inv_dx2 + g.inv_dy2 + g.inv_dz2);
+    g.inv_factor = 1.0 / g.factor;
+    for (int a = 0; a < 3; a++) g.glo[a] = g.ghi[a] = 1;
+    s->dec_axis = g.dim3 ? 2 : 1;
+    if (d.nranks > 1) {
+        g.glo[s->dec_axis] = (d.rank == 0);
+        g.ghi[s->dec_axis] = (d.rank == d.nranks - 1);
+        // global index of local layer 0 (uniform slabs: every rank owns n-2 interior layers)
+        if (g.dim3) g.gk0 = (long long)d.rank * (long long)(d.nz - 2);
+        else g.gj0 = (long long)d.rank * (long long)(d.ny - 2);
+    }
+    g.ncell = (long long)d.nx * d.ny * d.nz;
+}
+
+}  // namespace cfdb
+
+using namespace cfdb;
+
+extern "C" {
+
+const char* cfd_b200_last_error(void) { return cfdb::last_error(); }
+const char* cfd_b200_version(void) { return "cfd_b200 0.1.0 (sm_100a, FP64)"; }
+unsigned long long cfd_b200_kernel_launch_count(void) { return g_launches; }
+
+void* cfd_b200_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+void cfd_b200_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
+    if (!d || d->nx < 3 || d->ny < 3 || d->nz == 0 || d->nz == 2 || d->dx <= 0.0 || d->dy <= 0.0 ||
+        (d->nz > 1 && d->dz <= 0.0) || d->nranks < 1 || d->rank < 0 || d->rank >= d->nranks) {
+        set_error(CFD_ERROR_INVALID, "cfd_b200_session_create: invalid descriptor");
+        return nullptr;
+    }
+    if (d->nx > INT_MAX / 2 || d->ny > INT_MAX / 2 || d->nz > INT_MAX / 2) {
+        set_error(CFD_ERROR_LIMIT_EXCEEDED, "cfd_b200_session_create: extent too large");
+        return nullptr;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        set_error(CFD_ERROR_UNSUPPORTED, "no CUDA device available (libcfd_b200 has no CPU fallback)");
+        return nullptr;
+    }
+    cfd_b200_session* s = new cfd_b200_session();
+    s->desc = *d;
+    if (d->device >= 0) {
+        if (cudaSetDevice(d->device) != cudaSuccess) {
+            set_error(CFD_ERROR, "cudaSetDevice(%d) failed", d->device);
+            delete s;
+            return nullptr;
+        }
+    }
+    cudaGetDevice(&s->dev);
+    fill_geom(s);
+    s->N = (size_t)s->g.ncell;
+    bool ok = cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) == cudaSuccess;
+    // z chunking: enough blocks for ~20 waves of 148 SMs x 8 resident blocks
+    {
+        const long long tiles = (long long)((s->g.nx + 31) / 32) * ((s->g.ny + 7) / 8);
+        const int nzi = s->g.k1 - s->g.k0;
+        long long want = (148LL * 8 * 20 + tiles - 1) / tiles;
+        if (want < 1) want = 1;
+        if (want > nzi) want = nzi;
+        s->zchunk = (int)((nzi + want - 1) / want);
+        if (s->zchunk < 1) s->zchunk = 1;
+        const long long nchunks = (nzi + s->zchunk - 1) / s->zchunk;
+        s->rb_blocks = (size_t)(tiles * nchunks);
+        if (s->rb_blocks < 148 * 16) s->rb_blocks = 148 * 16;
+    }
+    ok = ok && cudaMalloc((void**)&s->ctl, sizeof(Ctl)) == cudaSuccess;
+    ok = ok && cudaMemset(s->ctl, 0, sizeof(Ctl)) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&s->rb.partials, s->rb_blocks * 4 * sizeof(double)) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&s->rb.ticket, sizeof(unsigned)) == cudaSuccess;
+    ok = ok && cudaMemset(s->rb.ticket, 0, sizeof(unsigned)) == cudaSuccess;
+    ok = ok && cudaHostAlloc((void**)&s->h_ctl, 2 * sizeof(Ctl), cudaHostAllocDefault) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&s->ev[0], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&s->ev[1], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&s->su_tab, d->ny * sizeof(double)) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&s->sv_tab, d->nx * sizeof(double)) == cudaSuccess;
+    if (ok) {
+        double** prim[] = {&s->u, &s->v, &s->w, &s->p, &s->T};
+        for (auto pp : prim) ok = ok && dalloc(s, pp) == CFD_SUCCESS;
+    }
+    if (!ok) {
+        if (!t_err[0]) set_error(CFD_ERROR_NOMEM, "cfd_b200_session_create: device allocation failed");
+        cudaGetLastError();
+        cfd_b200_session_destroy(s);
+        return nullptr;
+    }
+    s->xs.resize(d->nx);
+    s->ys.resize(d->ny);
+    for (size_t i = 0; i < d->nx; i++) s->xs[i] = d->xmin + ((double)i * d->dx);
+    for (size_t j = 0; j < d->ny; j++) s->ys[j] = d->ymin + ((double)j * d->dy);
+    cudaStreamSynchronize(s->st);
+    return s;
+}
+
+void cfd_b200_session_destroy(cfd_b200_session_t* s) {
+    if (!s) return;
+    cudaSetDevice(s->dev);
+    if (s->st) cudaStreamSynchronize(s->st);
+    double* all[] = {s->u, s->v, s->w, s->p, s->T, s->rho, s->us, s->vs, s->ws, s->pn, s->rhs, s->Tn, s->xt,
+                     s->su_tab, s->sv_tab};
+    for (double* q : all) if (q) cudaFree(q);
+    for (double* q : s->kv) if (q) cudaFree(q);
+    for (double* q : s->rk) if (q) cudaFree(q);
+    if (s->ctl) cudaFree(s->ctl);
+    if (s->rb.partials) cudaFree(s->rb.partials);
+    if (s->rb.ticket) cudaFree(s->rb.ticket);
+    if (s->h_ctl) cudaFreeHost(s->h_ctl);
+    for (auto& e : s->ev) if (e) cudaEventDestroy(e);
+    if (s->prof.e0) cudaEventDestroy(s->prof.e0);
+    if (s->prof.e1) cudaEventDestroy(s->prof.e1);
+    if (s->nccl.comm && s->nccl.CommDestroy) s->nccl.CommDestroy(s->nccl.comm);
+    if (s->st) cudaStreamDestroy(s->st);
+    if (t_prof == &s->prof) t_prof = nullptr;
+    delete s;
+}
+
+void* cfd_b200_session_stream(cfd_b200_session_t* s) { return s ? (void*)s->st : nullptr; }
+cfd_status_t cfd_b200_session_sync(cfd_b200_session_t* s) {
+    if (!s) return CFD_ERROR_INVALID;
+    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
+    return CFD_SUCCESS;
+}
+poisson_solver_stats_t cfd_b200_session_last_poisson_stats(const cfd_b200_session_t* s) {
+    return s->last_ps;
+}
+
+void cfd_b200_session_profile(cfd_b200_session_t* s, int enable) { s->prof.on = enable != 0; }
+void cfd_b200_session_reset_kernel_stats(cfd_b200_session_t* s) {
+    for (int k = 0; k < KK_COUNT; k++) {
+        s->prof.launches[k] = 0;
+        s->prof.ms[k] = 0.0;
+    }
+}
+int cfd_b200_session_kernel_stats(const cfd_b200_session_t* s, cfd_b200_kernel_stat_t* out, int max) {
+    int n = 0;
+    for (int k = 0; k < KK_COUNT && n < max; k++) {
+        if (!s->prof.launches[k]) continue;
+        out[n].name = kKernelNames[k];
+        out[n].launches = s->prof.launches[k];
+        out[n].total_ms = s->prof.ms[k];
+        out[n].bytes_per_cell = kKernelBytesPerCell[k];
+        n++;
+    }
+    return n;
+}
+
+}  // extern "C"

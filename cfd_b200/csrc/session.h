@@ -1,0 +1,87 @@
+// session.h -- device-resident state of one slab on one GPU and the host-side drivers.
+#pragma once
+#include "kernels.h"
+
+#include <vector>
+
+namespace cfdb {
+
+// Minimal NCCL surface, bound with dlopen at run time (no link-time dependency).  The enum
+// values are those of nccl.h 2.27/2.28: ncclDouble = 8, ncclSum = 0, ncclMax = 2.
+struct NcclId {
+    char internal[128];
+};
+struct Nccl {
+    void* lib = nullptr;
+    void* comm = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, /*ncclUniqueId by value*/ NcclId, int) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+};
+
+enum FieldMask { FM_U = 1, FM_V = 2, FM_W = 4, FM_P = 8, FM_RHO = 16, FM_T = 32, FM_ALL = 63 };
+
+}  // namespace cfdb
+
+struct cfd_b200_session {
+    cfd_b200_session_desc_t desc;
+    cfdb::Geom g;
+    int dev = 0;
+    cudaStream_t st = nullptr;
+    size_t N = 0;             // cells of the local slab
+    int dec_axis = 2;         // decomposed axis: 2 = z (3-D), 1 = y (2-D)
+    // primary fields
+    double *u = nullptr, *v = nullptr, *w = nullptr, *p = nullptr, *T = nullptr, *rho = nullptr;
+    // projection work arrays
+    double *us = nullptr, *vs = nullptr, *ws = nullptr, *pn = nullptr, *rhs = nullptr, *Tn = nullptr;
+    double* xt = nullptr;     // Jacobi ping-pong buffer
+    double* kv[8] = {};       // Krylov work vectors
+    double* rk[12] = {};      // RK: B[4], C[4], ACC[4]
+    double *su_tab = nullptr, *sv_tab = nullptr;  // device source tables [ny], [nx]
+    std::vector<double> xs, ys;                   // host coordinates of local i, j
+    double tab_au = 0.0, tab_av = 0.0;            // amplitudes the tables were built for
+    bool tab_valid = false;
+    double rho0 = 1.0;        // field->rho[0] (solver_projection.c:195)
+    cfdb::Ctl* ctl = nullptr;     // device
+    cfdb::Ctl* h_ctl = nullptr;   // pinned host mirror, 2 entries
+    cudaEvent_t ev[2] = {};
+    cfdb::RedBuf rb = {};
+    size_t rb_blocks = 0;
+    int zchunk = 1;
+    cfdb::Profiler prof;
+    cfdb::Nccl nccl;
+    poisson_solver_stats_t last_ps = {};
+    size_t bytes_allocated = 0;
+    int kernels_at_create = 0;
+
+    cfdb::LaunchCtx L() const {
+        cfdb::LaunchCtx l;
+        l.g = g;
+        l.st = st;
+        l.ctl = ctl;
+        l.rb = rb;
+        l.zchunk = zchunk;
+        return l;
+    }
+};
+
+namespace cfdb {
+cfd_status_t dalloc(cfd_b200_session* s, double** p);           // zero-filled N doubles
+cfd_status_t session_upload(cfd_b200_session* s, const flow_field* f, int mask);
+cfd_status_t session_download(cfd_b200_session* s, flow_field* f, int mask);
+cfd_status_t session_set_coords(cfd_b200_session* s, const double* x, const double* y);
+cfd_status_t halo_exchange(cfd_b200_session* s, double* const* fields, int nf, bool periodic_ring);
+cfd_status_t allreduce(cfd_b200_session* s, double* dev, int n, bool is_max);
+cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double** x,
+                           double** xtmp, const double* rhs, poisson_solver_stats_t* st);
+cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
+                            const cfd_b200_poisson_config_t* pc, int nsteps, ns_solver_stats_t* stats);
+cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* prm, int nsteps,
+                    ns_solver_stats_t* stats);
+cfd_status_t validate_common(const flow_field* f, const grid* g, const ns_solver_params_t* prm);
+}  // namespace cfdb

@@ -1,0 +1,211 @@
+// session_io.cu -- host<->device field movement, coordinate tables, halo exchange and
+// all-reduce over NCCL (one process per GPU; the communicator is bootstrapped by the caller,
+// e.g. through torch.distributed, and handed to us as a 128-byte ncclUniqueId).
+#include "session.h"
+
+#include <dlfcn.h>
+#include <math.h>
+#include <string.h>
+
+namespace cfdb {
+
+static double* const* field_ptrs(cfd_b200_session* s, double* out[6]) {
+    out[0] = s->u; out[1] = s->v; out[2] = s->w; out[3] = s->p; out[4] = s->rho; out[5] = s->T;
+    return out;
+}
+
+cfd_status_t session_upload(cfd_b200_session* s, const flow_field* f, int mask) {
+    if (!s || !f) return CFD_ERROR_INVALID;
+    if (f->nx != s->desc.nx || f->ny != s->desc.ny || f->nz != s->desc.nz) {
+        set_error(CFD_ERROR_INVALID, "upload: field is %zux%zux%zu but the session is %zux%zux%zu", f->nx,
+                  f->ny, f->nz, s->desc.nx, s->desc.ny, s->desc.nz);
+        return CFD_ERROR_INVALID;
+    }
+    CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    if ((mask & FM_RHO) && !s->rho) {
+        cfd_status_t rc = dalloc(s, &s->rho);
+        if (rc != CFD_SUCCESS) return rc;
+    }
+    double* dv[6];
+    field_ptrs(s, dv);
+    const double* hv[6] = {f->u, f->v, f->w, f->p, f->rho, f->T};
+    for (int q = 0; q < 6; q++) {
+        if (!(mask & (1 << q))) continue;
+        if (!hv[q]) return CFD_ERROR_INVALID;
+        CFDB_CUDA_OK(cudaMemcpyAsync(dv[q], hv[q], s->N * sizeof(double), cudaMemcpyHostToDevice, s->st));
+    }
+    if (f->rho) s->rho0 = f->rho[0];
+    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
+    return CFD_SUCCESS;
+}
+
+cfd_status_t session_download(cfd_b200_session* s, flow_field* f, int mask) {
+    if (!s || !f) return CFD_ERROR_INVALID;
+    if (f->nx != s->desc.nx || f->ny != s->desc.ny || f->nz != s->desc.nz) return CFD_ERROR_INVALID;
+    CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    double* dv[6];
+    field_ptrs(s, dv);
+    double* hv[6] = {f->u, f->v, f->w, f->p, f->rho, f->T};
+    for (int q = 0; q < 6; q++) {
+        if (!(mask & (1 << q)) || !dv[q] || !hv[q]) continue;
+        CFDB_CUDA_OK(cudaMemcpyAsync(hv[q], dv[q], s->N * sizeof(double), cudaMemcpyDeviceToHost, s->st));
+    }
+    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
+    return CFD_SUCCESS;
+}
+
+cfd_status_t session_set_coords(cfd_b200_session* s, const double* x, const double* y) {
+    if (x) s->xs.assign(x, x + s->desc.nx);
+    if (y) s->ys.assign(y, y + s->desc.ny);
+    s->tab_valid = false;
+    return CFD_SUCCESS;
+}
+
+// ---- NCCL plumbing -------------------------------------------------------------------
+static cfd_status_t load_nccl(Nccl& n, const char* path) {
+    if (n.lib) return CFD_SUCCESS;
+    n.lib = dlopen(path && path[0] ? path : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!n.lib) {
+        set_error(CFD_ERROR_UNSUPPORTED, "dlopen(%s) failed: %s", path ? path : "libnccl.so.2", dlerror());
+        return CFD_ERROR_UNSUPPORTED;
+    }
+#define SYM(field, name)                                                   \
+    *(void**)(&n.field) = dlsym(n.lib, name);                              \
+    if (!n.field) {                                                        \
+        set_error(CFD_ERROR_UNSUPPORTED, "NCCL symbol %s not found", name); \
+        return CFD_ERROR_UNSUPPORTED;                                      \
+    }
+    SYM(GetUniqueId, "ncclGetUniqueId")
+    SYM(CommInitRank, "ncclCommInitRank")
+    SYM(CommDestroy, "ncclCommDestroy")
+    SYM(AllReduce, "ncclAllReduce")
+    SYM(Send, "ncclSend")
+    SYM(Recv, "ncclRecv")
+    SYM(GroupStart, "ncclGroupStart")
+    SYM(GroupEnd, "ncclGroupEnd")
+#undef SYM
+    return CFD_SUCCESS;
+}
+
+// One-cell halo exchange along the decomposed axis for nf fields: send my first/last owned
+// plane (row in 2-D), receive into my halo plane.  periodic_ring also links rank 0 <-> last
+// (RK steppers: periodic wrap across the decomposed axis).  Stream-ordered, no host sync.
+cfd_status_t halo_exchange(cfd_b200_session* s, double* const* fields, int nf, bool periodic_ring) {
+    const int R = s->desc.nranks, r = s->desc.rank;
+    if (R <= 1) return CFD_SUCCESS;
+    if (!s->nccl.comm) {
+        set_error(CFD_ERROR, "multi-rank session without a communicator (call cfd_b200_session_init_comm)");
+        return CFD_ERROR;
+    }
+    const Geom& g = s->g;
+    const size_t cnt = g.dim3 ? (size_t)g.nx * g.ny : (size_t)g.nx;
+    const long long n_ax = g.dim3 ? g.nz : g.ny;
+    const long long st = g.dim3 ? (long long)g.nx * g.ny : g.nx;
+    int lo = r - 1, hi = r + 1;
+    if (periodic_ring) {
+        lo = (r + R - 1) % R;
+        hi = (r + 1) % R;
+    }
+    const Nccl& n = s->nccl;
+    n.GroupStart();
+    for (int q = 0; q < nf; q++) {
+        double* f = fields[q];
+        // sends in the order (lo, hi), receives in the order (hi, lo): with two ranks in a
+        // periodic ring both neighbours are the same peer and NCCL matches messages in order.
+        const bool has_lo = lo >= 0 && lo < R, has_hi = hi >= 0 && hi < R;
+        if (has_lo) n.Send(f + 1 * st, cnt, 8, lo, n.comm, s->st);
+        if (has_hi) n.Send(f + (n_ax - 2) * st, cnt, 8, hi, n.comm, s->st);
+        if (has_hi) n.Recv(f + (n_ax - 1) * st, cnt, 8, hi, n.comm, s->st);
+        if (has_lo) n.Recv(f + 0 * st, cnt, 8, lo, n.comm, s->st);
+    }
+    if (n.GroupEnd() != 0) {
+        set_error(CFD_ERROR, "NCCL halo exchange failed");
+        return CFD_ERROR;
+    }
+    return CFD_SUCCESS;
+}
+
+cfd_status_t allreduce(cfd_b200_session* s, double* dev, int cnt, bool is_max) {
+    if (s->desc.nranks <= 1) return CFD_SUCCESS;
+    if (!s->nccl.comm) return CFD_ERROR;
+    if (s->nccl.AllReduce(dev, dev, (size_t)cnt, 8, is_max ? 2 : 0, s->nccl.comm, s->st) != 0) {
+        set_error(CFD_ERROR, "NCCL all-reduce failed");
+        return CFD_ERROR;
+    }
+    return CFD_SUCCESS;
+}
+
+}  // namespace cfdb
+
+using namespace cfdb;
+
+extern "C" {
+
+cfd_status_t cfd_b200_nccl_unique_id(const char* nccl_lib, char out[128]) {
+    Nccl n;
+    cfd_status_t rc = load_nccl(n, nccl_lib);
+    if (rc != CFD_SUCCESS) return rc;
+    NcclId id;
+    if (n.GetUniqueId(&id) != 0) return CFD_ERROR;
+    memcpy(out, id.internal, 128);
+    return CFD_SUCCESS;
+}
+
+cfd_status_t cfd_b200_session_init_comm(cfd_b200_session_t* s, const char* nccl_lib, const char id[128]) {
+    if (!s || !id) return CFD_ERROR_INVALID;
+    cfd_status_t rc = load_nccl(s->nccl, nccl_lib);
+    if (rc != CFD_SUCCESS) return rc;
+    CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    NcclId nid;
+    memcpy(nid.internal, id, 128);
+    if (s->nccl.CommInitRank(&s->nccl.comm, s->desc.nranks, nid, s->desc.rank) != 0) {
+        set_error(CFD_ERROR, "ncclCommInitRank(rank %d of %d) failed", s->desc.rank, s->desc.nranks);
+        return CFD_ERROR;
+    }
+    return CFD_SUCCESS;
+}
+
+cfd_status_t cfd_b200_session_upload(cfd_b200_session_t* s, const flow_field* host) {
+    return session_upload(s, host, FM_ALL);
+}
+cfd_status_t cfd_b200_session_download(cfd_b200_session_t* s, flow_field* host) {
+    return session_download(s, host, FM_ALL);
+}
+cfd_status_t cfd_b200_session_upload_mask(cfd_b200_session_t* s, const flow_field* host, int mask) {
+    return session_upload(s, host, mask);
+}
+cfd_status_t cfd_b200_session_download_mask(cfd_b200_session_t* s, flow_field* host, int mask) {
+    return session_download(s, host, mask);
+}
+
+cfd_status_t cfd_b200_session_init_synthetic(cfd_b200_session_t* s, uint64_t seed, size_t global_k0,
+                                             size_t global_nz) {
+    if (!s) return CFD_ERROR_INVALID;
+    CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    t_prof = &s->prof;
+    launch_synth_init(s->L(), seed, (long long)global_k0, (long long)global_nz, s->u, s->v, s->w, s->p,
+                      s->T, s->rho);
+    s->rho0 = 1.0;
+    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
+    return CFD_SUCCESS;
+}
+
+cfd_status_t cfd_b200_session_upload_poisson(cfd_b200_session_t* s, const double* x, const double* rhs) {
+    if (!s) return CFD_ERROR_INVALID;
+    CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    cfd_status_t rc = dalloc(s, &s->rhs);
+    if (rc != CFD_SUCCESS) return rc;
+    if (x) CFDB_CUDA_OK(cudaMemcpyAsync(s->p, x, s->N * sizeof(double), cudaMemcpyHostToDevice, s->st));
+    if (rhs) CFDB_CUDA_OK(cudaMemcpyAsync(s->rhs, rhs, s->N * sizeof(double), cudaMemcpyHostToDevice, s->st));
+    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
+    return CFD_SUCCESS;
+}
+cfd_status_t cfd_b200_session_download_poisson(cfd_b200_session_t* s, double* x) {
+    if (!s || !x) return CFD_ERROR_INVALID;
+    CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    CFDB_CUDA_OK(cudaMemcpyAsync(x, s->p, s->N * sizeof(double), cudaMemcpyDeviceToHost, s->st));
+    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
+    return CFD_SUCCESS;
+}
+
+}  // extern "C"

@@ -414,19 +414,25 @@ typedef struct {
 CFD_B200_API cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* desc);
 CFD_B200_API void cfd_b200_session_destroy(cfd_b200_session_t* s);
 
-/* Attach an initialised NCCL communicator (ncclComm_t passed as void*) for halo exchange and
- * Krylov all-reduces. nccl_lib is the path of the libnccl.so.2 that created it. */
-CFD_B200_API cfd_status_t cfd_b200_session_set_comm(cfd_b200_session_t* s, void* nccl_comm,
-                                                    const char* nccl_lib);
+/* Multi-GPU: one process per GPU.  Rank 0 obtains a 128-byte ncclUniqueId, the caller
+ * broadcasts it (e.g. torch.distributed) and every rank joins.  nccl_lib is the path of the
+ * libnccl.so.2 to dlopen (NULL = default search).  Used for one-cell halo exchange
+ * (ncclSend/ncclRecv) and the Krylov / residual all-reduces; all stream-ordered. */
+CFD_B200_API cfd_status_t cfd_b200_nccl_unique_id(const char* nccl_lib, char out[128]);
+CFD_B200_API cfd_status_t cfd_b200_session_init_comm(cfd_b200_session_t* s, const char* nccl_lib,
+                                                     const char id[128]);
 
 /* Host<->device movement of the local slab (host arrays sized nx*ny*nz, reference layout).
  * rho: only rho[0] is used by the projection; RK uses the full field. */
 CFD_B200_API cfd_status_t cfd_b200_session_upload(cfd_b200_session_t* s, const flow_field* host);
 CFD_B200_API cfd_status_t cfd_b200_session_download(cfd_b200_session_t* s, flow_field* host);
+/* Same with a field mask: bit0 u, bit1 v, bit2 w, bit3 p, bit4 rho, bit5 T. */
+CFD_B200_API cfd_status_t cfd_b200_session_upload_mask(cfd_b200_session_t* s, const flow_field* host, int mask);
+CFD_B200_API cfd_status_t cfd_b200_session_download_mask(cfd_b200_session_t* s, flow_field* host, int mask);
 /* Fill the device fields with the deterministic synthetic state of SURVEY 8(d) config C5
  * (sinusoidal velocity + splitmix64 perturbation); no host traffic. */
 CFD_B200_API cfd_status_t cfd_b200_session_init_synthetic(cfd_b200_session_t* s, uint64_t seed,
-                                                          size_t global_k0);
+                                                          size_t global_k0, size_t global_nz);
 
 /* Advance nsteps projection steps (solver_projection.c:111-290) fully on the device. */
 CFD_B200_API cfd_status_t cfd_b200_session_projection(cfd_b200_session_t* s,

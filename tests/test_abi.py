@@ -1,0 +1,82 @@
+"""The C-ABI library loads, exports every symbol include/cfd_b200.h declares, and its view of
+the boundary types agrees with the compiled reference and with the ctypes mirror.  No compute."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from cfd_b200 import abi, lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _table(fn):
+    buf = (C.c_size_t * 256)()
+    n = fn(buf, 256)
+    return list(buf[:n])
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    L = lib.load()
+    for name in lib.DECLARED_SYMBOLS:
+        assert hasattr(L, name), "libcfd_b200.so does not export %s" % name
+    assert b"sm_100a" in L.cfd_b200_version()
+
+
+def test_header_and_binding_list_agree():
+    text = open(os.path.join(ROOT, "include", "cfd_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)  # drop comments
+    text = text[text.index("Part 2") if "Part 2" in text else 0:]
+    declared = set(re.findall(r"CFD_B200_API[^;(]*?\b([A-Za-z_][A-Za-z0-9_]*)\s*\(", text))
+    declared.discard("__attribute__")  # the macro definition itself
+    assert declared == set(lib.DECLARED_SYMBOLS), declared ^ set(lib.DECLARED_SYMBOLS)
+
+
+def test_abi_matches_compiled_reference(ref):
+    ours = _table(lib.load().cfd_b200_abi_table)
+    theirs = _table(ref.lib.ref_abi_table)
+    assert ours == theirs
+
+
+def test_ctypes_mirror_sizes():
+    t = _table(lib.load().cfd_b200_abi_table)
+    assert t[0] == C.sizeof(abi.FlowField)
+    sizes = {C.sizeof(abi.Grid), C.sizeof(abi.NSSolverParams), C.sizeof(abi.ThermalBC),
+             C.sizeof(abi.DirichletValues), C.sizeof(abi.NSSolverStats), C.sizeof(abi.NSSolver),
+             C.sizeof(abi.GpuConfig), C.sizeof(abi.GpuSolverStats), C.sizeof(abi.PoissonParams),
+             C.sizeof(abi.PoissonStats), C.sizeof(abi.PoissonSolver)}
+    assert sizes <= set(t)
+    assert abi.NSSolverParams.thermal_bc.offset in t and abi.NSSolverParams.alpha.offset in t
+    assert abi.PoissonSolver.params.offset in t and abi.PoissonSolver.solve.offset in t
+
+
+def test_poisson_config_roundtrip_without_gpu():
+    L = lib.load()
+    d = L.cfd_b200_poisson_config_default()
+    assert d.method == abi.POISSON_METHOD_CG and d.params.max_iterations == 5000
+    assert d.params.tolerance == 1e-6 and d.params.absolute_tolerance == 1e-10
+    cfg = abi.poisson_config("bicgstab", max_iterations=50)
+    assert L.cfd_b200_set_poisson_config(C.byref(cfg)) == 0
+    got = L.cfd_b200_get_poisson_config()
+    assert got.method == abi.POISSON_METHOD_BICGSTAB and got.params.max_iterations == 50
+    bad = abi.poisson_config("cg")
+    bad.method = abi.POISSON_METHOD_MULTIGRID
+    assert L.cfd_b200_set_poisson_config(C.byref(bad)) == abi.CFD_ERROR_UNSUPPORTED
+    L.cfd_b200_set_poisson_config(C.byref(d))
+
+
+def test_fails_loudly_without_cuda():
+    """No CPU fallback: on a box without a GPU every compute entry point refuses."""
+    L = lib.load()
+    if L.gpu_is_available():
+        pytest.skip("a GPU is present")
+    from cfd_b200 import api
+    import cases
+    g, f, p = cases.golden16()
+    p.max_iter = 1
+    assert api.solve_method_gpu("projection", f, g, p) == abi.CFD_ERROR
+    with pytest.raises(lib.CfdB200Error):
+        api.Session(16, 16, 1, 0.1, 0.1)
+    with pytest.raises(lib.CfdB200Error):
+        api.GpuSolver("projection_gpu")

@@ -1,0 +1,180 @@
+"""The oracle (oracle/oracle.c) pinned against (a) the reference's golden L2 norms,
+(b) committed golden vectors generated from the reference, and (c) the compiled reference
+itself when oracle/_ref is present.  CPU only."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import cases
+from cfd_b200 import abi
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+METH = {"jacobi": abi.POISSON_METHOD_JACOBI, "rbsor": abi.POISSON_METHOD_REDBLACK_SOR,
+        "cg": abi.POISSON_METHOD_CG, "pcg": abi.POISSON_METHOD_CG, "bicgstab": abi.POISSON_METHOD_BICGSTAB}
+
+# tests/solvers/navier_stokes/cpu/test_ns_solver_3d.c:343-367, tolerance 1e-12 (:326-328)
+GOLDEN_L2 = {
+    "projection": (6.84647639323831686e-02, 3.42315494726977212e-02, 1.00000039251590289e+00),
+    "rk2": (6.88584742267375205e-02, 3.49775875753182836e-02, 1.00000000000000044e+00),
+    "rk4": (6.88584742267390471e-02, 3.49775875752817156e-02, 1.00000000000000000e+00),
+}
+
+
+def l2(a):
+    a = a.ravel()
+    s = 0.0
+    for v in a:  # same summation order as the reference's compute_l2_norm
+        s += v * v
+    return np.sqrt(s / a.size)
+
+
+def run_oracle(orc, solver, g, f, p, nsteps):
+    """nsteps x solver_step: every step restarts the iteration index at 0 (registry wrappers
+    set max_iter = 1, solver_registry.c:928-929)."""
+    rc = 0
+    for _ in range(nsteps):
+        if solver == "projection":
+            rc, _ = orc.projection(f, g, p, abi.poisson_config("cg"), 1)
+        else:
+            rc = orc.rk(f, g, p, int(solver[2]), 1)
+        if rc != 0:
+            break
+    return rc
+
+
+@pytest.mark.parametrize("solver", ["projection", "rk2", "rk4"])
+def test_reference_golden_l2_norms(orc, solver):
+    g, f, p = cases.golden16()
+    assert run_oracle(orc, solver, g, f, p, 1) == 0
+    gu, gv, gp = GOLDEN_L2[solver]
+    assert abs(l2(f.u) - gu) < 1e-12 and abs(l2(f.v) - gv) < 1e-12 and abs(l2(f.p) - gp) < 1e-12
+    assert np.max(np.abs(f.w)) == 0.0
+
+
+def _load_step(path):
+    z = np.load(path)
+    nz, ny, nx = z["in_u"].shape
+    return z, nx, ny, nz
+
+
+@pytest.mark.parametrize("tag,case", [
+    ("golden16_projection", lambda: cases.golden16()),
+    ("golden16_rk2", lambda: cases.golden16()),
+    ("golden16_rk4", lambda: cases.golden16()),
+    ("tg3d_rk4", lambda: cases.taylor_green(12, 10, dt=1e-3)),
+    ("tg3d_projection", lambda: cases.taylor_green(12, 10, dt=1e-3)),
+    ("natconv2d_projection", lambda: cases.natural_convection(17, 1, dt=2e-3)),
+    ("source16_projection", lambda: cases.golden16()),
+])
+def test_oracle_matches_golden_vectors_bitwise(orc, tag, case):
+    z, nx, ny, nz = _load_step(os.path.join(GOLD, tag + ".npz"))
+    g, f, p = case()
+    if tag.startswith("source16"):
+        p.source_amplitude_u, p.source_amplitude_v = 0.1, 0.05
+    for k in f.NAMES:
+        np.testing.assert_array_equal(getattr(f, k), z["in_" + k])  # the case builder is the recipe
+    assert run_oracle(orc, str(z["solver"]), g, f, p, int(z["nsteps"])) == 0
+    for k in f.NAMES:
+        np.testing.assert_array_equal(getattr(f, k), z["out_" + k], err_msg="%s field %s" % (tag, k))
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "poisson_*.npz"))))
+def test_oracle_poisson_matches_golden_bitwise(orc, path):
+    z = np.load(path)
+    name = os.path.basename(path).split("_")[1]
+    nz, ny, nx = z["x0"].shape
+    g = abi.HostGrid(nx, ny, nz, 0, 1, 0, 1, 0, 1 if nz > 1 else 0)
+    pp = abi.poisson_params_default()
+    if name == "jacobi":
+        pp.max_iterations = 2000
+    if name == "pcg":
+        pp.preconditioner = abi.POISSON_PRECOND_JACOBI
+    x = abi.aligned_zeros(z["x0"].size).reshape(z["x0"].shape)
+    x[...] = z["x0"]
+    rhs = np.ascontiguousarray(z["rhs"])
+    xt = np.zeros_like(x)
+    dx, dy, dz = g.spacing
+    rc, st = orc.poisson(METH[name], nx, ny, nz, dx, dy, dz, pp, x, rhs, xt)
+    assert rc == int(z["rc"]) and st.iterations == int(z["iterations"]) and st.status == int(z["status"])
+    np.testing.assert_array_equal(x, z["x"])
+    assert st.final_residual == float(z["final_residual"])
+
+
+# ---- live comparison with the compiled reference (skipped where oracle/_ref is absent) ----
+
+@pytest.mark.parametrize("shape", [(9, 9, 1), (20, 13, 1), (10, 9, 8), (3, 3, 3), (5, 4, 1)])
+@pytest.mark.parametrize("solver", ["projection", "rk2", "rk4"])
+def test_oracle_vs_reference_steps(orc, ref, shape, solver):
+    g, f = cases.random_field(*shape, seed=7)
+    p = cases.params(dt=1e-3, amp=(0.1, 0.05))
+    f2 = f.copy()
+    rc_r, _ = ref.run_solver(solver, f, g, p, 3)
+    rc_o = run_oracle(orc, solver, g, f2, p, 3)
+    assert rc_r == rc_o
+    for k in f.NAMES:
+        np.testing.assert_array_equal(getattr(f, k), getattr(f2, k))
+
+
+def test_oracle_vs_reference_solve_multi_step(orc, ref):
+    """solver_solve(max_iter=N): the iteration index enters the source term."""
+    g, f = cases.random_field(14, 11, 1, seed=2)
+    p = cases.params(dt=1e-3, amp=(0.1, 0.05))
+    f2 = f.copy()
+    rc_r, _ = ref.run_solver("projection", f, g, p, 4, use_solve=True)
+    rc_o, _ = orc.projection(f2, g, p, abi.poisson_config("cg"), 4)
+    assert rc_r == rc_o == 0
+    for k in f.NAMES:
+        np.testing.assert_array_equal(getattr(f, k), getattr(f2, k))
+
+
+@pytest.mark.parametrize("shape", [(17, 15, 1), (9, 8, 7), (3, 3, 1), (33, 33, 1)])
+@pytest.mark.parametrize("name", list(METH))
+def test_oracle_vs_reference_poisson(orc, ref, shape, name):
+    nx, ny, nz = shape
+    g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=11)
+    pp = abi.poisson_params_default()
+    if name == "jacobi":
+        pp.max_iterations = 2000
+    if name == "pcg":
+        pp.preconditioner = abi.POISSON_PRECOND_JACOBI
+    x2 = x.copy()
+    dx, dy, dz = g.spacing
+    rc_r, st_r = ref.poisson(METH[name], abi.POISSON_BACKEND_SCALAR, nx, ny, nz, dx, dy, dz, pp, x, rhs,
+                             np.zeros_like(x))
+    rc_o, st_o = orc.poisson(METH[name], nx, ny, nz, dx, dy, dz, pp, x2, rhs, np.zeros_like(x))
+    assert (rc_r, st_r.iterations, st_r.status) == (rc_o, st_o.iterations, st_o.status)
+    assert st_r.final_residual == st_o.final_residual and st_r.initial_residual == st_o.initial_residual
+    np.testing.assert_array_equal(x, x2)
+
+
+def test_oracle_vs_reference_energy_and_thermal_bcs(orc, ref):
+    for nz in (1, 7):
+        g, f, p = cases.natural_convection(13, nz, dt=1e-3)
+        p.thermal_bc.top = abi.BC_TYPE_PERIODIC  # mixed types: exercises corner precedence
+        f2 = f.copy()
+        rc_r, _ = ref.run_solver("projection", f, g, p, 3)
+        rc_o = 0
+        for _ in range(3):
+            rc_o, _ = orc.projection(f2, g, p, abi.poisson_config("cg"), 1)
+        assert rc_r == rc_o == 0
+        for k in f.NAMES:
+            np.testing.assert_array_equal(getattr(f, k), getattr(f2, k))
+
+
+def test_optimal_omega_formula(orc):
+    # linear_solver_internal.h:184-220 on a square grid: omega = 2/(1+sin(pi/(n-1)))
+    n = 33
+    w = orc.lib.orc_optimal_omega(n, n, 1, 1.0 / (n - 1), 1.0 / (n - 1), 0.0)
+    assert abs(w - 2.0 / (1.0 + np.sin(np.pi / (n - 1)))) < 1e-12
+
+
+def test_nonconvergence_policy(orc):
+    g, f, p = cases.cavity(17)
+    pc = abi.poisson_config("jacobi", max_iterations=5)
+    rc, st = orc.projection(f, g, p, pc, 1)
+    assert rc == abi.CFD_ERROR_MAX_ITER and st.status == abi.POISSON_MAX_ITER
+    pc.on_nonconvergence = abi.CFD_B200_NONCONV_CONTINUE
+    rc, _ = orc.projection(f, g, p, pc, 1)
+    assert rc == 0
