@@ -294,13 +294,7 @@ cfd_status_t gpu_solver_step(gpu_solver_context_t* c, const grid* g, const ns_so
         // adopt the real spacing; device fields stay as uploaded
         s->desc.dx = dx; s->desc.dy = dy; s->desc.dz = dz;
         s->desc.xmin = g->xmin; s->desc.ymin = g->ymin;
-        Geom& q = s->g;
-        q.inv_2dx = 1.0 / (2.0 * dx); q.inv_2dy = 1.0 / (2.0 * dy);
-        q.inv_dx2 = 1.0 / (dx * dx);  q.inv_dy2 = 1.0 / (dy * dy);
-        q.inv_2dz = (q.dim3 && dz > 0.0) ? 1.0 / (2.0 * dz) : 0.0;
-        q.inv_dz2 = (q.dim3 && dz > 0.0) ? 1.0 / (dz * dz) : 0.0;
-        q.factor = 2.0 * (q.inv_dx2 + q.inv_dy2 + q.inv_dz2);
-        q.inv_factor = 1.0 / q.factor;
+        set_spacing(s->g, dx, dy, dz);
     }
     session_set_coords(s, g->x, g->y);
     const unsigned long long l0 = g_launches;

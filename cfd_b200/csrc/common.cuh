@@ -21,6 +21,10 @@ struct Geom {
     int k0, k1;              // updated k range [k0,k1): 1..nz-1 in 3-D, 0..1 in 2-D
     int dim3;                // nz > 1
     double inv_2dx, inv_2dy, inv_2dz, inv_dx2, inv_dy2, inv_dz2;
+    // divisors in the reference's own form: it DIVIDES by 2.0*dx, dx*dx (x, y) and multiplies by
+    // the z reciprocals (solver_projection.c:80-84,120-160; linear_solver_jacobi.c:100-108), so
+    // bit-exact parity needs the same operations.
+    double two_dx, two_dy, dx2, dy2;
     double factor, inv_factor;  // 2(1/dx2+1/dy2+1/dz2) and its reciprocal (linear_solver_jacobi.c:62-63)
     // physical-boundary flags: glo[a]/ghi[a] == 1 when the low/high side of axis a (0=x,1=y,2=z)
     // is a true domain boundary (Neumann ghost / BC applies); 0 when it is a halo.

@@ -54,12 +54,12 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
             const double* f = qin.a[q];
             if (D3) F[q].p = f[zp];
             const double e = f[n + oxp], w_ = f[n + oxm], nn = f[n + oyp], s_ = f[n + oym], cc = F[q].c;
-            d1[q][0] = clampv(100.0, (e - w_) * g.inv_2dx);
-            d1[q][1] = clampv(100.0, (nn - s_) * g.inv_2dy);
+            d1[q][0] = clampv(100.0, (e - w_) / g.two_dx);
+            d1[q][1] = clampv(100.0, (nn - s_) / g.two_dy);
             d1[q][2] = clampv(100.0, (F[q].p - F[q].m) * g.inv_2dz);
             if (q < 3) {
-                d2[q][0] = clampv(1000.0, (e - 2.0 * cc + w_) * g.inv_dx2);
-                d2[q][1] = clampv(1000.0, (nn - 2.0 * cc + s_) * g.inv_dy2);
+                d2[q][0] = clampv(1000.0, (e - 2.0 * cc + w_) / g.dx2);
+                d2[q][1] = clampv(1000.0, (nn - 2.0 * cc + s_) / g.dy2);
                 d2[q][2] = clampv(1000.0, (F[q].p - 2.0 * cc + F[q].m) * g.inv_dz2);
             }
         }
@@ -74,11 +74,11 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
                 fv += -c.beta * dT * c.gy;
                 fw += -c.beta * dT * c.gz;
             }
-            const double uc = F[0].c, vc = F[1].c, wc = F[2].c, rinv = 1.0 / rh;
+            const double uc = F[0].c, vc = F[1].c, wc = F[2].c;
             const double src[3] = {fu, fv, fw};
 #pragma unroll
             for (int q = 0; q < 3; q++)
-                kq[q] = -uc * d1[q][0] - vc * d1[q][1] - wc * d1[q][2] - d1[3][q] * rinv +
+                kq[q] = -uc * d1[q][0] - vc * d1[q][1] - wc * d1[q][2] - d1[3][q] / rh +
                         nu * (d2[q][0] + d2[q][1] + d2[q][2]) + src[q];
             const double div = clampv(10.0, d1[0][0] + d1[1][1] + d1[2][2]);
             kq[3] = -0.1 * rh * div;

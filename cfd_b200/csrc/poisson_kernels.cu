@@ -138,7 +138,7 @@ __global__ void k_stationary_final(Ctl* ctl, KArgs a) { (void)stationary_decide(
 
 // Jacobi sweep s: reads x_s (ghosts valid), writes x_{s+1} with its Neumann ghosts, and gets
 // the L-inf residual of x_s for free from the same loads.  24 B/cell: x in, rhs in, x out.
-template <bool D3>
+template <bool D3, bool RES>
 __global__ void __launch_bounds__(TX* TY)
 k_jacobi(Geom g, const double* __restrict__ xin, double* __restrict__ xout,
          const double* __restrict__ rhs, Ctl* ctl, RedBuf rb, KArgs a) {
@@ -160,20 +160,22 @@ k_jacobi(Geom g, const double* __restrict__ xin, double* __restrict__ xout,
             if (D3) zp = xin[n + g.sz];
             const double xe = xin[n + 1], xw = xin[n - 1], yn = xin[n + g.sy], ys = xin[n - g.sy];
             const double f = __ldg(rhs + n);
-            const double lap = (xe - 2.0 * zc + xw) * g.inv_dx2 + (yn - 2.0 * zc + ys) * g.inv_dy2 +
-                               (zp + zm - 2.0 * zc) * g.inv_dz2;
-            rmax[0] = fmax(rmax[0], fabs(lap - f));
-            const double v = -(f - (xe + xw) * g.inv_dx2 - (yn + ys) * g.inv_dy2 -
+            if (RES) {
+                const double lap = (xe - 2.0 * zc + xw) / g.dx2 + (yn - 2.0 * zc + ys) / g.dy2 +
+                                   (zp + zm - 2.0 * zc) * g.inv_dz2;
+                rmax[0] = fmax(rmax[0], fabs(lap - f));
+            }
+            const double v = -(f - (xe + xw) / g.dx2 - (yn + ys) / g.dy2 -
                                (zp + zm) * g.inv_dz2) * g.inv_factor;
             store_with_ghosts<D3>(g, xout, i, j, k, n, v);
             zm = zc;
             zc = zp;
         }
     }
-    block_reduce_finish<1, true>(rmax, rb, &ctl->dot[a.it & 1]);
+    if (RES) block_reduce_finish<1, true>(rmax, rb, &ctl->dot[a.it & 1]);
 }
 
-// One colour of Red-Black SOR, in place.  colour 0 = (i+j+k) even (global indices).
+// One colour of Red-Black SOR, in place.  colour 0 = first half-sweep = (i+j+k) odd (global indices).
 template <bool D3>
 __global__ void __launch_bounds__(TX* TY)
 k_redblack(Geom g, double* x, const double* __restrict__ rhs, Ctl* ctl, KArgs a, int colour,
@@ -184,10 +186,12 @@ k_redblack(Geom g, double* x, const double* __restrict__ rhs, Ctl* ctl, KArgs a,
     long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
     const int par0 = (int)((g.gi0 + i + g.gj0 + j + g.gk0) & 1);
     for (int k = kb; k < ke; k++, n += g.sz) {
-        if (((par0 + k) & 1) != colour) continue;
+        // first half-sweep: i_start = ((j+k)%2==0) ? 1 : 2, i.e. the cells with (i+j+k) ODD
+        // (linear_solver_redblack.c:103-105; the "red = even" comment there does not match the code)
+        if (((par0 + k) & 1) == colour) continue;
         const double zp = D3 ? x[n + g.sz] : 0.0, zm = D3 ? x[n - g.sz] : 0.0;
-        const double pn = -(__ldg(rhs + n) - (x[n + 1] + x[n - 1]) * g.inv_dx2 -
-                            (x[n + g.sy] + x[n - g.sy]) * g.inv_dy2 - (zp + zm) * g.inv_dz2) *
+        const double pn = -(__ldg(rhs + n) - (x[n + 1] + x[n - 1]) / g.dx2 -
+                            (x[n + g.sy] + x[n - g.sy]) / g.dy2 - (zp + zm) * g.inv_dz2) *
                           g.inv_factor;
         const double xc = x[n];
         store_with_ghosts<D3>(g, x, i, j, k, n, xc + a.omega * (pn - xc));
@@ -208,8 +212,8 @@ k_linf_residual(Geom g, const double* __restrict__ x, const double* __restrict__
         double zm = D3 ? x[n - g.sz] : 0.0, zc = x[n], zp = 0.0;
         for (int k = kb; k < ke; k++, n += g.sz) {
             if (D3) zp = x[n + g.sz];
-            const double lap = (x[n + 1] - 2.0 * zc + x[n - 1]) * g.inv_dx2 +
-                               (x[n + g.sy] - 2.0 * zc + x[n - g.sy]) * g.inv_dy2 +
+            const double lap = (x[n + 1] - 2.0 * zc + x[n - 1]) / g.dx2 +
+                               (x[n + g.sy] - 2.0 * zc + x[n - g.sy]) / g.dy2 +
                                (zp + zm - 2.0 * zc) * g.inv_dz2;
             rmax[0] = fmax(rmax[0], fabs(lap - __ldg(rhs + n)));
             zm = zc;
@@ -571,8 +575,12 @@ void launch_neumann_fill(const LaunchCtx& L, double* x, int seq, int honour_skip
 }
 void launch_jacobi(const LaunchCtx& L, const KArgs& a0, const double* xin, double* xout, const double* rhs) {
     const KArgs a = with_chunk(L, a0);
-    if (L.g.dim3) CFDB_LAUNCH(KK_JACOBI, L.st, k_jacobi<true><<<L.grid(), blk(), 0, L.st>>>(L.g, xin, xout, rhs, L.ctl, L.rb, a));
-    else CFDB_LAUNCH(KK_JACOBI, L.st, k_jacobi<false><<<L.grid(), blk(), 0, L.st>>>(L.g, xin, xout, rhs, L.ctl, L.rb, a));
+    // the residual of x_q is only consulted when the reference would have computed it
+    const bool res = (a.it == 0) || ((a.it - 1) % a.check == 0);
+#define CFDB_JAC(D3, RES) CFDB_LAUNCH(KK_JACOBI, L.st, (k_jacobi<D3, RES><<<L.grid(), blk(), 0, L.st>>>(L.g, xin, xout, rhs, L.ctl, L.rb, a)))
+    if (L.g.dim3) { if (res) CFDB_JAC(true, true); else CFDB_JAC(true, false); }
+    else { if (res) CFDB_JAC(false, true); else CFDB_JAC(false, false); }
+#undef CFDB_JAC
 }
 void launch_redblack(const LaunchCtx& L, const KArgs& a0, double* x, const double* rhs, int colour, int decide) {
     const KArgs a = with_chunk(L, a0);

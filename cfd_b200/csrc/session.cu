@@ -68,6 +68,22 @@ cfd_status_t dalloc(cfd_b200_session* s, double** p) {
     return CFD_SUCCESS;
 }
 
+// Every spacing-derived constant, formed exactly as the reference forms it on the host.
+void set_spacing(Geom& g, double dx, double dy, double dz) {
+    g.two_dx = 2.0 * dx;
+    g.two_dy = 2.0 * dy;
+    g.dx2 = dx * dx;
+    g.dy2 = dy * dy;
+    g.inv_2dx = 1.0 / (2.0 * dx);
+    g.inv_2dy = 1.0 / (2.0 * dy);
+    g.inv_dx2 = 1.0 / (dx * dx);
+    g.inv_dy2 = 1.0 / (dy * dy);
+    g.inv_2dz = (g.dim3 && dz > 0.0) ? 1.0 / (2.0 * dz) : 0.0;
+    g.inv_dz2 = (g.dim3 && dz > 0.0) ? 1.0 / (dz * dz) : 0.0;
+    g.factor = 2.0 * (g.inv_dx2 + g.inv_dy2 + g.inv_dz2);
+    g.inv_factor = 1.0 / g.factor;
+}
+
 static void fill_geom(cfd_b200_session* s) {
     const cfd_b200_session_desc_t& d = s->desc;
     Geom& g = s->g;
@@ -80,14 +96,7 @@ static void fill_geom(cfd_b200_session* s) {
     g.sz = g.dim3 ? (long long)d.nx * d.ny : 0;
     g.k0 = g.dim3 ? 1 : 0;
     g.k1 = g.dim3 ? g.nz - 1 : 1;
-    g.inv_2dx = 1.0 / (2.0 * d.dx);
-    g.inv_2dy = 1.0 / (2.0 * d.dy);
-    g.inv_dx2 = 1.0 / (d.dx * d.dx);
-    g.inv_dy2 = 1.0 / (d.dy * d.dy);
-    g.inv_2dz = (g.dim3 && d.dz > 0.0) ? 1.0 / (2.0 * d.dz) : 0.0;
-    g.inv_dz2 = (g.dim3 && d.dz > 0.0) ? 1.0 / (d.dz * d.dz) : 0.0;
-    g.factor = 2.0 * (g.inv_dx2 + g.inv_dy2 + g.inv_dz2);
-    g.inv_factor = 1.0 / g.factor;
+    set_spacing(g, d.dx, d.dy, d.dz);
     for (int a = 0; a < 3; a++) g.glo[a] = g.ghi[a] = 1;
     s->dec_axis = g.dim3 ? 2 : 1;
     if (d.nranks > 1) {

@@ -71,6 +71,7 @@ struct cfd_b200_session {
 };
 
 namespace cfdb {
+void set_spacing(Geom& g, double dx, double dy, double dz);
 cfd_status_t dalloc(cfd_b200_session* s, double** p);           // zero-filled N doubles
 cfd_status_t session_upload(cfd_b200_session* s, const flow_field* f, int mask);
 cfd_status_t session_download(cfd_b200_session* s, flow_field* f, int mask);

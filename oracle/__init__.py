@@ -28,8 +28,9 @@ def build(quiet=True):
 class Oracle:
     """CPU restatement (oracle.c)."""
 
-    def __init__(self):
-        path = os.path.join(HERE, "liboracle.so")
+    def __init__(self, variant=""):
+        """variant "ld": Krylov dot products accumulated in long double (sensitivity probe)."""
+        path = os.path.join(HERE, "liboracle%s.so" % (("_" + variant) if variant else ""))
         if not os.path.exists(path):
             build()
         L = self.lib = C.CDLL(path)

@@ -339,6 +339,15 @@ static int stationary_solve(const geo_t* g, poisson_solver_method_t method,
 
 /* Krylov building blocks on interior cells -- cpu/linear_solver_cg.c:67-193. */
 static double dot(const geo_t* g, const double* a, const double* b) {
+#ifdef ORC_DOT_LONGDOUBLE
+    /* Sensitivity probe only (liboracle_ld.so, tests/test_oracle.py::test_bicgstab_is_sensitive...):
+     * the same sum accumulated in 80-bit precision, i.e. a legal re-rounding of the reduction.
+     * Shows how far the reference's own Krylov iterates move when a dot product changes in the
+     * last bit -- which is what any parallel (re-ordered) reduction does. */
+    long double sl = 0.0L;
+    FOR_INTERIOR(*g, i, j, k, n) sl += (long double)a[n] * (long double)b[n];
+    return (double)sl;
+#endif
     double s = 0.0;
     FOR_INTERIOR(*g, i, j, k, n) s += a[n] * b[n];
     return s;

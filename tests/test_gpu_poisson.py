@@ -2,8 +2,15 @@
 (create_{jacobi,redblack,cg,bicgstab}_gpu_solver) and compared with the oracle.
 
 Tolerances (BASELINE.json north_star): Jacobi / Red-Black SOR reproduce the reference's
-iteration count exactly and x to <= 1e-10 (rel L2 and rel Linf); CG / PCG / BiCGSTAB, whose
+iteration count exactly and x BIT-EXACTLY (bar: <= 1e-10); CG / PCG / BiCGSTAB, whose
 reductions are reordered, to <= 1e-8 on the final field.
+
+BiCGSTAB: the reference's own iterates are chaotic under a last-bit change of a dot product
+(tests/test_oracle.py::test_bicgstab_is_sensitive_to_reduction_rounding_but_cg_is_not), so at
+the default 1e-6 tolerance two correct implementations differ by a few iterations and ~1e-4 in
+x.  Its <= 1e-8 gate is therefore taken at Poisson tolerance 1e-13 (both sides converge to the
+same solution); at the default tolerance the test checks the stopping rule and iteration count
+within 15 %.
 """
 import glob
 import os
@@ -20,6 +27,9 @@ GOLD = os.path.join(os.path.dirname(__file__), "golden")
 METH = {"jacobi": abi.POISSON_METHOD_JACOBI, "rbsor": abi.POISSON_METHOD_REDBLACK_SOR,
         "cg": abi.POISSON_METHOD_CG, "pcg": abi.POISSON_METHOD_CG, "bicgstab": abi.POISSON_METHOD_BICGSTAB}
 TOL = {"jacobi": 1e-10, "rbsor": 1e-10, "cg": 1e-8, "pcg": 1e-8, "bicgstab": 1e-8}
+
+
+TIGHT = dict(tolerance=1e-13, absolute_tolerance=1e-15)
 
 
 def pparams(name, **kw):
@@ -48,13 +58,19 @@ def gpu_solve(name, g, x, rhs, pp):
 def test_poisson_matches_oracle(orc, shape, name):
     nx, ny, nz = shape
     g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=5)
-    pp = pparams(name)
+    pp = pparams(name, **(TIGHT if name == "bicgstab" else {}))
     xo = x.copy()
     dx, dy, dz = g.spacing
     rc_o, st_o = orc.poisson(METH[name], nx, ny, nz, dx, dy, dz, pp, xo, rhs, np.zeros_like(x))
     rc_g, st_g = gpu_solve(name, g, x, rhs, pp)
     assert rc_g == rc_o
     assert st_g.status == st_o.status
+    assert abs(st_g.initial_residual - st_o.initial_residual) <= 1e-9 * st_o.initial_residual
+    if name == "bicgstab":
+        assert abs(st_g.iterations - st_o.iterations) <= 3 + 0.15 * st_o.iterations
+        l2, li = cases.rel_err(x, xo)
+        assert l2 <= TOL[name] and li <= TOL[name], (l2, li)
+        return
     if name in ("jacobi", "rbsor"):
         assert st_g.iterations == st_o.iterations
     else:
@@ -62,8 +78,51 @@ def test_poisson_matches_oracle(orc, shape, name):
     if st_g.iterations == st_o.iterations:
         l2, li = cases.rel_err(x, xo)
         assert l2 <= TOL[name] and li <= TOL[name], (l2, li)
-        assert abs(st_g.final_residual - st_o.final_residual) <= 1e-6 * max(st_o.final_residual, 1e-300)
-    assert abs(st_g.initial_residual - st_o.initial_residual) <= 1e-9 * st_o.initial_residual
+        if name in ("jacobi", "rbsor"):  # no reordered reduction anywhere: bit-exact
+            assert np.array_equal(x, xo)
+            assert st_g.final_residual == st_o.final_residual
+        # (a residual already below the absolute tolerance is rounding noise of the dot order)
+        assert abs(st_g.final_residual - st_o.final_residual) <= 1e-6 * max(st_o.final_residual, pp.absolute_tolerance)
+
+
+@pytest.mark.parametrize("shape", [(33, 33, 1), (34, 20, 18), (129, 129, 1)])
+def test_bicgstab_default_tolerance(orc, shape):
+    """Default 1e-6 tolerance: same status, iteration count within 15 %, and the GPU result
+    satisfies the reference's stopping rule on an independently computed residual."""
+    nx, ny, nz = shape
+    g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=5)
+    pp = pparams("bicgstab")
+    xo, x0 = x.copy(), x.copy()
+    dx, dy, dz = g.spacing
+    rc_o, st_o = orc.poisson(METH["bicgstab"], nx, ny, nz, dx, dy, dz, pp, xo, rhs, None)
+    rc_g, st_g = gpu_solve("bicgstab", g, x, rhs, pp)
+    assert rc_g == rc_o == 0 and st_g.status == st_o.status == abi.POISSON_CONVERGED
+    assert abs(st_g.iterations - st_o.iterations) <= 3 + 0.15 * st_o.iterations
+    res = krylov_true_residual(orc, x, x0, rhs, g)
+    assert res <= 1.05 * max(pp.tolerance * st_g.initial_residual, pp.absolute_tolerance)
+    assert max(cases.rel_err(x, xo)) <= 5e-2
+
+
+def krylov_true_residual(orc, x, x0, rhs, g):
+    """L2 norm of rhs - lap(x) on interior cells with the ghost values the Krylov solvers hold
+    fixed during the iteration: the Neumann fill of the INITIAL guess (linear_solver_cg.c:310,
+    the work vectors keep zero boundaries, so x's ghosts only change in the final BC)."""
+    nz, ny, nx = x.shape
+    xe = x0.copy()
+    orc.lib.orc_neumann_scalar(abi._ptr(xe), nx, ny, nz)
+    if nz > 1:
+        xe[1:-1, 1:-1, 1:-1] = x[1:-1, 1:-1, 1:-1]
+    else:
+        xe[:, 1:-1, 1:-1] = x[:, 1:-1, 1:-1]
+    dx, dy, dz = g.spacing
+    lap = (xe[:, 1:-1, 2:] - 2 * xe[:, 1:-1, 1:-1] + xe[:, 1:-1, :-2]) / dx ** 2 + \
+          (xe[:, 2:, 1:-1] - 2 * xe[:, 1:-1, 1:-1] + xe[:, :-2, 1:-1]) / dy ** 2
+    if nz > 1:
+        lap = lap[1:-1] + (xe[2:, 1:-1, 1:-1] - 2 * xe[1:-1, 1:-1, 1:-1] + xe[:-2, 1:-1, 1:-1]) / dz ** 2
+        r = lap - rhs[1:-1, 1:-1, 1:-1]
+    else:
+        r = lap - rhs[:, 1:-1, 1:-1]
+    return float(np.sqrt(np.sum(r * r)))
 
 
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "poisson_*.npz"))))
@@ -88,6 +147,11 @@ def test_iteration_cap_and_check_interval(orc, name):
         xg, xo = x.copy(), x.copy()
         rc_o, st_o = orc.poisson(METH[name], 24, 18, 1, dx, dy, dz, pp, xo, rhs, np.zeros_like(x))
         rc_g, st_g = gpu_solve(name, g, xg, rhs, pp)
+        if name == "bicgstab" and "max_iterations" not in kw:
+            # uncapped run at the default tolerance: chaotic trajectory (see module docstring)
+            assert (rc_g, st_g.status) == (rc_o, st_o.status), kw
+            assert abs(st_g.iterations - st_o.iterations) <= 3 + 0.15 * st_o.iterations
+            continue
         assert (rc_g, st_g.status, st_g.iterations) == (rc_o, st_o.status, st_o.iterations), kw
         l2, li = cases.rel_err(xg, xo)
         assert max(l2, li) <= TOL[name], (kw, l2, li)
@@ -117,32 +181,32 @@ def test_omega_override_and_sor_factor(orc):
 @pytest.mark.parametrize("name,shape", [("jacobi", (256, 256, 1)), ("rbsor", (96, 96, 96)),
                                         ("cg", (128, 128, 128)), ("pcg", (512, 512, 1)),
                                         ("bicgstab", (128, 128, 128))])
-def test_large_grid_properties(name, shape):
+def test_large_grid_properties(orc, name, shape):
     """Sizes the oracle does not finish in seconds: check size-independent properties instead --
     residual reduction as promised by the stopping rule, Neumann ghosts, rhs untouched."""
     nx, ny, nz = shape
     g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=9)
-    rhs0 = rhs.copy()
+    rhs0, x0 = rhs.copy(), x.copy()
     pp = pparams(name, max_iterations=400 if name in ("jacobi", "rbsor") else 5000)
     rc, st = gpu_solve(name, g, x, rhs, pp)
     assert np.array_equal(rhs, rhs0)
     dx, dy, dz = g.spacing
-    xi = x
-    lap = (xi[:, 1:-1, 2:] - 2 * xi[:, 1:-1, 1:-1] + xi[:, 1:-1, :-2]) / dx ** 2 + \
-          (xi[:, 2:, 1:-1] - 2 * xi[:, 1:-1, 1:-1] + xi[:, :-2, 1:-1]) / dy ** 2
-    if nz > 1:
-        lap = lap[1:-1] + (xi[2:, 1:-1, 1:-1] - 2 * xi[1:-1, 1:-1, 1:-1] + xi[:-2, 1:-1, 1:-1]) / dz ** 2
-        r = lap - rhs[1:-1, 1:-1, 1:-1]
-    else:
-        r = lap - rhs[:, 1:-1, 1:-1]
     if name in ("jacobi", "rbsor"):
+        xi = x
+        lap = (xi[:, 1:-1, 2:] - 2 * xi[:, 1:-1, 1:-1] + xi[:, 1:-1, :-2]) / dx ** 2 + \
+              (xi[:, 2:, 1:-1] - 2 * xi[:, 1:-1, 1:-1] + xi[:, :-2, 1:-1]) / dy ** 2
+        if nz > 1:
+            lap = lap[1:-1] + (xi[2:, 1:-1, 1:-1] - 2 * xi[1:-1, 1:-1, 1:-1] + xi[:-2, 1:-1, 1:-1]) / dz ** 2
+            r = lap - rhs[1:-1, 1:-1, 1:-1]
+        else:
+            r = lap - rhs[:, 1:-1, 1:-1]
         res = np.max(np.abs(r))
         assert res <= st.initial_residual * 1.0000001  # never worse than the start
         assert abs(res - st.final_residual) <= 1e-6 * st.final_residual
     else:
         assert rc == 0 and st.status == abi.POISSON_CONVERGED
-        res = np.sqrt(np.sum(r * r))
-        assert res <= 1.01 * max(1e-6 * st.initial_residual, 1e-10) + 1e-9 * st.initial_residual
+        res = krylov_true_residual(orc, x, x0, rhs, g)
+        assert res <= 1.05 * max(1e-6 * st.initial_residual, 1e-10)
     # Neumann ghosts: boundary = nearest interior (linear_solver.c:348-392)
     assert np.array_equal(x[:, :, 0], x[:, :, 1]) and np.array_equal(x[:, :, -1], x[:, :, -2])
     assert np.array_equal(x[:, 0, :], x[:, 1, :]) and np.array_equal(x[:, -1, :], x[:, -2, :])

@@ -50,7 +50,11 @@ def test_projection_step_by_step(orc, poisson_cfg, method, tol, case):
         p = cases.params(dt=1e-3, amp=(0.1, 0.05))
     # early cavity steps do not converge within Jacobi's 2000-iteration cap: use the documented
     # "continue" policy on both sides
-    pc = abi.poisson_config(method, on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
+    # BiCGSTAB's <= 1e-8 gate is taken at Poisson tolerance 1e-13: at the default 1e-6 the
+    # reference's own iterates are chaotic under reduction re-rounding (test_oracle.py,
+    # test_bicgstab_is_sensitive_to_reduction_rounding_but_cg_is_not)
+    kw = dict(tolerance=1e-13, absolute_tolerance=1e-15) if method == "bicgstab" else {}
+    pc = abi.poisson_config(method, on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE, **kw)
     api.set_poisson(pc)
     fo = f.copy()
     slv = api.GpuSolver("projection_gpu")
@@ -207,10 +211,20 @@ def test_error_behaviour(poisson_cfg):
     assert api.solve_method_gpu("projection", f, g, p) == abi.CFD_ERROR_MAX_ITER
     for k in FIELDS:
         np.testing.assert_array_equal(getattr(f, k), getattr(before, k))
-    # NaN in the input -> CFD_ERROR_DIVERGED
+    # NaN handling is the reference's, oddities included: a NaN in an INTERIOR velocity cell is
+    # laundered to +100 by the fmax(-100, fmin(100, .)) clamp (solver_projection.c:180-182) and the
+    # step reports success; a NaN on a boundary cell or in p survives to the scan (:281-289).
     api.set_poisson("cg", on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
-    f.u[0, 5, 5] = np.nan
-    assert api.solve_method_gpu("projection", f, g, p) == abi.CFD_ERROR_DIVERGED
+    f1 = before.copy()
+    f1.u[0, 5, 5] = np.nan
+    assert api.solve_method_gpu("projection", f1, g, p) == abi.CFD_SUCCESS
+    assert np.all(np.isfinite(f1.u))
+    f2 = before.copy()
+    f2.u[0, 0, 5] = np.nan
+    assert api.solve_method_gpu("projection", f2, g, p) == abi.CFD_ERROR_DIVERGED
+    f3 = before.copy()
+    f3.p[0, 5, 5] = np.nan
+    assert api.solve_method_gpu("projection", f3, g, p) == abi.CFD_ERROR_DIVERGED
     # explicit Euler is outside the hot path
     assert api.solve_method_gpu("explicit_euler", before, g, p) == abi.CFD_ERROR_UNSUPPORTED
 

@@ -178,3 +178,35 @@ def test_nonconvergence_policy(orc):
     pc.on_nonconvergence = abi.CFD_B200_NONCONV_CONTINUE
     rc, _ = orc.projection(f, g, p, pc, 1)
     assert rc == 0
+
+
+def test_bicgstab_is_sensitive_to_reduction_rounding_but_cg_is_not():
+    """Why BiCGSTAB parity is tested at a tight Poisson tolerance.
+
+    Accumulating the Krylov dot products in long double -- a legal re-rounding, the kind any
+    parallel reduction performs -- leaves the reference's CG trajectory intact (same iteration
+    count, x equal to ~1e-14) but moves its BiCGSTAB off by several iterations and by far more
+    than 1e-8 in x at the default 1e-6 tolerance.  At tolerance 1e-13 both variants land on
+    the same solution to better than 1e-8, which is what the GPU tests compare."""
+    import oracle
+    a, b = oracle.Oracle(), oracle.Oracle("ld")
+    g, x, rhs = cases.poisson_problem(129, 129, 1, seed=5)
+    dx, dy, dz = g.spacing
+
+    def run(o, meth, tol):
+        pp = abi.poisson_params_default()
+        pp.tolerance, pp.absolute_tolerance = tol, min(1e-10, tol * 1e-2)
+        xs = x.copy()
+        rc, st = o.poisson(meth, 129, 129, 1, dx, dy, dz, pp, xs, rhs, None)
+        assert rc == 0
+        return st.iterations, xs
+
+    ia, xa = run(a, abi.POISSON_METHOD_CG, 1e-6)
+    ib, xb = run(b, abi.POISSON_METHOD_CG, 1e-6)
+    assert ia == ib and max(cases.rel_err(xa, xb)) < 1e-12
+    ia, xa = run(a, abi.POISSON_METHOD_BICGSTAB, 1e-6)
+    ib, xb = run(b, abi.POISSON_METHOD_BICGSTAB, 1e-6)
+    assert ia != ib and max(cases.rel_err(xa, xb)) > 1e-6  # chaotic at the default tolerance
+    ia, xa = run(a, abi.POISSON_METHOD_BICGSTAB, 1e-13)
+    ib, xb = run(b, abi.POISSON_METHOD_BICGSTAB, 1e-13)
+    assert max(cases.rel_err(xa, xb)) < 1e-8
