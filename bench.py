@@ -1,0 +1,455 @@
+#!/usr/bin/env python
+"""bench.py -- projection-step MLUPS (FP64) and Poisson-sweep HBM GB/s against the roofline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 1024] [--iters 50]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json configs[4], the configuration the metric is quoted on): synthetic 3-D box,
+n^3 cells PER GPU (n = 1024 when it fits), slab-decomposed along z, one projection step =
+predictor + divergence + pressure Poisson (BiCGSTAB, exactly `--iters` iterations: cap reached =>
+continue, SURVEY 8d C5 "fixed-50-iteration timing mode") + corrector.  A fixed iteration count
+makes MLUPS size-normalised, so the CPU arms can run the same step on a smaller box.
+
+One JSON line on stdout (rank 0).  `value` is device-resident throughput (CUDA events on the
+session stream, max over ranks); `e2e` goes through the drop-in C-ABI entry point
+solve_projection_method_gpu() with pinned HOST flow_field arrays (H2D + D2H inside the timed
+region); `roofline` is the dominant kernel, timed with per-launch CUDA events inside the same
+timed region; `cpu_baseline` is the reference CPU code on this host (see oracle/Makefile).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "projection_step_mlups_fp64"
+UNIT = "MLUPS"
+DT = 1e-4
+NU = 0.01
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=0, help="cells per axis per GPU (0 = 1024 if it fits, else smaller)")
+    ap.add_argument("--iters", type=int, default=50, help="BiCGSTAB iterations per step (fixed)")
+    ap.add_argument("--method", default="bicgstab", choices=["jacobi", "rbsor", "cg", "pcg", "bicgstab"])
+    ap.add_argument("--cpu-n", type=int, default=0, help="box edge of the CPU sample (0 = auto)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# ------------------------------------------------------------------------------------------
+# clocks sampler (B200_PROFILING.md: sample nvidia-smi DURING the timed region)
+# ------------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.stop, self.index = [], False, index
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                if out.returncode == 0 and out.stdout.strip():
+                    self.rows.append([c.strip() for c in out.stdout.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for q, n in enumerate(names) if any(len(r) > 2 + q and r[2 + q].startswith("Active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+# ------------------------------------------------------------------------------------------
+# workload helpers shared by both arms
+# ------------------------------------------------------------------------------------------
+def make_params():
+    from cfd_b200 import abi
+    p = abi.ns_params_default()
+    p.dt, p.mu = DT, NU
+    p.source_amplitude_u = p.source_amplitude_v = 0.0  # amplitudes 0
+    p.max_iter = 1
+    return p
+
+
+def poisson_cfg(method, iters):
+    from cfd_b200 import abi
+    return abi.poisson_config(method, max_iterations=iters, on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
+
+
+def synthetic_host_field(n, alloc=None):
+    """The C5 state on the host (numpy): u = 0.1 sin2pix cos2piy cos2piz, v = -0.1 cos2pix sin2piy cos2piz,
+    w = 0, each + 1e-3 uniform noise (seed 12345); p = 0, rho = 1, T = 300."""
+    import numpy as np
+    from cfd_b200 import abi
+    g = abi.HostGrid(n, n, n, 0.0, 1.0, 0.0, 1.0, 0.0, 1.0)
+    f = abi.HostField(n, n, n, alloc=alloc) if alloc else abi.HostField(n, n, n)
+    x = np.linspace(0.0, 1.0, n)
+    sx, cx = np.sin(2 * np.pi * x), np.cos(2 * np.pi * x)
+    rng = np.random.default_rng(12345)
+    for k in range(n):  # plane by plane: keeps the temporary small at 1024^3
+        cz = cx[k]
+        f.u[k] = 0.1 * cz * np.outer(cx, sx) + 1e-3 * (2.0 * rng.random((n, n)) - 1.0)
+        f.v[k] = -0.1 * cz * np.outer(sx, cx) + 1e-3 * (2.0 * rng.random((n, n)) - 1.0)
+        f.w[k] = 1e-3 * (2.0 * rng.random((n, n)) - 1.0)
+    f.p[...] = 0.0
+    f.rho[...] = 1.0
+    f.T[...] = 300.0
+    return g, f
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the reference's own code on the host cores (oracle/_ref, see oracle/Makefile):
+# reference Poisson solver objects + the restated OpenMP stencil loops of solver_projection_omp.c
+# ------------------------------------------------------------------------------------------
+def cpu_arm(method, iters, steps, warmup, budget_s, n_force=0):
+    import numpy as np
+    import oracle
+    from cfd_b200 import abi
+    kind = "reference"
+    try:
+        orc = oracle.Oracle("ref")
+    except (FileNotFoundError, OSError):
+        orc, kind = oracle.Oracle(), "port"  # scalar restatement, 1 thread
+    cores = host_cores() if kind == "reference" else 1
+    meth = {"jacobi": abi.POISSON_METHOD_JACOBI, "rbsor": abi.POISSON_METHOD_REDBLACK_SOR,
+            "cg": abi.POISSON_METHOD_CG, "pcg": abi.POISSON_METHOD_CG, "bicgstab": abi.POISSON_METHOD_BICGSTAB}[method]
+    pc, p = poisson_cfg(method, iters), make_params()
+    names = {1: "scalar", 2: "omp", 3: "simd(avx2+omp)"}
+
+    def run(n, backend, nsteps):
+        if kind == "reference":
+            orc.lib.orc_set_ref_backend(backend)
+        g, f = synthetic_host_field(n)
+        t0 = time.perf_counter()
+        rc, st = orc.projection(f, g, p, pc, nsteps)
+        dt = time.perf_counter() - t0
+        if rc != 0:
+            raise RuntimeError("CPU projection failed rc=%d" % rc)
+        return dt
+
+    backend = 1
+    if kind == "reference":
+        # probe every backend the reference offers for this method on a small box, keep the fastest
+        best = None
+        for b in (3, 2, 1):
+            if not orc.lib.orc_ref_backend_available(meth, b):
+                continue
+            run(48, b, 1)
+            t = run(64, b, 1)
+            if best is None or t < best[0]:
+                best = (t, b)
+        t64, backend = best
+        if backend == 1:
+            pass  # the stencil loops still use OpenMP; the scalar Poisson dominates
+    else:
+        t64 = run(64, 1, 1)
+    per_cell_step = t64 / 64 ** 3
+    n = n_force
+    if not n:
+        n = 64
+        for cand in (96, 128, 160, 192, 256, 320, 384):
+            if per_cell_step * cand ** 3 * (steps + warmup) <= budget_s:
+                n = cand
+    for _ in range(warmup):
+        run(n, backend, 1)
+    dt = run(n, backend, steps)
+    mlups = n ** 3 * steps / dt / 1e6
+    sample = ("%d^3 box, %d projection steps (+%d warm-up), %s x%d iterations, reference Poisson backend %s, "
+              "restated OpenMP stencil loops, %d threads" % (n, steps, warmup, method, iters,
+                                                            names.get(backend, "?") if kind == "reference" else "scalar port",
+                                                            cores))
+    return {"value": mlups, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample, "n": n,
+            "ms_per_step": dt / steps * 1e3}
+
+
+def reference_main(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    r = cpu_arm(a.method, a.iters, a.steps, a.warmup, budget_s=150.0, n_force=a.cpu_n)
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": a.gpus,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C5 synthetic 3-D box, projection step + %s x%d iterations (fixed), CPU sample %d^3"
+                                   % (a.method, a.iters, r["n"]), "poisson": a.method, "poisson_iterations": a.iters,
+                       "dt": DT, "nu": NU},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------
+FIELDS_RESIDENT = {"bicgstab": 17, "cg": 13, "pcg": 13, "rbsor": 9, "jacobi": 10}  # device arrays of one slab
+
+
+def pick_n(method, want, free_bytes):
+    for n in ([want] if want else [1024, 896, 768, 640, 512, 384, 256]):
+        if (FIELDS_RESIDENT[method] + 0.5) * 8.0 * n ** 3 <= 0.92 * free_bytes:
+            return n
+    raise RuntimeError("not enough device memory for the smallest bench box")
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ours_main(a):
+    import numpy as np
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: cfd_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    td = None
+    if world > 1:
+        import torch.distributed as td
+        td.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from cfd_b200 import abi, api, dist, lib
+    L = lib.load()
+    free, _total = torch.cuda.mem_get_info()
+    n = pick_n(a.method, a.n, free)
+    if td is not None:  # every rank must use the same box
+        t = torch.tensor([n], device="cuda", dtype=torch.int64)
+        td.all_reduce(t, op=td.ReduceOp.MIN)
+        n = int(t.item())
+    h = 1.0 / (n - 1)
+    gnz = (n - 2) * world + 2
+    s = api.Session(n, n, n, h, h, h, 0.0, 0.0, rank * (n - 2) * h, rank=rank, nranks=world, device=local)
+    dist.attach_comm(s, rank, world)
+    s.init_synthetic(12345, rank * (n - 2), gnz)
+    prm, pc = make_params(), poisson_cfg(a.method, a.iters)
+    stream = torch.cuda.ExternalStream(s.stream())
+
+    def barrier():
+        torch.cuda.synchronize()
+        if td is not None:
+            td.barrier()
+        torch.cuda.synchronize()
+
+    def run_steps(k):
+        rc, st = s.projection(prm, pc, k)
+        if rc != 0:
+            raise RuntimeError("projection failed rc=%d: %s" % (rc, lib.last_error()))
+        return st
+
+    run_steps(a.warmup)
+    s.reset_kernel_stats()
+    s.profile(True)
+    l0 = L.cfd_b200_kernel_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    with Clocks(local) as clk:
+        e0.record(stream)
+        st = run_steps(a.steps)
+        e1.record(stream)
+        barrier()
+    ms = e0.elapsed_time(e1)
+    launches = int(L.cfd_b200_kernel_launch_count() - l0)
+    s.profile(False)
+    kstats = s.kernel_stats()
+    if td is not None:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        ms = float(t.item())
+    cells_global = n * n * gnz
+    value = cells_global * a.steps / (ms * 1e-3) / 1e6
+
+    # ---- roofline of the dominant kernel (per-launch CUDA events inside the timed region) ----
+    interior = (n - 2) ** 3
+    peak, peak_src = peaks()
+    kstats = [k for k in kstats if k["total_ms"] > 0 and k["bytes_per_cell"] > 0]
+    kstats.sort(key=lambda k: -k["total_ms"])
+    ksum = sum(k["total_ms"] for k in kstats) or 1.0
+    table = []
+    for k in kstats:
+        avg = k["total_ms"] / k["launches"]
+        gbs = k["bytes_per_cell"] * interior / (avg * 1e-3) / 1e9
+        table.append({"kernel": k["name"], "launches": k["launches"], "avg_ms": round(avg, 4),
+                      "share": round(k["total_ms"] / ksum, 4), "bytes_per_cell": k["bytes_per_cell"],
+                      "GBps": round(gbs, 1), "frac": round(gbs / peak, 4)})
+    top = table[0] if table else None
+    roofline = None
+    if top:
+        roofline = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["GBps"], "peak": peak, "unit": "GB/s",
+                    "frac": top["frac"], "traffic": NCU_TRAFFIC.get(top["kernel"]), "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": top["bytes_per_cell"] * interior, "kernels": table}
+    return dict(rank=rank, world=world, local=local, n=n, gnz=gnz, ms=ms, value=value, launches=launches,
+                roofline=roofline, clocks=clk.summary(), session=s, prm=prm, pc=pc, td=td, L=L, stats=st)
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full`
+# capture (profiles/), keyed by kernel family; filled in as captures are taken.
+NCU_TRAFFIC = {}
+
+
+def e2e_arm(a, r):
+    """The same step through the reference-facing boundary with HOST buffers: N = 1 calls the drop-in
+    symbol solve_projection_method_gpu(field, grid, params{max_iter=1}, config) (what the reference's
+    registry wrapper gpu_projection_step calls, solver_registry.c:1121-1135); N > 1 runs the same
+    upload -> step -> download sequence on each rank's slab through the session API (the drop-in symbol
+    is single-GPU).  Inputs live in pinned host memory; every step copies u,v,w,p H2D and back."""
+    import ctypes as C
+    import numpy as np
+    import psutil
+    from cfd_b200 import abi, api, lib
+    L, s, n, world, td = r["L"], r["session"], r["n"], r["world"], r["td"]
+    ne = n
+    need = lambda m: 5.2 * 8.0 * m ** 3 * world  # 4 pinned arrays + rho, every rank on this host
+    while ne > 64 and need(ne) > 0.7 * psutil.virtual_memory().available:
+        ne = ne * 3 // 4
+    if td is not None and ne != n:
+        return {"value": None, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                "note": "host memory too small for pinned slabs on every rank"}
+    count = [0]
+
+    def alloc(m):
+        count[0] += 1
+        if count[0] > 4:  # rho, T: never transferred by the projection path without energy/buoyancy
+            return abi.aligned_zeros(m)
+        p = L.cfd_b200_host_alloc(m * 8)
+        if not p:
+            raise MemoryError("cfd_b200_host_alloc(%d bytes) failed" % (m * 8))
+        keep.append(p)
+        return np.frombuffer((C.c_double * m).from_address(p), dtype=np.float64)
+
+    keep = []
+    g = abi.HostGrid(ne, ne, ne, 0.0, 1.0, 0.0, 1.0, 0.0, 1.0)
+    f = abi.HostField(ne, ne, ne, alloc=alloc)
+    mask = api.FM_U | api.FM_V | api.FM_W | api.FM_P
+    steps = max(1, min(a.steps, 2))
+    if world == 1:
+        if ne == n:
+            s.init_synthetic(12345, 0, n)
+            s.download(f, mask)
+        s.close()  # the drop-in path owns its own cached session; both do not fit at 1024^3
+        if ne != n:
+            _, f0 = synthetic_host_field(ne)
+            for nm in ("u", "v", "w", "p"):
+                getattr(f, nm)[...] = getattr(f0, nm)
+            del f0
+        api.set_poisson(r["pc"])
+        prm = r["prm"]
+        call = lambda: api.solve_method_gpu("projection", f, g, prm)
+    else:
+        s.init_synthetic(12345, r["rank"] * (n - 2), r["gnz"])
+        s.download(f, mask)
+
+        def call():
+            s.upload(f, mask)
+            rc, _ = s.projection(r["prm"], r["pc"], 1)
+            s.download(f, mask)
+            return rc
+    import torch
+    rc = call()  # warm-up: allocations, cached session
+    if rc != 0:
+        raise RuntimeError("e2e projection failed rc=%d: %s" % (rc, lib.last_error()))
+    torch.cuda.synchronize()
+    if td is not None:
+        td.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        rc = call()
+        if rc != 0:
+            raise RuntimeError("e2e projection failed rc=%d: %s" % (rc, lib.last_error()))
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if td is not None:
+        t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        dt = float(t.item())
+    cells = ne * ne * (((ne - 2) * world + 2) if world > 1 else ne)
+    out = {"value": cells * steps / dt / 1e6, "unit": UNIT, "h2d_bytes_per_step": 4 * 8 * ne ** 3 * world,
+           "d2h_bytes_per_step": 4 * 8 * ne ** 3 * world, "steps": steps, "ms_per_step": dt / steps * 1e3,
+           "api": "solve_projection_method_gpu (C-ABI drop-in), pinned host flow_field" if world == 1
+                  else "cfd_b200_session_upload/projection/download per rank, pinned host slabs",
+           "box": "%d^3 per GPU" % ne}
+    for p in keep:
+        L.cfd_b200_host_free(p)
+    return out
+
+
+def main():
+    a = parse()
+    os.environ.setdefault("OMP_NUM_THREADS", str(host_cores()))
+    os.environ.setdefault("OMP_PROC_BIND", "close")
+    if a.impl == "reference":
+        return reference_main(a)
+    r = ours_main(a)
+    e2e = None
+    if not a.no_e2e:
+        try:
+            e2e = e2e_arm(a, r)
+        except MemoryError as ex:
+            e2e = {"value": None, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0, "note": str(ex)}
+    cpu = None
+    if r["rank"] == 0 and r["world"] == 1 and not a.no_cpu:
+        c = cpu_arm(a.method, a.iters, steps=1, warmup=1, budget_s=24.0, n_force=a.cpu_n)
+        cpu = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    if r["rank"] == 0:
+        n, world = r["n"], r["world"]
+        line = {"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": a.steps,
+                "warmup": a.warmup, "ms_per_step": r["ms"] / a.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "C5 synthetic 3-D box %d^3 per GPU, z-slab decomposition, projection step + "
+                                       "%s x%d iterations (fixed: cap reached => continue)" % (n, a.method, a.iters),
+                           "grid_global": [n, n, r["gnz"]], "poisson": a.method, "poisson_iterations": a.iters,
+                           "dt": DT, "nu": NU, "parallelism": "zslab%d" % world,
+                           "l2": "inputs larger than L2 (each field %.1f GB vs 126 MB L2); no flush needed" % (8 * n ** 3 / 1e9)},
+                "roofline": r["roofline"], "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": r["launches"],
+                "clocks": r["clocks"]}
+        print(json.dumps(line))
+    if r["td"] is not None:
+        r["td"].barrier()
+        r["td"].destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -3,6 +3,8 @@
 #include "common.cuh"
 #include "ns_args.h"
 
+#include <vector>
+
 namespace cfdb {
 
 // Everything a launcher needs besides the per-kernel operands.
@@ -25,14 +27,20 @@ enum KernelKind {
 extern const char* const kKernelNames[KK_COUNT];
 extern const double kKernelBytesPerCell[KK_COUNT];
 
-// Optional per-launch profiling hook (set by the session when profiling is enabled).
+// Optional per-launch timing (cfd_b200_session_profile): one CUDA event pair per launch from a
+// growing pool, recorded on the launching stream and NOT synchronised, so a timed region can
+// run with it switched on; collect() resolves the pairs after the stream has drained.
 struct Profiler {
     bool on = false;
     unsigned long long launches[KK_COUNT] = {};
     double ms[KK_COUNT] = {};
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    struct Pair { cudaEvent_t a, b; int kind; };
+    std::vector<Pair> pool;
+    size_t used = 0;
     void begin(cudaStream_t st);
     void end(cudaStream_t st, int kind);
+    void collect();   // adds the elapsed time of every recorded pair to ms[]
+    void release();
 };
 extern thread_local Profiler* t_prof;
 
@@ -86,6 +94,7 @@ void launch_rk_stage(const LaunchCtx& L, const NsConst& c, const RkArgs& ra, con
 void launch_synth_init(const LaunchCtx& L, uint64_t seed, long long gk0, long long gnz, double* u, double* v,
                        double* w, double* p, double* T, double* rho);
 void launch_copy(const LaunchCtx& L, double* dst, const double* src, size_t n);
+void launch_fill(const LaunchCtx& L, double* dst, double v, size_t n);
 void launch_zero_ctl(const LaunchCtx& L);
 
 

@@ -167,7 +167,7 @@ k_field_stats(Geom g, const double* __restrict__ u, const double* __restrict__ v
         const double a = u[t], b = v[t], c = w[t];
         m[0] = fmax(m[0], sqrt(a * a + b * b + c * c));
         m[1] = fmax(m[1], fabs(p[t]));
-        m[2] = fmax(m[2], T[t]);
+        if (T) m[2] = fmax(m[2], T[t]);
     }
     block_reduce_finish<3, true>(m, rb, &ctl->stat[0]);
 }
@@ -199,13 +199,18 @@ __global__ void k_synth_init(Geom g, uint64_t seed, long long gk0, long long gnz
     v[t] = -0.1 * cos(tp * x) * sin(tp * y) * cz + 1e-3 * rnd(1);
     w[t] = g.dim3 ? 1e-3 * rnd(2) : 0.0;
     p[t] = 0.0;
-    T[t] = 300.0;
+    if (T) T[t] = 300.0;
     if (rho) rho[t] = 1.0;
 }
 
 __global__ void k_copy(double* __restrict__ dst, const double* __restrict__ src, size_t n) {
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += stride) dst[t] = src[t];
+}
+
+__global__ void k_fill(double* __restrict__ dst, double v, size_t n) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += stride) dst[t] = v;
 }
 
 __global__ void k_zero_ctl(Ctl* ctl) {

@@ -37,20 +37,38 @@ void set_error(cfd_status_t st, const char* fmt, ...) {
 const char* last_error() { return t_err; }
 
 void Profiler::begin(cudaStream_t st) {
-    if (!e0) {
-        cudaEventCreate(&e0);
-        cudaEventCreate(&e1);
+    if (used >= (1u << 16)) collect();  // bound the pool on very long profiled runs
+    if (used == pool.size()) {
+        Pair p;
+        cudaEventCreate(&p.a);
+        cudaEventCreate(&p.b);
+        p.kind = 0;
+        pool.push_back(p);
     }
-    cudaEventRecord(e0, st);
+    cudaEventRecord(pool[used].a, st);
 }
 void Profiler::end(cudaStream_t st, int kind) {
     launches[kind]++;
     if (!on) return;
-    cudaEventRecord(e1, st);
-    cudaEventSynchronize(e1);
-    float ms_ = 0.f;
-    cudaEventElapsedTime(&ms_, e0, e1);
-    ms[kind] += ms_;
+    pool[used].kind = kind;
+    cudaEventRecord(pool[used].b, st);
+    used++;
+}
+void Profiler::collect() {
+    for (size_t q = 0; q < used; q++) {
+        cudaEventSynchronize(pool[q].b);
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, pool[q].a, pool[q].b) == cudaSuccess) ms[pool[q].kind] += t;
+    }
+    used = 0;
+}
+void Profiler::release() {
+    for (auto& p : pool) {
+        cudaEventDestroy(p.a);
+        cudaEventDestroy(p.b);
+    }
+    pool.clear();
+    used = 0;
 }
 
 cfd_status_t dalloc(cfd_b200_session* s, double** p) {
@@ -184,7 +202,7 @@ cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
     ok = ok && cudaMalloc((void**)&s->su_tab, d->ny * sizeof(double)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&s->sv_tab, d->nx * sizeof(double)) == cudaSuccess;
     if (ok) {
-        double** prim[] = {&s->u, &s->v, &s->w, &s->p, &s->T};
+        double** prim[] = {&s->u, &s->v, &s->w, &s->p};  // T and rho are allocated on first use
         for (auto pp : prim) ok = ok && dalloc(s, pp) == CFD_SUCCESS;
     }
     if (!ok) {
@@ -215,8 +233,7 @@ void cfd_b200_session_destroy(cfd_b200_session_t* s) {
     if (s->rb.ticket) cudaFree(s->rb.ticket);
     if (s->h_ctl) cudaFreeHost(s->h_ctl);
     for (auto& e : s->ev) if (e) cudaEventDestroy(e);
-    if (s->prof.e0) cudaEventDestroy(s->prof.e0);
-    if (s->prof.e1) cudaEventDestroy(s->prof.e1);
+    s->prof.release();
     if (s->nccl.comm && s->nccl.CommDestroy) s->nccl.CommDestroy(s->nccl.comm);
     if (s->st) cudaStreamDestroy(s->st);
     if (t_prof == &s->prof) t_prof = nullptr;
@@ -233,14 +250,20 @@ poisson_solver_stats_t cfd_b200_session_last_poisson_stats(const cfd_b200_sessio
     return s->last_ps;
 }
 
-void cfd_b200_session_profile(cfd_b200_session_t* s, int enable) { s->prof.on = enable != 0; }
+void cfd_b200_session_profile(cfd_b200_session_t* s, int enable) {
+    if (!enable && s->prof.on) s->prof.collect();
+    s->prof.on = enable != 0;
+}
 void cfd_b200_session_reset_kernel_stats(cfd_b200_session_t* s) {
+    s->prof.collect();
     for (int k = 0; k < KK_COUNT; k++) {
         s->prof.launches[k] = 0;
         s->prof.ms[k] = 0.0;
     }
 }
-int cfd_b200_session_kernel_stats(const cfd_b200_session_t* s, cfd_b200_kernel_stat_t* out, int max) {
+int cfd_b200_session_kernel_stats(const cfd_b200_session_t* cs, cfd_b200_kernel_stat_t* out, int max) {
+    cfd_b200_session_t* s = const_cast<cfd_b200_session_t*>(cs);
+    s->prof.collect();
     int n = 0;
     for (int k = 0; k < KK_COUNT && n < max; k++) {
         if (!s->prof.launches[k]) continue;

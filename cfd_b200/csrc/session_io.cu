@@ -26,6 +26,10 @@ cfd_status_t session_upload(cfd_b200_session* s, const flow_field* f, int mask) 
         cfd_status_t rc = dalloc(s, &s->rho);
         if (rc != CFD_SUCCESS) return rc;
     }
+    if ((mask & FM_T) && !s->T) {
+        cfd_status_t rc = dalloc(s, &s->T);
+        if (rc != CFD_SUCCESS) return rc;
+    }
     double* dv[6];
     field_ptrs(s, dv);
     const double* hv[6] = {f->u, f->v, f->w, f->p, f->rho, f->T};

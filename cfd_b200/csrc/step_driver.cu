@@ -94,6 +94,8 @@ cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
         if ((rc = dalloc(s, q)) != CFD_SUCCESS) return rc;
     if (pc->method == POISSON_METHOD_JACOBI && (rc = dalloc(s, &s->xt)) != CFD_SUCCESS) return rc;
     const bool energy = prm->alpha > 0.0;
+    const bool thermo = energy || prm->beta != 0.0;
+    if (thermo && (rc = dalloc(s, &s->T)) != CFD_SUCCESS) return rc;  // (zeros unless uploaded)
     if (energy && (rc = dalloc(s, &s->Tn)) != CFD_SUCCESS) return rc;
     if ((rc = ensure_tables(s, prm)) != CFD_SUCCESS) return rc;
     NsConst c = make_const(s, prm);
@@ -104,7 +106,7 @@ cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
         c.src_decay = exp(-prm->source_decay_rate * iter * prm->dt);
         if (R > 1) {
             double* f[4] = {s->u, s->v, s->w, s->T};
-            halo_exchange(s, f, 4, false);
+            halo_exchange(s, f, thermo ? 4 : 3, false);
         }
         launch_predictor(L, c, s->u, s->v, s->w, s->T, s->su_tab, s->sv_tab, s->us, s->vs, s->ws);
         if (R > 1) {
@@ -162,11 +164,12 @@ cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* pr
     const int nbuf = (order == 4) ? 12 : 8;  // B[4], (C[4]), ACC[4]
     for (int q = 0; q < nbuf; q++)
         if ((rc = dalloc(s, &s->rk[q])) != CFD_SUCCESS) return rc;
-    if (!s->rho) {
-        set_error(CFD_ERROR_INVALID, "RK steppers need the density field on the device (upload with rho)");
-        return CFD_ERROR_INVALID;
+    if (!s->rho) {  // session extension: no density uploaded => rho = 1 everywhere
+        if ((rc = dalloc(s, &s->rho)) != CFD_SUCCESS) return rc;
+        launch_fill(s->L(), s->rho, 1.0, s->N);
     }
     const bool energy = prm->alpha > 0.0;
+    if ((energy || prm->beta != 0.0) && (rc = dalloc(s, &s->T)) != CFD_SUCCESS) return rc;
     if (energy && (rc = dalloc(s, &s->Tn)) != CFD_SUCCESS) return rc;
     if ((rc = ensure_tables(s, prm)) != CFD_SUCCESS) return rc;
     NsConst c = make_const(s, prm);
@@ -219,9 +222,10 @@ cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* pr
             std::swap(s->T, s->Tn);
         }
         // apply_boundary_conditions: periodic wrap of u,v,w,p,rho,T (solver_explicit_euler.c:231-314)
-        double* all[6] = {s->u, s->v, s->w, s->p, s->T, s->rho};
-        for (double* f : all) launch_periodic_bc(L, f, wrap_y, wrap_z);
-        if (R > 1) halo_exchange(s, all, 6, true);
+        double* all[6] = {s->u, s->v, s->w, s->p, s->rho, s->T};
+        const int nall = s->T ? 6 : 5;  // a T that never reached the device stays on the host untouched
+        for (int q = 0; q < nall; q++) launch_periodic_bc(L, all[q], wrap_y, wrap_z);
+        if (R > 1) halo_exchange(s, all, nall, true);
         if (energy) launch_thermal_bc(s->L(), prm->thermal_bc, s->T);
         int bad = 0;
         if ((rc = read_flags(s, &bad)) != CFD_SUCCESS) return rc;

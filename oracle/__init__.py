@@ -30,10 +30,20 @@ class Oracle:
 
     def __init__(self, variant=""):
         """variant "ld": Krylov dot products accumulated in long double (sensitivity probe)."""
-        path = os.path.join(HERE, "liboracle%s.so" % (("_" + variant) if variant else ""))
-        if not os.path.exists(path):
-            build()
+        if variant == "ref":
+            # timed CPU baseline: OpenMP stencil loops + the reference's own Poisson solver objects
+            path = os.path.join(HERE, "_ref", "liboracle_ref.so")
+            if not os.path.exists(path):
+                raise FileNotFoundError(path + " (run `make -C oracle ref` where /root/reference exists)")
+        else:
+            path = os.path.join(HERE, "liboracle%s.so" % (("_" + variant) if variant else ""))
+            if not os.path.exists(path):
+                build()
         L = self.lib = C.CDLL(path)
+        if variant == "ref":
+            L.orc_set_ref_backend.argtypes = [C.c_int]
+            L.orc_ref_backend_available.argtypes = [C.c_int, C.c_int]
+            L.orc_ref_backend_available.restype = C.c_int
         L.orc_projection.restype = C.c_int
         L.orc_projection.argtypes = [C.POINTER(abi.FlowField), C.POINTER(abi.Grid),
                                      C.POINTER(abi.NSSolverParams), C.POINTER(abi.PoissonConfig),

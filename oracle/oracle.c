@@ -54,6 +54,20 @@ static geo_t make_geo(size_t nx, size_t ny, size_t nz, double dx, double dy, dou
         for (size_t j = 1; j < (g).ny - 1; j++)                         \
             for (size_t i = 1, idx = k * (g).sz + j * (g).nx + 1; i < (g).nx - 1; i++, idx++)
 
+/* Loops without cross-cell dependencies (predictor, divergence, corrector, energy, RK RHS) use
+ * FOR_INTERIOR_PAR: identical to FOR_INTERIOR in the scalar build (liboracle.so, no -fopenmp);
+ * in the timed multi-threaded baseline build (_ref/liboracle_ref.so) it is the reference's own
+ * OpenMP structure (solver_projection_omp.c:93-160: parallel for over the outer loops). */
+#ifdef _OPENMP
+#define FOR_INTERIOR_PAR(g, i, j, k, idx)                               \
+    _Pragma("omp parallel for collapse(2) schedule(static)")            \
+    for (size_t k = (g).k0; k < (g).k1; k++)                            \
+        for (size_t j = 1; j < (g).ny - 1; j++)                         \
+            for (size_t i = 1, idx = k * (g).sz + j * (g).nx + 1; i < (g).nx - 1; i++, idx++)
+#else
+#define FOR_INTERIOR_PAR FOR_INTERIOR
+#endif
+
 /* ======================================================================
  * Boundary helpers
  * ====================================================================== */
@@ -214,7 +228,7 @@ static int energy_step(flow_field* f, const geo_t* g, const ns_solver_params_t* 
     const double* T = f->T;
     size_t nx = g->nx, sz = g->sz;
     memcpy(ws, T, g->total * sizeof(double));
-    FOR_INTERIOR(*g, i, j, k, n) {
+    FOR_INTERIOR_PAR(*g, i, j, k, n) {
         double Tc = T[n];
         double dTdx = (T[n + 1] - T[n - 1]) * inv_2dx;
         double dTdy = (T[n + nx] - T[n - nx]) * inv_2dy;
@@ -532,9 +546,51 @@ done:
 
 /* poisson_solver_solve() equivalent for the scalar backend -- linear_solver.c:487-509.
  * x_temp may be NULL unless method is Jacobi. */
+#ifdef ORC_REF_POISSON
+/* Timed-baseline build only (_ref/liboracle_ref.so, linked against _ref/libcfd_ref_fast.so):
+ * the pressure solve is the REFERENCE's own solver object, created through its public API
+ * (poisson_solver.h) with the backend chosen by orc_set_ref_backend(); the stencil loops above
+ * stay the restated ones.  Lets bench.py time "projection step with method M" on the CPU
+ * although the reference hard-codes CG inside solve_projection_method. */
+extern poisson_solver_t* poisson_solver_create(poisson_solver_method_t, poisson_solver_backend_t);
+extern cfd_status_t poisson_solver_init(poisson_solver_t*, size_t, size_t, size_t, double, double,
+                                        double, const poisson_solver_params_t*);
+extern cfd_status_t poisson_solver_solve(poisson_solver_t*, double*, double*, const double*,
+                                         poisson_solver_stats_t*);
+extern void poisson_solver_destroy(poisson_solver_t*);
+static int g_ref_backend = POISSON_BACKEND_SCALAR;
+static poisson_solver_t* g_ref_solver = NULL;
+static int g_ref_key_method = -1, g_ref_key_backend = -1;
+static poisson_solver_params_t g_ref_key_params;
+ORC_API void orc_set_ref_backend(int backend) { g_ref_backend = backend; }
+ORC_API int orc_ref_backend_available(int method, int backend) {
+    poisson_solver_t* s = poisson_solver_create((poisson_solver_method_t)method,
+                                                (poisson_solver_backend_t)backend);
+    if (!s) return 0;
+    poisson_solver_destroy(s);
+    return 1;
+}
+#endif
+
 ORC_API int orc_poisson_solve(int method, size_t nx, size_t ny, size_t nz, double dx, double dy,
                               double dz, const poisson_solver_params_t* prm, double* x,
                               double* x_temp, const double* rhs, poisson_solver_stats_t* stats) {
+#ifdef ORC_REF_POISSON
+    if (!g_ref_solver || g_ref_key_method != method || g_ref_key_backend != g_ref_backend ||
+        g_ref_solver->nx != nx || g_ref_solver->ny != ny || g_ref_solver->nz != nz ||
+        memcmp(&g_ref_key_params, prm, sizeof(*prm)) != 0) {
+        if (g_ref_solver) poisson_solver_destroy(g_ref_solver);
+        g_ref_solver = poisson_solver_create((poisson_solver_method_t)method,
+                                             (poisson_solver_backend_t)g_ref_backend);
+        if (!g_ref_solver) return CFD_ERROR_UNSUPPORTED;
+        cfd_status_t irc = poisson_solver_init(g_ref_solver, nx, ny, nz, dx, dy, dz, prm);
+        if (irc != CFD_SUCCESS) return irc;
+        g_ref_key_method = method;
+        g_ref_key_backend = g_ref_backend;
+        g_ref_key_params = *prm;
+    }
+    return poisson_solver_solve(g_ref_solver, x, x_temp, rhs, stats);
+#endif
     poisson_solver_stats_t local;
     poisson_solver_stats_t* st = stats ? stats : &local;
     st->status = POISSON_ERROR;
@@ -582,7 +638,7 @@ ORC_API int orc_projection(flow_field* f, const grid* gr, const ns_solver_params
     const double *u = f->u, *v = f->v, *w = f->w;
     for (int iter = 0; iter < nsteps; iter++) {
         /* predictor :116-185 */
-        FOR_INTERIOR(g, i, j, k, n) {
+        FOR_INTERIOR_PAR(g, i, j, k, n) {
             double uc = u[n], vc = v[n], wc = w[n];
             double du_dx = (u[n + 1] - u[n - 1]) / (2.0 * dx);
             double du_dy = (u[n + nx] - u[n - nx]) / (2.0 * dy);
@@ -618,7 +674,7 @@ ORC_API int orc_projection(flow_field* f, const grid* gr, const ns_solver_params
         /* divergence -> rhs :195-214 */
         double rho = f->rho[0];
         if (rho < 1e-10) rho = 1.0;
-        FOR_INTERIOR(g, i, j, k, n) {
+        FOR_INTERIOR_PAR(g, i, j, k, n) {
             double a = (us[n + 1] - us[n - 1]) / (2.0 * dx);
             double b = (vs[n + nx] - vs[n - nx]) / (2.0 * dy);
             double c = (ws[n + sz] - ws[n - sz]) * g.inv_2dz;
@@ -637,7 +693,7 @@ ORC_API int orc_projection(flow_field* f, const grid* gr, const ns_solver_params
         }
         /* corrector :230-250 */
         double dtr = dt / rho;
-        FOR_INTERIOR(g, i, j, k, n) {
+        FOR_INTERIOR_PAR(g, i, j, k, n) {
             double px = (pn[n + 1] - pn[n - 1]) / (2.0 * dx);
             double py = (pn[n + nx] - pn[n - nx]) / (2.0 * dy);
             double pz = (pn[n + sz] - pn[n - sz]) * g.inv_2dz;
@@ -671,7 +727,7 @@ static void rk_rhs(const flow_field* f, const grid* gr, const geo_t* g,
                    double* kw, double* kp) {
     const double *u = f->u, *v = f->v, *w = f->w, *p = f->p, *rho = f->rho, *T = f->T;
     size_t nx = g->nx, ny = g->ny, nz = g->nz, sz = g->sz;
-    FOR_INTERIOR(*g, i, j, k, n) {
+    FOR_INTERIOR_PAR(*g, i, j, k, n) {
         if (rho[n] <= 1e-10 || fabs(gr->dx[i]) < 1e-10 || fabs(gr->dy[j]) < 1e-10) {
             ku[n] = kv[n] = kw[n] = kp[n] = 0.0;
             continue;
