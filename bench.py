@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--cpu-n", type=int, default=0, help="box edge of the CPU sample (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--budget", type=float, default=150.0, help="seconds of CPU work allowed to --impl reference")
     return ap.parse_args()
 
 
@@ -203,7 +204,7 @@ def reference_main(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    r = cpu_arm(a.method, a.iters, a.steps, a.warmup, budget_s=150.0, n_force=a.cpu_n)
+    r = cpu_arm(a.method, a.iters, a.steps, a.warmup, budget_s=a.budget, n_force=a.cpu_n)
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": a.gpus,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -417,9 +418,9 @@ def e2e_arm(a, r):
 
 def main():
     a = parse()
-    os.environ.setdefault("OMP_NUM_THREADS", str(host_cores()))
-    os.environ.setdefault("OMP_PROC_BIND", "close")
     if a.impl == "reference":
+        # all host cores for the reference's OpenMP / AVX2 backends (set before libgomp loads)
+        os.environ.setdefault("OMP_NUM_THREADS", str(host_cores()))
         return reference_main(a)
     r = ours_main(a)
     e2e = None
@@ -430,8 +431,15 @@ def main():
             e2e = {"value": None, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0, "note": str(ex)}
     cpu = None
     if r["rank"] == 0 and r["world"] == 1 and not a.no_cpu:
-        c = cpu_arm(a.method, a.iters, steps=1, warmup=1, budget_s=24.0, n_force=a.cpu_n)
-        cpu = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        # a fresh process: torch's OpenMP runtime and thread affinity stay out of the CPU measurement
+        cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "1", "--warmup", "1",
+               "--budget", "24", "--method", a.method, "--iters", str(a.iters), "--cpu-n", str(a.cpu_n)]
+        env = {k: v for k, v in os.environ.items() if not k.startswith("OMP_")}
+        out = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600)
+        try:
+            cpu = json.loads(out.stdout.strip().splitlines()[-1])["cpu_baseline"]
+        except Exception:
+            cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "failed: " + out.stderr[-300:]}
     if r["rank"] == 0:
         n, world = r["n"], r["world"]
         line = {"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": a.steps,

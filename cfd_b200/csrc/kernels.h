@@ -3,9 +3,20 @@
 #include "common.cuh"
 #include "ns_args.h"
 
+#include <cuda.h>
+#include <unordered_map>
 #include <vector>
 
 namespace cfdb {
+
+// Tensor maps of a session's device arrays for the TMA kernels (tma_host.cu).
+struct TmaCache {
+    int nx = 0, ny = 0, nz = 0;
+    bool usable = false;
+    std::unordered_map<const double*, CUtensorMap> maps;
+    void configure(const Geom& g);
+    const CUtensorMap* get(const double* p);   // nullptr => take the direct (non-TMA) kernel
+};
 
 // Everything a launcher needs besides the per-kernel operands.
 struct LaunchCtx {
@@ -14,6 +25,8 @@ struct LaunchCtx {
     Ctl* ctl;       // device
     RedBuf rb;      // device
     int zchunk;     // planes marched per block
+    TmaCache* tc;   // may be null
+    int zchunk_tma; // planes marched per block of the TMA kernels
     dim3 grid() const;   // tile grid over (nx, ny, z-chunks)
 };
 

@@ -13,6 +13,7 @@
 // floating-point atomics anywhere inside an iteration.
 #include "common.cuh"
 #include "kernels.h"
+#include "tma.cuh"
 
 #include <limits.h>
 
@@ -308,7 +309,13 @@ __device__ __forceinline__ void comb_matvec(const Geom& g, const KArgs& a, const
 
 // ---- CG -------------------------------------------------------------------------------
 struct CgDirOp {
-    static constexpr int NV = 1;
+    static constexpr int NV = 1, NS = 2;   // TMA operands: r, pold
+    __device__ __forceinline__ double combv(const double (&q)[2]) const {
+        if (first) return q[1];
+        return (precond ? dinv * q[0] : q[0]) + beta * q[1];
+    }
+    __device__ __forceinline__ double pw(long long) const { return 0.0; }
+    __device__ __forceinline__ void dotsv(double, double c, double Ac, double (&acc)[1]) const { acc[0] += c * Ac; }
     const double* r;
     const double* pold;
     double beta, dinv;
@@ -326,16 +333,13 @@ struct CgDirOp {
 
 // Start of CG iteration `it`: convergence / breakdown decisions of iteration it-1
 // (linear_solver_cg.c:397-415), then p = z + beta p, Ap = A p, p.Ap.
-template <bool D3>
-__global__ void __launch_bounds__(TX* TY)
-k_cg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold,
-         double* __restrict__ pnew, double* __restrict__ Ap, Ctl* ctl, RedBuf rb, KArgs a,
-         int precond, int decide_only) {
-    if (a.seq > ctl->done_seq) return;
+// Decisions at the start of CG iteration a.it; false => the kernel must not run.
+__device__ __forceinline__ bool cg_dir_prologue(Ctl* ctl, const KArgs& a, int precond, double& beta) {
+    if (a.seq > ctl->done_seq) return false;
     const int it = a.it, par = it & 1;
     const double rr = ctl->dot[2 * par], rho_new = ctl->dot[2 * par + precond];
     const double res = sqrt(rr);
-    double beta = 0.0;
+    beta = 0.0;
     if (it == 0) {
         const double tol = fmax(a.rel_tol * res, a.abs_tol);
         if (leader()) {
@@ -344,7 +348,7 @@ k_cg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold,
         }
         if (res < a.abs_tol) {
             finish(ctl, a, POISSON_CONVERGED, 0, res, 1, 0);
-            return;
+            return false;
         }
     } else {
         const double tol = ctl->tol;
@@ -352,20 +356,30 @@ k_cg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold,
         const bool conv = (res < tol || res < a.abs_tol);
         if (((it - 1) % a.check) == 0 && conv) {
             finish(ctl, a, POISSON_CONVERGED, it, res, 0, 0);
-            return;
+            return false;
         }
         if (fabs(rho_old) < 1e-30) {
             finish(ctl, a, POISSON_STAGNATED, it, res, 1, 0);
-            return;
+            return false;
         }
         if (it >= a.max_iter) {
             finish(ctl, a, conv ? POISSON_CONVERGED : POISSON_MAX_ITER, a.max_iter, res, 0, 0);
-            return;
+            return false;
         }
         beta = rho_new / rho_old;
     }
-    if (decide_only) return;
-    CgDirOp op{r, pold, beta, a.dinv, it == 0, precond};
+    return true;
+}
+
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_cg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold,
+         double* __restrict__ pnew, double* __restrict__ Ap, Ctl* ctl, RedBuf rb, KArgs a,
+         int precond, int decide_only) {
+    double beta;
+    if (!cg_dir_prologue(ctl, a, precond, beta) || decide_only) return;
+    const int par = a.it & 1;
+    CgDirOp op{r, pold, beta, a.dinv, a.it == 0, precond};
     double acc[1] = {0.0};
     comb_matvec<D3>(g, a, op, pnew, Ap, acc);
     block_reduce_finish<1, false>(acc, rb, &ctl->dot[4 + par]);
@@ -402,7 +416,13 @@ k_cg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const double
 
 // ---- BiCGSTAB -------------------------------------------------------------------------
 struct BiDirOp {  // p = r + beta (p - omega v) ; v = A p ; rhat.v
-    static constexpr int NV = 1;
+    static constexpr int NV = 1, NS = 3;   // TMA operands: r, pold, vold
+    __device__ __forceinline__ double combv(const double (&q)[3]) const {
+        if (first) return q[0];
+        return q[0] + beta * (q[1] - omega * q[2]);
+    }
+    __device__ __forceinline__ double pw(long long n) const { return __ldg(rhat + n); }
+    __device__ __forceinline__ void dotsv(double rh, double, double Ac, double (&acc)[1]) const { acc[0] += rh * Ac; }
     const double *r, *pold, *vold, *rhat;
     double beta, omega;
     int first;  // iteration 0: p = v = 0 (linear_solver_bicgstab.c:307-308) without reading them
@@ -416,7 +436,14 @@ struct BiDirOp {  // p = r + beta (p - omega v) ; v = A p ; rhat.v
     }
 };
 struct BiSOp {  // s = r - alpha v ; t = A s ; s.s, t.s, t.t
-    static constexpr int NV = 3;
+    static constexpr int NV = 3, NS = 2;   // TMA operands: r, v
+    __device__ __forceinline__ double combv(const double (&q)[2]) const { return q[0] - alpha * q[1]; }
+    __device__ __forceinline__ double pw(long long) const { return 0.0; }
+    __device__ __forceinline__ void dotsv(double, double c, double Ac, double (&acc)[3]) const {
+        acc[0] += c * c;
+        acc[1] += Ac * c;
+        acc[2] += Ac * Ac;
+    }
     const double *r, *v;
     double alpha;
     __device__ __forceinline__ double comb(long long n) const {
@@ -439,17 +466,12 @@ __device__ __forceinline__ double bi_omega(const Ctl* ctl, int it) {
 
 // Start of iteration `it` (linear_solver_bicgstab.c:338-370 preceded by the tail checks :451-474
 // of iteration it-1).
-template <bool D3>
-__global__ void __launch_bounds__(TX* TY)
-k_bicg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold,
-           const double* __restrict__ vold, const double* __restrict__ rhat,
-           double* __restrict__ pnew, double* __restrict__ vnew, Ctl* ctl, RedBuf rb, KArgs a,
-           int decide_only) {
-    if (a.seq > ctl->done_seq) return;
+__device__ __forceinline__ bool bicg_dir_prologue(Ctl* ctl, const KArgs& a, double& beta, double& omega_old) {
+    if (a.seq > ctl->done_seq) return false;
     const int it = a.it, par = it & 1;
     const double res = sqrt(ctl->dot[2 * par]);
     const double rho_new = ctl->dot[2 * par + 1];
-    double beta, omega_old = 1.0;
+    omega_old = 1.0;
     if (it == 0) {
         const double tol = fmax(a.rel_tol * res, a.abs_tol);
         if (leader()) {
@@ -458,11 +480,11 @@ k_bicg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold
         }
         if (res < a.abs_tol) {
             finish(ctl, a, POISSON_CONVERGED, 0, res, 1, 0);
-            return;
+            return false;
         }
         if (fabs(rho_new) < 1e-30) {
             finish(ctl, a, POISSON_STAGNATED, 1, res, 1, 0);
-            return;
+            return false;
         }
         beta = rho_new;  // (rho_new / 1) * (1 / 1)
     } else {
@@ -470,46 +492,63 @@ k_bicg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold
         const bool conv = (res < tol || res < a.abs_tol);
         if (((it - 1) % a.check) == 0 && conv) {
             finish(ctl, a, POISSON_CONVERGED, it, res, 0, 0);
-            return;
+            return false;
         }
         omega_old = bi_omega(ctl, it - 1);
         if (fabs(omega_old) < 1e-30) {
             finish(ctl, a, POISSON_STAGNATED, it, res, 1, 0);
-            return;
+            return false;
         }
         if (it >= a.max_iter) {
             finish(ctl, a, conv ? POISSON_CONVERGED : POISSON_MAX_ITER, a.max_iter, res, 0, 0);
-            return;
+            return false;
         }
         if (fabs(rho_new) < 1e-30) {
             finish(ctl, a, POISSON_STAGNATED, it + 1, res, 1, 0);
-            return;
+            return false;
         }
         const double rho_old = ctl->dot[2 * (par ^ 1) + 1];
         beta = (rho_new / rho_old) * (bi_alpha(ctl, it - 1) / omega_old);
     }
-    if (decide_only) return;
-    BiDirOp op{r, pold, vold, rhat, beta, omega_old, it == 0};
+    return true;
+}
+
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_bicg_dir(Geom g, const double* __restrict__ r, const double* __restrict__ pold,
+           const double* __restrict__ vold, const double* __restrict__ rhat,
+           double* __restrict__ pnew, double* __restrict__ vnew, Ctl* ctl, RedBuf rb, KArgs a,
+           int decide_only) {
+    double beta, omega_old;
+    if (!bicg_dir_prologue(ctl, a, beta, omega_old) || decide_only) return;
+    BiDirOp op{r, pold, vold, rhat, beta, omega_old, a.it == 0};
     double acc[1] = {0.0};
     comb_matvec<D3>(g, a, op, pnew, vnew, acc);
-    block_reduce_finish<1, false>(acc, rb, &ctl->dot[4 + par]);
+    block_reduce_finish<1, false>(acc, rb, &ctl->dot[4 + (a.it & 1)]);
+}
+
+__device__ __forceinline__ bool bicg_s_prologue(Ctl* ctl, const KArgs& a, double& alpha) {
+    if (a.seq > ctl->done_seq) return false;
+    const int par = a.it & 1;
+    const double rhv = ctl->dot[4 + par];
+    if (fabs(rhv) < 1e-30) {
+        finish(ctl, a, POISSON_STAGNATED, a.it + 1, a.it == 0 ? ctl->r0 : sqrt(ctl->dot[2 * par]), 1, 0);
+        return false;
+    }
+    alpha = ctl->dot[2 * par + 1] / rhv;
+    return true;
 }
 
 template <bool D3>
 __global__ void __launch_bounds__(TX* TY)
 k_bicg_s(Geom g, const double* __restrict__ r, const double* __restrict__ v,
          double* __restrict__ s, double* __restrict__ t, Ctl* ctl, RedBuf rb, KArgs a) {
-    if (a.seq > ctl->done_seq) return;
-    const int par = a.it & 1;
-    const double rhv = ctl->dot[4 + par];
-    if (fabs(rhv) < 1e-30) {
-        finish(ctl, a, POISSON_STAGNATED, a.it + 1, a.it == 0 ? ctl->r0 : sqrt(ctl->dot[2 * par]), 1, 0);
-        return;
-    }
-    BiSOp op{r, v, ctl->dot[2 * par + 1] / rhv};
+    double alpha;
+    if (!bicg_s_prologue(ctl, a, alpha)) return;
+    BiSOp op{r, v, alpha};
     double acc[3] = {0.0, 0.0, 0.0};
     comb_matvec<D3>(g, a, op, s, t, acc);
-    block_reduce_finish<3, false>(acc, rb, &ctl->dot[8 + 4 * par]);
+    block_reduce_finish<3, false>(acc, rb, &ctl->dot[8 + 4 * (a.it & 1)]);
 }
 
 // Tail of the iteration (:396-451): early exit on ||s||, omega, x and r updates, r.r and rhat.r.
@@ -554,6 +593,8 @@ k_bicg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const doub
     if (mode == 0) block_reduce_finish<2, false>(acc, rb, &ctl->dot[2 * (par ^ 1)]);
 }
 
+
+#include "poisson_tma.inc"
 
 // =======================================================================================
 // Host launchers
@@ -603,6 +644,20 @@ void launch_krylov_init(const LaunchCtx& L, const KArgs& a0, const double* x, co
 }
 void launch_cg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const double* pold, double* pnew,
                    double* Ap, int precond, int decide_only) {
+    if (!decide_only) {
+        TmaSet<2> tm;
+        const double* const ops[2] = {r, pold};
+        if (tma_maps(L, ops, tm)) {
+            KArgs a = a0;
+            a.zchunk = L.zchunk_tma;
+            constexpr size_t SM = TmaPipe<2>::SMEM;
+            static bool once = (tma_optin(k_cg_dir_tma<true>, SM), tma_optin(k_cg_dir_tma<false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_CG_DIR, L.st, (k_cg_dir_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, pnew, Ap, L.ctl, L.rb, a, precond)));
+            else CFDB_LAUNCH(KK_CG_DIR, L.st, (k_cg_dir_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, pnew, Ap, L.ctl, L.rb, a, precond)));
+            return;
+        }
+    }
     const KArgs a = with_chunk(L, a0);
     const dim3 gr = decide_only ? dim3(1, 1, 1) : L.grid();
     if (L.g.dim3) CFDB_LAUNCH(KK_CG_DIR, L.st, k_cg_dir<true><<<gr, blk(), 0, L.st>>>(L.g, r, pold, pnew, Ap, L.ctl, L.rb, a, precond, decide_only));
@@ -618,12 +673,40 @@ void launch_bicg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const
                      const double* vold, const double* rhat, double* pnew, double* vnew, int first,
                      int decide_only) {
     (void)first;
+    if (!decide_only) {
+        TmaSet<3> tm;
+        const double* const ops[3] = {r, pold, vold};
+        if (tma_maps(L, ops, tm)) {
+            KArgs a = a0;
+            a.zchunk = L.zchunk_tma;
+            constexpr size_t SM = TmaPipe<3>::SMEM;
+            static bool once = (tma_optin(k_bicg_dir_tma<true>, SM), tma_optin(k_bicg_dir_tma<false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_BICG_DIR, L.st, (k_bicg_dir_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhat, pnew, vnew, L.ctl, L.rb, a)));
+            else CFDB_LAUNCH(KK_BICG_DIR, L.st, (k_bicg_dir_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhat, pnew, vnew, L.ctl, L.rb, a)));
+            return;
+        }
+    }
     const KArgs a = with_chunk(L, a0);
     const dim3 gr = decide_only ? dim3(1, 1, 1) : L.grid();
     if (L.g.dim3) CFDB_LAUNCH(KK_BICG_DIR, L.st, k_bicg_dir<true><<<gr, blk(), 0, L.st>>>(L.g, r, pold, vold, rhat, pnew, vnew, L.ctl, L.rb, a, decide_only));
     else CFDB_LAUNCH(KK_BICG_DIR, L.st, k_bicg_dir<false><<<gr, blk(), 0, L.st>>>(L.g, r, pold, vold, rhat, pnew, vnew, L.ctl, L.rb, a, decide_only));
 }
 void launch_bicg_s(const LaunchCtx& L, const KArgs& a0, const double* r, const double* v, double* s, double* t) {
+    {
+        TmaSet<2> tm;
+        const double* const ops[2] = {r, v};
+        if (tma_maps(L, ops, tm)) {
+            KArgs a = a0;
+            a.zchunk = L.zchunk_tma;
+            constexpr size_t SM = TmaPipe<2>::SMEM;
+            static bool once = (tma_optin(k_bicg_s_tma<true>, SM), tma_optin(k_bicg_s_tma<false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_BICG_S, L.st, (k_bicg_s_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, s, t, L.ctl, L.rb, a)));
+            else CFDB_LAUNCH(KK_BICG_S, L.st, (k_bicg_s_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, s, t, L.ctl, L.rb, a)));
+            return;
+        }
+    }
     const KArgs a = with_chunk(L, a0);
     if (L.g.dim3) CFDB_LAUNCH(KK_BICG_S, L.st, k_bicg_s<true><<<L.grid(), blk(), 0, L.st>>>(L.g, r, v, s, t, L.ctl, L.rb, a));
     else CFDB_LAUNCH(KK_BICG_S, L.st, k_bicg_s<false><<<L.grid(), blk(), 0, L.st>>>(L.g, r, v, s, t, L.ctl, L.rb, a));

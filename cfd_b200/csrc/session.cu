@@ -1,5 +1,6 @@
 // session.cu -- session lifecycle, host<->device movement, NCCL plumbing, globals.
 #include "session.h"
+#include "tma.cuh"
 
 #include <dlfcn.h>
 #include <limits.h>
@@ -190,6 +191,14 @@ cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
         const long long nchunks = (nzi + s->zchunk - 1) / s->zchunk;
         s->rb_blocks = (size_t)(tiles * nchunks);
         if (s->rb_blocks < 148 * 16) s->rb_blocks = 148 * 16;
+        // TMA kernels: 64x16 tiles, 2 blocks per SM; aim at >= 8 waves but keep chunks >= 32 planes
+        // (each chunk re-reads 2 planes in its prologue)
+        const long long ttiles = (long long)((s->g.nx - 2 + Tile::BX - 1) / Tile::BX) * ((s->g.ny - 2 + Tile::BY - 1) / Tile::BY);
+        long long nch = (148LL * 2 * 8 + ttiles - 1) / ttiles;
+        if (nch > nzi / 32) nch = nzi / 32;
+        if (nch < 1) nch = 1;
+        s->zchunk_tma = (int)((nzi + nch - 1) / nch);
+        s->tma.configure(s->g);
     }
     ok = ok && cudaMalloc((void**)&s->ctl, sizeof(Ctl)) == cudaSuccess;
     ok = ok && cudaMemset(s->ctl, 0, sizeof(Ctl)) == cudaSuccess;

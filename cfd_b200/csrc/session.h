@@ -54,6 +54,8 @@ struct cfd_b200_session {
     size_t rb_blocks = 0;
     int zchunk = 1;
     cfdb::Profiler prof;
+    cfdb::TmaCache tma;
+    int zchunk_tma = 1;
     cfdb::Nccl nccl;
     poisson_solver_stats_t last_ps = {};
     size_t bytes_allocated = 0;
@@ -66,6 +68,8 @@ struct cfd_b200_session {
         l.ctl = ctl;
         l.rb = rb;
         l.zchunk = zchunk;
+        l.tc = const_cast<cfdb::TmaCache*>(&tma);
+        l.zchunk_tma = zchunk_tma;
         return l;
     }
 };

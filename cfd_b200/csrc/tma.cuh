@@ -1,0 +1,85 @@
+// tma.cuh -- Blackwell TMA (cp.async.bulk.tensor) + mbarrier plumbing of the plane-pipelined
+// stencil kernels (sm_100a).
+//
+// Every stencil operand is described to the TMA unit as a rank-3 FP64 tensor {nx, ny, nz}
+// (x fastest, the reference layout of cfd/core/indexing.h:17-20).  A block owns a BX x BY tile
+// of interior cells and marches along z; for each plane it needs the tile plus a one-cell halo,
+// i.e. a {BX+2, BY+2, 1} box, which one elected thread requests with a single instruction per
+// operand.  Out-of-bounds parts of a box (tiles on the domain edge) are zero-filled by the
+// hardware, so the kernels carry no edge branches on the load side.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cfdb {
+
+struct Tile {
+    static constexpr int BX = 64, BY = 16;            // interior cells per block and plane
+    static constexpr int HX = BX + 2, HY = BY + 2;    // box with halo
+    static constexpr int PLANE = HX * HY;             // doubles per operand plane (1188)
+    static constexpr int PLANE_PAD = 1200;            // padded so every plane starts 128-B aligned
+    static constexpr int PLANE_BYTES = PLANE * 8;     // bytes the TMA delivers per operand plane
+    static constexpr int THREADS = 512;               // 2 cells per thread: rows ly and ly + 8
+    __host__ __device__ static constexpr int OWN0(int lx, int ly) { return (ly + 1) * HX + lx + 1; }
+};
+static_assert((Tile::HX * 8) % 16 == 0, "TMA box rows must be a multiple of 16 bytes");
+static_assert((Tile::PLANE_PAD * 8) % 128 == 0, "TMA destinations must stay 128-byte aligned");
+
+// Up to 4 tensor maps by value in kernel parameter space (must be __grid_constant__).
+template <int N>
+struct TmaSet {
+    CUtensorMap m[N];
+};
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+// make the barrier initialisation visible to the async (TMA) proxy
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// generic-proxy reads of a stage are finished (ordered by the preceding __syncthreads); order
+// them before the async-proxy write that refills the stage
+__device__ __forceinline__ void fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+// one {HX, HY, 1} box of `map` at (x0, y0, z) -> smem dst; completion counted in bytes on bar
+__device__ __forceinline__ void tma_load_plane(void* dst, const CUtensorMap* map, int x0, int y0, int z,
+                                               uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(dst)),
+        "l"(map), "r"(x0), "r"(y0), "r"(z), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
+#endif  // __CUDACC__
+
+}  // namespace cfdb

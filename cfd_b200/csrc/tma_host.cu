@@ -1,0 +1,54 @@
+// tma_host.cu -- host side of the TMA path: tensor-map creation (cuTensorMapEncodeTiled, reached
+// through cudaGetDriverEntryPoint so the library does not link libcuda) and a per-session cache
+// keyed by device pointer (the arrays of a session are few and long-lived).
+#include "kernels.h"
+#include "tma.cuh"
+
+#include <cudaTypedefs.h>
+
+namespace cfdb {
+
+static PFN_cuTensorMapEncodeTiled encode_fn() {
+    static PFN_cuTensorMapEncodeTiled fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (PFN_cuTensorMapEncodeTiled)p;
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
+
+void TmaCache::configure(const Geom& g) {
+    nx = g.nx; ny = g.ny; nz = g.nz;
+    maps.clear();
+    // TMA needs 16-byte global strides: nx even (the odd-nx grids, e.g. 129^2, take the direct kernels)
+    usable = (nx % 2 == 0) && nx >= 4 && encode_fn() != nullptr && !getenv("CFD_B200_NO_TMA");
+}
+
+const CUtensorMap* TmaCache::get(const double* p) {
+    if (!usable || !p) return nullptr;
+    auto it = maps.find(p);
+    if (it != maps.end()) return &it->second;
+    if (((uintptr_t)p & 15) != 0) return nullptr;
+    CUtensorMap m;
+    const cuuint64_t dims[3] = {(cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)nz};
+    const cuuint64_t strides[2] = {(cuuint64_t)nx * 8, (cuuint64_t)nx * ny * 8};
+    const cuuint32_t box[3] = {(cuuint32_t)Tile::HX, (cuuint32_t)Tile::HY, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, (void*)p, dims, strides, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        usable = false;  // never retry: every later launch takes the direct kernels
+        return nullptr;
+    }
+    return &maps.emplace(p, m).first->second;
+}
+
+}  // namespace cfdb
