@@ -83,17 +83,17 @@ k_predictor(Geom g, NsConst c, int zchunk, const double* __restrict__ u, const d
         const double we = w[n + 1], ww = w[n - 1], wn = w[n + g.sy], wsth = w[n - g.sy];
         const double uc = U.c, vc = V.c, wc = W.c;
         // operation order and the /(2.0*dx), /(dx*dx) divisions of solver_projection.c:120-171
-        const double conv_u = uc * ((ue - uw) / g.two_dx) + vc * ((un - usth) / g.two_dy) +
+        const double conv_u = uc * (ediv(ue - uw, g.two_dx, g.inv_2dx)) + vc * (ediv(un - usth, g.two_dy, g.inv_2dy)) +
                               wc * ((U.p - U.m) * g.inv_2dz);
-        const double conv_v = uc * ((ve - vw) / g.two_dx) + vc * ((vn - vsth) / g.two_dy) +
+        const double conv_v = uc * (ediv(ve - vw, g.two_dx, g.inv_2dx)) + vc * (ediv(vn - vsth, g.two_dy, g.inv_2dy)) +
                               wc * ((V.p - V.m) * g.inv_2dz);
-        const double conv_w = uc * ((we - ww) / g.two_dx) + vc * ((wn - wsth) / g.two_dy) +
+        const double conv_w = uc * (ediv(we - ww, g.two_dx, g.inv_2dx)) + vc * (ediv(wn - wsth, g.two_dy, g.inv_2dy)) +
                               wc * ((W.p - W.m) * g.inv_2dz);
-        const double visc_u = c.nu * ((ue - 2.0 * uc + uw) / g.dx2 + (un - 2.0 * uc + usth) / g.dy2 +
+        const double visc_u = c.nu * (ediv(ue - 2.0 * uc + uw, g.dx2, g.inv_dx2) + ediv(un - 2.0 * uc + usth, g.dy2, g.inv_dy2) +
                                       (U.p - 2.0 * uc + U.m) * g.inv_dz2);
-        const double visc_v = c.nu * ((ve - 2.0 * vc + vw) / g.dx2 + (vn - 2.0 * vc + vsth) / g.dy2 +
+        const double visc_v = c.nu * (ediv(ve - 2.0 * vc + vw, g.dx2, g.inv_dx2) + ediv(vn - 2.0 * vc + vsth, g.dy2, g.inv_dy2) +
                                       (V.p - 2.0 * vc + V.m) * g.inv_dz2);
-        const double visc_w = c.nu * ((we - 2.0 * wc + ww) / g.dx2 + (wn - 2.0 * wc + wsth) / g.dy2 +
+        const double visc_w = c.nu * (ediv(we - 2.0 * wc + ww, g.dx2, g.inv_dx2) + ediv(wn - 2.0 * wc + wsth, g.dy2, g.inv_dy2) +
                                       (W.p - 2.0 * wc + W.m) * g.inv_dz2);
         double fu = su, fv = sv, fw = 0.0;
         if (c.beta != 0.0) {
@@ -127,7 +127,7 @@ k_divergence(Geom g, NsConst c, int zchunk, const double* __restrict__ us, const
     double wm = D3 ? ws[n - g.sz] : 0.0, wc = D3 ? ws[n] : 0.0, wp = 0.0;
     for (int k = kb; k < ke; k++, n += g.sz) {
         if (D3) wp = ws[n + g.sz];
-        const double div = (us[n + 1] - us[n - 1]) / g.two_dx + (vs[n + g.sy] - vs[n - g.sy]) / g.two_dy +
+        const double div = ediv(us[n + 1] - us[n - 1], g.two_dx, g.inv_2dx) + ediv(vs[n + g.sy] - vs[n - g.sy], g.two_dy, g.inv_2dy) +
                            (wp - wm) * g.inv_2dz;
         rhs[n] = c.rho_over_dt * div;
         wm = wc;
@@ -177,8 +177,8 @@ k_corrector(Geom g, NsConst c, int zchunk, const double* __restrict__ us, const 
                 P.p = p[n + g.sz];
                 if (ENERGY) Q.p = T[n + g.sz];
             }
-            const double un = clamp100(us[n] - c.dt_over_rho * ((p[n + 1] - p[n - 1]) / g.two_dx));
-            const double vn = clamp100(vs[n] - c.dt_over_rho * ((p[n + g.sy] - p[n - g.sy]) / g.two_dy));
+            const double un = clamp100(us[n] - c.dt_over_rho * (ediv(p[n + 1] - p[n - 1], g.two_dx, g.inv_2dx)));
+            const double vn = clamp100(vs[n] - c.dt_over_rho * (ediv(p[n + g.sy] - p[n - g.sy], g.two_dy, g.inv_2dy)));
             const double wn = clamp100(ws[n] - c.dt_over_rho * ((P.p - P.m) * g.inv_2dz));
             u[n] = un;
             v[n] = vn;

@@ -54,12 +54,12 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
             const double* f = qin.a[q];
             if (D3) F[q].p = f[zp];
             const double e = f[n + oxp], w_ = f[n + oxm], nn = f[n + oyp], s_ = f[n + oym], cc = F[q].c;
-            d1[q][0] = clampv(100.0, (e - w_) / g.two_dx);
-            d1[q][1] = clampv(100.0, (nn - s_) / g.two_dy);
+            d1[q][0] = clampv(100.0, ediv(e - w_, g.two_dx, g.inv_2dx));
+            d1[q][1] = clampv(100.0, ediv(nn - s_, g.two_dy, g.inv_2dy));
             d1[q][2] = clampv(100.0, (F[q].p - F[q].m) * g.inv_2dz);
             if (q < 3) {
-                d2[q][0] = clampv(1000.0, (e - 2.0 * cc + w_) / g.dx2);
-                d2[q][1] = clampv(1000.0, (nn - 2.0 * cc + s_) / g.dy2);
+                d2[q][0] = clampv(1000.0, ediv(e - 2.0 * cc + w_, g.dx2, g.inv_dx2));
+                d2[q][1] = clampv(1000.0, ediv(nn - 2.0 * cc + s_, g.dy2, g.inv_dy2));
                 d2[q][2] = clampv(1000.0, (F[q].p - 2.0 * cc + F[q].m) * g.inv_dz2);
             }
         }

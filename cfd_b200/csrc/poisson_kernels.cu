@@ -162,11 +162,11 @@ k_jacobi(Geom g, const double* __restrict__ xin, double* __restrict__ xout,
             const double xe = xin[n + 1], xw = xin[n - 1], yn = xin[n + g.sy], ys = xin[n - g.sy];
             const double f = __ldg(rhs + n);
             if (RES) {
-                const double lap = (xe - 2.0 * zc + xw) / g.dx2 + (yn - 2.0 * zc + ys) / g.dy2 +
+                const double lap = ediv(xe - 2.0 * zc + xw, g.dx2, g.inv_dx2) + ediv(yn - 2.0 * zc + ys, g.dy2, g.inv_dy2) +
                                    (zp + zm - 2.0 * zc) * g.inv_dz2;
                 rmax[0] = fmax(rmax[0], fabs(lap - f));
             }
-            const double v = -(f - (xe + xw) / g.dx2 - (yn + ys) / g.dy2 -
+            const double v = -(f - ediv(xe + xw, g.dx2, g.inv_dx2) - ediv(yn + ys, g.dy2, g.inv_dy2) -
                                (zp + zm) * g.inv_dz2) * g.inv_factor;
             store_with_ghosts<D3>(g, xout, i, j, k, n, v);
             zm = zc;
@@ -191,8 +191,8 @@ k_redblack(Geom g, double* x, const double* __restrict__ rhs, Ctl* ctl, KArgs a,
         // (linear_solver_redblack.c:103-105; the "red = even" comment there does not match the code)
         if (((par0 + k) & 1) == colour) continue;
         const double zp = D3 ? x[n + g.sz] : 0.0, zm = D3 ? x[n - g.sz] : 0.0;
-        const double pn = -(__ldg(rhs + n) - (x[n + 1] + x[n - 1]) / g.dx2 -
-                            (x[n + g.sy] + x[n - g.sy]) / g.dy2 - (zp + zm) * g.inv_dz2) *
+        const double pn = -(__ldg(rhs + n) - ediv(x[n + 1] + x[n - 1], g.dx2, g.inv_dx2) -
+                            ediv(x[n + g.sy] + x[n - g.sy], g.dy2, g.inv_dy2) - (zp + zm) * g.inv_dz2) *
                           g.inv_factor;
         const double xc = x[n];
         store_with_ghosts<D3>(g, x, i, j, k, n, xc + a.omega * (pn - xc));
@@ -213,8 +213,8 @@ k_linf_residual(Geom g, const double* __restrict__ x, const double* __restrict__
         double zm = D3 ? x[n - g.sz] : 0.0, zc = x[n], zp = 0.0;
         for (int k = kb; k < ke; k++, n += g.sz) {
             if (D3) zp = x[n + g.sz];
-            const double lap = (x[n + 1] - 2.0 * zc + x[n - 1]) / g.dx2 +
-                               (x[n + g.sy] - 2.0 * zc + x[n - g.sy]) / g.dy2 +
+            const double lap = ediv(x[n + 1] - 2.0 * zc + x[n - 1], g.dx2, g.inv_dx2) +
+                               ediv(x[n + g.sy] - 2.0 * zc + x[n - g.sy], g.dy2, g.inv_dy2) +
                                (zp + zm - 2.0 * zc) * g.inv_dz2;
             rmax[0] = fmax(rmax[0], fabs(lap - __ldg(rhs + n)));
             zm = zc;

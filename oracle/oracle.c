@@ -850,3 +850,28 @@ ORC_API void orc_field_stats(const flow_field* f, double* max_vel, double* max_p
     }
     *max_vel = mv; *max_p = mp; *max_T = mt;
 }
+
+/* ======================================================================
+ * Check of the device division sequence ediv() (cfd_b200/csrc/common.cuh): a/b from y = RN(1/b)
+ * with q = a*y, r = fma(-b,q,a), q' = fma(r,y,q) must equal the IEEE quotient the reference
+ * computes with '/'.  Returns the number of mismatches over `count` pseudo-random numerators
+ * (xorshift64, exponents 2^-40 .. 2^10, both signs) for the divisor b.
+ * ====================================================================== */
+ORC_API long orc_ediv_mismatches(double b, unsigned long long seed, long count) {
+    unsigned long long s = seed ? seed : 88172645463325252ULL;
+    double y = 1.0 / b;
+    long bad = 0;
+    for (long t = 0; t < count; t++) {
+        s ^= s << 13; s ^= s >> 7; s ^= s << 17;
+        unsigned long long m = s;
+        s ^= s << 13; s ^= s >> 7; s ^= s << 17;
+        unsigned long long bits = (m & 0x800FFFFFFFFFFFFFULL) | ((unsigned long long)(1023 - 40 + (s % 51)) << 52);
+        double a;
+        memcpy(&a, &bits, 8);
+        double q = a * y;
+        double r = fma(-b, q, a);
+        double q1 = fma(r, y, q);
+        if (q1 != a / b) bad++;
+    }
+    return bad;
+}

@@ -210,3 +210,18 @@ def test_bicgstab_is_sensitive_to_reduction_rounding_but_cg_is_not():
     ia, xa = run(a, abi.POISSON_METHOD_BICGSTAB, 1e-13)
     ib, xb = run(b, abi.POISSON_METHOD_BICGSTAB, 1e-13)
     assert max(cases.rel_err(xa, xb)) < 1e-8
+
+
+def test_exact_division_sequence(orc):
+    """The kernels divide by 2*dx, dx*dx with ediv(): a*y + one FMA residual + one FMA correction,
+    y = RN(1/b) from the host.  It must reproduce the IEEE quotient the reference gets from '/':
+    checked here with the same C fma() sequence on 2e7 numerators for each divisor a grid of the
+    BASELINE configs produces (and a few awkward ones)."""
+    import ctypes as C
+    fn = orc.lib.orc_ediv_mismatches
+    fn.restype = C.c_long
+    fn.argtypes = [C.c_double, C.c_ulonglong, C.c_long]
+    hs = [1.0 / 128, 1.0 / 127, 1.0 / 255, 1.0 / 1023, 1.0 / 4095, 2 * np.pi / 127, 1.3 / 19, 0.7 / 10, 1.0 / 3, 0.1]
+    for q, h in enumerate(hs):
+        for b in (2.0 * h, h * h):
+            assert fn(b, 1234567 + q, 1_000_000) == 0, b
