@@ -13,7 +13,7 @@
 // floating-point atomics anywhere inside an iteration.
 #include "common.cuh"
 #include "kernels.h"
-#include "tma.cuh"
+#include "stencil_tma.cuh"
 
 #include <limits.h>
 
@@ -42,23 +42,26 @@ template <bool D3>
 __device__ __forceinline__ void store_with_ghosts(const Geom& g, double* x, int i, int j, int k,
                                                   long long n, double v) {
     x[n] = v;
-    const bool ex = (i == 1) | (i == g.nx - 2), ey = (j == 1) | (j == g.ny - 2);
-    const bool ez = D3 && ((k == 1) | (k == g.nz - 2));
-    if (!(ex | ey | ez)) return;
-    long long ox[3] = {0, 0, 0}, oy[3] = {0, 0, 0}, oz[3] = {0, 0, 0};
-    int cx = 1, cy = 1, cz = 1;
-    if (i == 1 && g.glo[0]) ox[cx++] = -1;
-    if (i == g.nx - 2 && g.ghi[0]) ox[cx++] = 1;
-    if (j == 1 && g.glo[1]) oy[cy++] = -g.sy;
-    if (j == g.ny - 2 && g.ghi[1]) oy[cy++] = g.sy;
-    if (D3) {
-        if (k == 1 && g.glo[2]) oz[cz++] = -g.sz;
-        if (k == g.nz - 2 && g.ghi[2]) oz[cz++] = g.sz;
+    const bool xl = (i == 1) && g.glo[0], xh = (i == g.nx - 2) && g.ghi[0];
+    const bool yl = (j == 1) && g.glo[1], yh = (j == g.ny - 2) && g.ghi[1];
+    const bool zl = D3 && (k == 1) && g.glo[2], zh = D3 && (k == g.nz - 2) && g.ghi[2];
+    if (!(xl | xh | yl | yh | zl | zh)) return;
+    // every combination of {0, low ghost, high ghost} per axis except (0,0,0); no local arrays
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        if ((c == 1 && !zl) || (c == 2 && !zh)) continue;
+        const long long oz = (c == 0) ? 0 : (c == 1 ? -g.sz : g.sz);
+#pragma unroll
+        for (int b = 0; b < 3; b++) {
+            if ((b == 1 && !yl) || (b == 2 && !yh)) continue;
+            const long long oy = (b == 0) ? 0 : (b == 1 ? -g.sy : g.sy);
+#pragma unroll
+            for (int a = 0; a < 3; a++) {
+                if ((a == 1 && !xl) || (a == 2 && !xh)) continue;
+                if (a | b | c) x[n + oz + oy + ((a == 0) ? 0 : (a == 1 ? -1 : 1))] = v;
+            }
+        }
     }
-    for (int c = 0; c < cz; c++)
-        for (int b = 0; b < cy; b++)
-            for (int a = 0; a < cx; a++)
-                if (a | b | c) x[n + ox[a] + oy[b] + oz[c]] = v;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -595,6 +598,7 @@ k_bicg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const doub
 
 
 #include "poisson_tma.inc"
+#include "poisson_tma2.inc"
 
 // =======================================================================================
 // Host launchers
@@ -618,17 +622,62 @@ void launch_jacobi(const LaunchCtx& L, const KArgs& a0, const double* xin, doubl
     const KArgs a = with_chunk(L, a0);
     // the residual of x_q is only consulted when the reference would have computed it
     const bool res = (a.it == 0) || ((a.it - 1) % a.check == 0);
+    {
+        TmaSet<1> tm;
+        const double* const ops[1] = {xin};
+        if (tma_maps(L, ops, tm)) {
+            KArgs at = a0;
+            at.zchunk = L.zchunk_tma;
+            constexpr size_t SM = DirectPipe<1>::SMEM;
+            static bool once = (tma_optin(k_jacobi_tma<true, true>, SM), tma_optin(k_jacobi_tma<true, false>, SM),
+                                tma_optin(k_jacobi_tma<false, true>, SM), tma_optin(k_jacobi_tma<false, false>, SM), true);
+            (void)once;
+#define CFDB_JACT(D3, RES) CFDB_LAUNCH(KK_JACOBI, L.st, (k_jacobi_tma<D3, RES><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, xout, rhs, L.ctl, L.rb, at)))
+            if (L.g.dim3) { if (res) CFDB_JACT(true, true); else CFDB_JACT(true, false); }
+            else { if (res) CFDB_JACT(false, true); else CFDB_JACT(false, false); }
+#undef CFDB_JACT
+            return;
+        }
+    }
 #define CFDB_JAC(D3, RES) CFDB_LAUNCH(KK_JACOBI, L.st, (k_jacobi<D3, RES><<<L.grid(), blk(), 0, L.st>>>(L.g, xin, xout, rhs, L.ctl, L.rb, a)))
     if (L.g.dim3) { if (res) CFDB_JAC(true, true); else CFDB_JAC(true, false); }
     else { if (res) CFDB_JAC(false, true); else CFDB_JAC(false, false); }
 #undef CFDB_JAC
 }
 void launch_redblack(const LaunchCtx& L, const KArgs& a0, double* x, const double* rhs, int colour, int decide) {
+    {
+        TmaSet<1> tm;
+        const double* const ops[1] = {x};
+        if (tma_maps(L, ops, tm)) {
+            KArgs at = a0;
+            at.zchunk = L.zchunk_tma;
+            constexpr size_t SM = DirectPipe<1>::SMEM;
+            static bool once = (tma_optin(k_redblack_tma<true>, SM), tma_optin(k_redblack_tma<false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_REDBLACK, L.st, (k_redblack_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, x, rhs, L.ctl, at, colour, decide)));
+            else CFDB_LAUNCH(KK_REDBLACK, L.st, (k_redblack_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, x, rhs, L.ctl, at, colour, decide)));
+            return;
+        }
+    }
     const KArgs a = with_chunk(L, a0);
     if (L.g.dim3) CFDB_LAUNCH(KK_REDBLACK, L.st, k_redblack<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, a, colour, decide));
     else CFDB_LAUNCH(KK_REDBLACK, L.st, k_redblack<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, a, colour, decide));
 }
 void launch_linf_residual(const LaunchCtx& L, const KArgs& a0, const double* x, const double* rhs, int slot) {
+    {
+        TmaSet<1> tm;
+        const double* const ops[1] = {x};
+        if (tma_maps(L, ops, tm)) {
+            KArgs at = a0;
+            at.zchunk = L.zchunk_tma;
+            constexpr size_t SM = DirectPipe<1>::SMEM;
+            static bool once = (tma_optin(k_linf_residual_tma<true>, SM), tma_optin(k_linf_residual_tma<false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_LINF, L.st, (k_linf_residual_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhs, L.ctl, L.rb, at, slot)));
+            else CFDB_LAUNCH(KK_LINF, L.st, (k_linf_residual_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhs, L.ctl, L.rb, at, slot)));
+            return;
+        }
+    }
     const KArgs a = with_chunk(L, a0);
     if (L.g.dim3) CFDB_LAUNCH(KK_LINF, L.st, k_linf_residual<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, L.rb, a, slot));
     else CFDB_LAUNCH(KK_LINF, L.st, k_linf_residual<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, L.rb, a, slot));
@@ -638,6 +687,20 @@ void launch_stationary_final(const LaunchCtx& L, const KArgs& a) {
 }
 void launch_krylov_init(const LaunchCtx& L, const KArgs& a0, const double* x, const double* rhs, double* r,
                         double* p0, double* rhat, int precond) {
+    {
+        TmaSet<1> tm;
+        const double* const ops[1] = {x};
+        if (tma_maps(L, ops, tm)) {
+            KArgs at = a0;
+            at.zchunk = L.zchunk_tma;
+            constexpr size_t SM = DirectPipe<1>::SMEM;
+            static bool once = (tma_optin(k_krylov_init_tma<true>, SM), tma_optin(k_krylov_init_tma<false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, (k_krylov_init_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhs, r, p0, rhat, L.ctl, L.rb, at, precond)));
+            else CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, (k_krylov_init_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhs, r, p0, rhat, L.ctl, L.rb, at, precond)));
+            return;
+        }
+    }
     const KArgs a = with_chunk(L, a0);
     if (L.g.dim3) CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, k_krylov_init<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, r, p0, rhat, L.ctl, L.rb, a, precond));
     else CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, k_krylov_init<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, r, p0, rhat, L.ctl, L.rb, a, precond));

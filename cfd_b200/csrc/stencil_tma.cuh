@@ -1,0 +1,153 @@
+// stencil_tma.cuh -- generic TMA plane pipeline for 7-point stencils on NF fields (sm_100a).
+//
+// One block = one 64 x 16 tile of interior cells marched along z (tma.cuh).  The {66,18,1} boxes
+// of the NF stencil fields arrive in a ring of ST stages (one mbarrier per stage, bytes counted
+// by the TMA unit).  For plane k a thread takes the in-plane neighbours of its 2 cells from the
+// shared plane k, the z neighbours from registers (plane k-1, k) and from the freshly landed
+// plane k+1.  Pointwise operands (centre only: rhs, u*, ...) are plain loads issued one plane
+// ahead.  One __syncthreads per plane retires plane k; thread 0 refills the stage at once.
+//
+// The functor supplies the arithmetic:
+//   static constexpr int NF, NPW;                                 // NPW >= 1 (a dummy if none)
+//   void pw_load(long long n, double (&pw)[NPW]) const;          // pointwise operands of cell n
+//   void cell(const St<NF>& s, const double (&pw)[NPW], long long n, int i, int j, int k);
+#pragma once
+#include "common.cuh"
+#include "tma.cuh"
+
+namespace cfdb {
+
+template <int NF>
+struct St {  // stencil values of NF fields at one cell
+    double c[NF], e[NF], w[NF], n[NF], s[NF], m[NF], p[NF];  // centre, x+1, x-1, y+1, y-1, z-1, z+1
+};
+
+template <int NF>
+struct DirectPipe {
+    static constexpr int ST = (NF == 1) ? 6 : (NF == 2 ? 4 : 3);
+    static constexpr int RING = ST * NF * Tile::PLANE_PAD;
+    static constexpr size_t SMEM = (size_t)RING * sizeof(double) + ST * sizeof(uint64_t);
+};
+
+#ifdef __CUDACC__
+
+template <bool D3, class Op>
+__device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const Geom& g, int zchunk, Op& op) {
+    constexpr int NF = Op::NF, NPW = Op::NPW, ST = DirectPipe<NF>::ST;
+    constexpr int HX = Tile::HX, PP = Tile::PLANE_PAD;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double* ring = reinterpret_cast<double*>(smem_raw);                          // [ST][NF][PP]
+    uint64_t* full = reinterpret_cast<uint64_t*>(ring + DirectPipe<NF>::RING);  // [ST]
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * Tile::BX, y0 = blockIdx.y * Tile::BY;
+    const int kb = g.k0 + blockIdx.z * zchunk, ke = min(kb + zchunk, g.k1);
+    const int np = D3 ? (ke - kb + 2) : 1;  // planes kb-1 .. ke
+    const int pz0 = D3 ? kb - 1 : 0;
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < ST; s++) mbar_init(&full[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    int next_q = 0;
+    auto issue = [&](int q) {
+        const int slot = q % ST;
+        mbar_expect_tx(&full[slot], NF * Tile::PLANE_BYTES);
+#pragma unroll
+        for (int f = 0; f < NF; f++)
+            tma_load_plane(ring + (slot * NF + f) * PP, &tm.m[f], x0, y0, pz0 + q, &full[slot]);
+    };
+    if (tid == 0)
+        for (; next_q < ST && next_q < np; next_q++) issue(next_q);
+    const int lx = tid & (Tile::BX - 1), ly = tid >> 6;
+    const int i = x0 + 1 + lx;
+    int o[2], j[2];
+    bool act[2];
+    long long n[2];
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+        o[c] = Tile::OWN0(lx, ly + 8 * c);
+        j[c] = y0 + 1 + ly + 8 * c;
+        act[c] = (i < g.nx - 1) && (j[c] < g.ny - 1);
+        n[c] = (long long)kb * g.sz + (long long)j[c] * g.sy + i;
+    }
+    St<NF> s[2];
+    double pwn[2][NPW];
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+        if (act[c]) op.pw_load(n[c], pwn[c]);
+#pragma unroll
+        for (int f = 0; f < NF; f++) s[c].m[f] = s[c].p[f] = 0.0;
+    }
+    auto wait_q = [&](int q) -> const double* {
+        const int slot = q % ST;
+        mbar_wait(&full[slot], (q / ST) & 1);
+        return ring + slot * NF * PP;
+    };
+    const double* cur;  // shared plane k
+    if (D3) {
+        const double* p0 = wait_q(0);
+        cur = wait_q(1);
+#pragma unroll
+        for (int c = 0; c < 2; c++)
+#pragma unroll
+            for (int f = 0; f < NF; f++) {
+                s[c].m[f] = p0[f * PP + o[c]];
+                s[c].c[f] = cur[f * PP + o[c]];
+            }
+    } else {
+        cur = wait_q(0);
+#pragma unroll
+        for (int c = 0; c < 2; c++)
+#pragma unroll
+            for (int f = 0; f < NF; f++) s[c].c[f] = cur[f * PP + o[c]];
+    }
+    for (int k = kb; k < ke; k++) {
+        const int q = k - kb + 2;  // raw plane k+1 (3-D)
+        double pw[2][NPW];
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+#pragma unroll
+            for (int v = 0; v < NPW; v++) pw[c][v] = pwn[c][v];
+            if (act[c] && k + 1 < ke) op.pw_load(n[c] + g.sz, pwn[c]);
+        }
+        const double* nxt = cur;
+        if (D3) nxt = wait_q(q);
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+#pragma unroll
+            for (int f = 0; f < NF; f++) {
+                const double* pl = cur + f * PP + o[c];
+                if (D3) s[c].p[f] = nxt[f * PP + o[c]];
+                s[c].e[f] = pl[1];
+                s[c].w[f] = pl[-1];
+                s[c].n[f] = pl[HX];
+                s[c].s[f] = pl[-HX];
+            }
+            if (act[c]) op.cell(s[c], pw[c], n[c], i, j[c], k);
+#pragma unroll
+            for (int f = 0; f < NF; f++) {
+                s[c].m[f] = s[c].c[f];
+                s[c].c[f] = s[c].p[f];
+            }
+            n[c] += g.sz;
+        }
+        if (D3) {
+            __syncthreads();  // every thread is done with shared plane k (stage of q-1) and older
+            if (tid == 0) {
+                fence_proxy_async();
+                while (next_q < np && next_q - ST <= q - 1) issue(next_q++);
+            }
+            cur = nxt;
+        }
+    }
+}
+
+template <class K>
+static inline void tma_optin(K kernel, size_t smem) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+}
+
+#endif  // __CUDACC__
+
+}  // namespace cfdb
