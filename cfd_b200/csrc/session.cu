@@ -194,10 +194,22 @@ cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
         // TMA kernels: 64x16 tiles, 2 blocks per SM; aim at >= 8 waves but keep chunks >= 32 planes
         // (each chunk re-reads 2 planes in its prologue)
         const long long ttiles = (long long)((s->g.nx - 2 + Tile::BX - 1) / Tile::BX) * ((s->g.ny - 2 + Tile::BY - 1) / Tile::BY);
-        long long nch = (148LL * 2 * 8 + ttiles - 1) / ttiles;
-        if (nch > nzi / 32) nch = nzi / 32;
-        if (nch < 1) nch = 1;
-        s->zchunk_tma = (int)((nzi + nch - 1) / nch);
+        // Short chunks win (measured at 1024^3: 32 planes -> 1.03 of the copy peak for bicg_dir, 341
+        // planes -> 0.85): blocks of one x-y neighbourhood stay within a few planes of each other, so
+        // the halo rows they share are still in L2.  32 planes cost 6 % prologue re-reads; small grids
+        // use shorter chunks to get at least ~4 waves of 148 x 2 blocks.
+        const long long nch_target = (148LL * 2 * 4 + ttiles - 1) / ttiles;
+        long long zc = (nzi + nch_target - 1) / nch_target;
+        if (zc > 32) zc = 32;
+        if (zc < 4) zc = 4;
+        if (zc > nzi) zc = nzi;
+        s->zchunk_tma = (int)(zc < 1 ? 1 : zc);
+        if (const char* e = getenv("CFD_B200_ZCHUNK_TMA")) {  // tuning knob
+            const int v = atoi(e);
+            if (v >= 1) s->zchunk_tma = v > nzi ? nzi : v;
+        }
+        const size_t tma_blocks = (size_t)ttiles * (size_t)((nzi + s->zchunk_tma - 1) / s->zchunk_tma);
+        if (s->rb_blocks < tma_blocks) s->rb_blocks = tma_blocks;  // one partial-sum row per block
         s->tma.configure(s->g);
     }
     ok = ok && cudaMalloc((void**)&s->ctl, sizeof(Ctl)) == cudaSuccess;
