@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- projection-step MLUPS (FP64) and Poisson-sweep HBM GB/s against the roofline.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 1024] [--iters 50]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--box 1024] [--iters 50]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
         --master-port P bench.py --gpus N --steps K --warmup W
 
@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=0, help="cells per axis per GPU (0 = 1024 if it fits, else smaller)")
+    ap.add_argument("--box", dest="n", type=int, default=0, help="cells per axis per GPU (0 = 1024 if it fits, else smaller)")
     ap.add_argument("--iters", type=int, default=50, help="BiCGSTAB iterations per step (fixed)")
     ap.add_argument("--method", default="bicgstab", choices=["jacobi", "rbsor", "cg", "pcg", "bicgstab"])
     ap.add_argument("--cpu-n", type=int, default=0, help="box edge of the CPU sample (0 = auto)")

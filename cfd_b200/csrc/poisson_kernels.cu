@@ -303,6 +303,10 @@ __device__ __forceinline__ void comb_matvec(const Geom& g, const KArgs& a, const
                             (cp + cm - 2.0 * cc) * g.inv_dz2);
         cout[n] = cc;
         aout[n] = Ac;
+        if (!D3) {  // 2-D slabs are cut along y: keep the halo ROWS of c current
+            if (j == 1 && !g.glo[1]) cout[n - g.sy] = cs;
+            if (j == g.ny - 2 && !g.ghi[1]) cout[n + g.sy] = cn;
+        }
         op.dots(n, cc, Ac, acc);
         cm = cc;
         cc = cp;

@@ -98,8 +98,18 @@ cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
     if (thermo && (rc = dalloc(s, &s->T)) != CFD_SUCCESS) return rc;  // (zeros unless uploaded)
     if (energy && (rc = dalloc(s, &s->Tn)) != CFD_SUCCESS) return rc;
     if ((rc = ensure_tables(s, prm)) != CFD_SUCCESS) return rc;
-    NsConst c = make_const(s, prm);
     const int R = s->desc.nranks;
+    if (R > 1) {
+        // the projection uses field->rho[0] of the GLOBAL field (solver_projection.c:195): rank 0 owns it
+        const double mine = (s->desc.rank == 0) ? s->rho0 : 0.0;
+        CFDB_CUDA_OK(cudaMemcpyAsync(&s->ctl->stat[3], &mine, sizeof(double), cudaMemcpyHostToDevice, s->st));
+        if ((rc = allreduce(s, &s->ctl->stat[3], 1, false)) != CFD_SUCCESS) return rc;
+        double all = 0.0;
+        CFDB_CUDA_OK(cudaMemcpyAsync(&all, &s->ctl->stat[3], sizeof(double), cudaMemcpyDeviceToHost, s->st));
+        CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
+        s->rho0 = all;
+    }
+    NsConst c = make_const(s, prm);
     CFDB_CUDA_OK(cudaMemsetAsync(&s->ctl->nonfinite, 0, sizeof(int), s->st));
     for (int iter = 0; iter < nsteps; iter++) {
         const LaunchCtx L = s->L();
