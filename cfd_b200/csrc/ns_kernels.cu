@@ -13,6 +13,7 @@
 // z-1/z/z+1 values in registers, in-plane neighbours through L1.
 #include "common.cuh"
 #include "kernels.h"
+#include "stencil_tma.cuh"
 
 #include <limits.h>
 
@@ -244,16 +245,59 @@ k_energy(Geom g, NsConst c, int zchunk, const double* __restrict__ u, const doub
 }
 
 
+#include "ns_tma.inc"
+
 // ---- host launchers ----
 static inline dim3 blk2() { return dim3(TX, TY); }
+static inline dim3 tma_grid2(const LaunchCtx& L) {
+    const int nzi = L.g.k1 - L.g.k0;
+    return dim3((L.g.nx - 2 + Tile::BX - 1) / Tile::BX, (L.g.ny - 2 + Tile::BY - 1) / Tile::BY,
+                (nzi + L.zchunk_tma - 1) / L.zchunk_tma);
+}
+template <int N>
+static inline bool tma_maps2(const LaunchCtx& L, const double* const (&ptr)[N], TmaSet<N>& out) {
+    if (!L.tc || !L.tc->usable) return false;
+    for (int q = 0; q < N; q++) {
+        const CUtensorMap* m = L.tc->get(ptr[q]);
+        if (!m) return false;
+        out.m[q] = *m;
+    }
+    return true;
+}
+static inline int face_blocks(const Geom& g) { return (int)((face_cells(g) + 255) / 256); }
 void launch_predictor(const LaunchCtx& L, const NsConst& c, const double* u, const double* v, const double* w,
                       const double* T, const double* su_tab, const double* sv_tab, double* us, double* vs,
                       double* ws) {
+    {
+        TmaSet<3> tm;
+        const double* const ops[3] = {u, v, w};
+        if (tma_maps2(L, ops, tm)) {
+            constexpr size_t SM = DirectPipe<3>::SMEM;
+            static bool once = (tma_optin(k_predictor_tma<true>, SM), tma_optin(k_predictor_tma<false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_PREDICTOR, L.st, (k_predictor_tma<true><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, T, su_tab, sv_tab, us, vs, ws)));
+            else CFDB_LAUNCH(KK_PREDICTOR, L.st, (k_predictor_tma<false><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, T, su_tab, sv_tab, us, vs, ws)));
+            CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_carry3<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, us, vs, ws)));
+            return;
+        }
+    }
     if (L.g.dim3) CFDB_LAUNCH(KK_PREDICTOR, L.st, k_predictor<true><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, u, v, w, T, su_tab, sv_tab, us, vs, ws));
     else CFDB_LAUNCH(KK_PREDICTOR, L.st, k_predictor<false><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, u, v, w, T, su_tab, sv_tab, us, vs, ws));
 }
 void launch_divergence(const LaunchCtx& L, const NsConst& c, const double* us, const double* vs,
                        const double* ws, double* rhs) {
+    {
+        TmaSet<3> tm;
+        const double* const ops[3] = {us, vs, ws};
+        if (tma_maps2(L, ops, tm)) {
+            constexpr size_t SM = DirectPipe<3>::SMEM;
+            static bool once = (tma_optin(k_divergence_tma<true>, SM), tma_optin(k_divergence_tma<false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_DIVERGENCE, L.st, (k_divergence_tma<true><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, rhs)));
+            else CFDB_LAUNCH(KK_DIVERGENCE, L.st, (k_divergence_tma<false><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, rhs)));
+            return;
+        }
+    }
     if (L.g.dim3) CFDB_LAUNCH(KK_DIVERGENCE, L.st, k_divergence<true><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, us, vs, ws, rhs));
     else CFDB_LAUNCH(KK_DIVERGENCE, L.st, k_divergence<false><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, us, vs, ws, rhs));
 }
@@ -261,6 +305,31 @@ void launch_corrector(const LaunchCtx& L, const NsConst& c, const double* us, co
                       const double* ws, const double* p, double* u, double* v, double* w, const double* T,
                       double* Tn) {
     const bool en = c.alpha > 0.0;
+    if (en) {
+        TmaSet<2> tm;
+        const double* const ops[2] = {p, T};
+        if (tma_maps2(L, ops, tm)) {
+            constexpr size_t SM = DirectPipe<2>::SMEM;
+            static bool once = (tma_optin(k_corrector_tma<true, true>, SM), tma_optin(k_corrector_tma<false, true>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_corrector_tma<true, true><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, us, vs, ws, u, v, w, Tn, L.ctl)));
+            else CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_corrector_tma<false, true><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, us, vs, ws, u, v, w, Tn, L.ctl)));
+            CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_scan<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, p, T, Tn, L.ctl)));
+            return;
+        }
+    } else {
+        TmaSet<1> tm;
+        const double* const ops[1] = {p};
+        if (tma_maps2(L, ops, tm)) {
+            constexpr size_t SM = DirectPipe<1>::SMEM;
+            static bool once = (tma_optin(k_corrector_tma<true, false>, SM), tma_optin(k_corrector_tma<false, false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_corrector_tma<true, false><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, us, vs, ws, u, v, w, Tn, L.ctl)));
+            else CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_corrector_tma<false, false><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, us, vs, ws, u, v, w, Tn, L.ctl)));
+            CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_scan<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, p, nullptr, nullptr, L.ctl)));
+            return;
+        }
+    }
     if (L.g.dim3) {
         if (en) CFDB_LAUNCH(KK_CORRECTOR, L.st, k_corrector<true, true><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, us, vs, ws, p, u, v, w, T, Tn, L.ctl));
         else CFDB_LAUNCH(KK_CORRECTOR, L.st, k_corrector<true, false><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, us, vs, ws, p, u, v, w, T, Tn, L.ctl));
@@ -271,6 +340,20 @@ void launch_corrector(const LaunchCtx& L, const NsConst& c, const double* us, co
 }
 void launch_energy(const LaunchCtx& L, const NsConst& c, const double* u, const double* v, const double* w,
                    const double* T, double* Tn) {
+    {
+        TmaSet<1> tm;
+        const double* const ops[1] = {T};
+        if (tma_maps2(L, ops, tm)) {
+            constexpr size_t SM = DirectPipe<1>::SMEM;
+            static bool once = (tma_optin(k_energy_tma<true>, SM), tma_optin(k_energy_tma<false>, SM), true);
+            (void)once;
+            if (L.g.dim3) CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_energy_tma<true><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, u, v, w, Tn, L.ctl)));
+            else CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_energy_tma<false><<<tma_grid2(L), Tile::THREADS, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, u, v, w, Tn, L.ctl)));
+            // T carry-over and finiteness on boundary cells (u stands in for p: scanned twice, harmless)
+            CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_scan<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, u, T, Tn, L.ctl)));
+            return;
+        }
+    }
     if (L.g.dim3) CFDB_LAUNCH(KK_CORRECTOR, L.st, k_energy<true><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, u, v, w, T, Tn, L.ctl));
     else CFDB_LAUNCH(KK_CORRECTOR, L.st, k_energy<false><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, u, v, w, T, Tn, L.ctl));
 }

@@ -80,3 +80,25 @@ def test_fails_loudly_without_cuda():
         api.Session(16, 16, 1, 0.1, 0.1)
     with pytest.raises(lib.CfdB200Error):
         api.GpuSolver("projection_gpu")
+
+
+def test_dropin_library_registers_the_gpu_names(ref):
+    """oracle/_ref/libcfd_ref_dropin.so = unmodified reference core/api + libcfd_b200.so in place of
+    libcfd_cuda.a.  Without a GPU the reference's factory must get NULL from our side
+    (solver_registry.c:1157-1160) -- never a silent CPU path."""
+    import ctypes as C
+    import oracle
+    try:
+        d = oracle.Ref("dropin")
+    except (FileNotFoundError, OSError) as e:
+        pytest.skip(str(e))
+    L = d.lib
+    reg = L.cfd_registry_create()
+    L.cfd_registry_register_defaults(reg)
+    L.cfd_registry_has.restype = C.c_int
+    L.cfd_registry_has.argtypes = [C.c_void_p, C.c_char_p]
+    for name in (b"projection_gpu", b"rk2_gpu", b"rk4_gpu"):
+        assert L.cfd_registry_has(reg, name) == 1
+    if not lib.load().gpu_is_available():
+        assert not L.cfd_solver_create(reg, b"projection_gpu")
+    L.cfd_registry_destroy(reg)

@@ -301,3 +301,31 @@ def test_legacy_context_api(orc, poisson_cfg):
     rc, _ = orc.projection(fo, g, p, abi.poisson_config("cg"), 1)
     assert_close(f, fo, 1e-8, "legacy")
     assert st.kernels_launched > 0 and st.poisson_iterations > 0
+
+
+@pytest.mark.parametrize("name,kind", [("projection_gpu", "projection"), ("rk4_gpu", "rk4"), ("rk2_gpu", "rk2")])
+def test_dropin_through_the_reference_registry(orc, poisson_cfg, name, kind):
+    """Link-time drop-in: the UNMODIFIED reference core/api, compiled with
+    CFD_HAS_CUDA=1 and linked against libcfd_b200.so instead of libcfd_cuda.a
+    (oracle/_ref/libcfd_ref_dropin.so), creates "<name>" from its own registry and steps it; the
+    reference's wrappers (solver_registry.c:1121-1245) call our solve_*_method_gpu symbols."""
+    import oracle
+    try:
+        ref = oracle.Ref("dropin")
+    except (FileNotFoundError, OSError) as e:
+        pytest.skip(str(e))
+    api.set_poisson("cg")
+    g, f = cases.random_field(18, 14, 9, seed=4, scale=0.05)
+    p = cases.params(dt=1e-3, amp=(0.1, 0.05))
+    fo = f.copy()
+    n0 = api.load().cfd_b200_kernel_launch_count()
+    rc, st = ref.run_solver(name, f, g, p, nsteps=2)
+    assert rc == 0
+    assert api.load().cfd_b200_kernel_launch_count() > n0  # our kernels did the work
+    for _ in range(2):
+        if kind == "projection":
+            rco, _ = orc.projection(fo, g, p, abi.poisson_config("cg"), 1)
+        else:
+            rco = orc.rk(fo, g, p, int(kind[2]), 1)
+        assert rco == 0
+    assert_close(f, fo, 1e-8 if kind == "projection" else 1e-10, "dropin " + name)
