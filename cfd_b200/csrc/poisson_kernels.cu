@@ -228,6 +228,33 @@ k_linf_residual(Geom g, const double* __restrict__ x, const double* __restrict__
 }
 
 
+// Pointwise sweeps (axpy-type updates with dots): 1-D blocks of PW_THREADS along x, each block a
+// chunk of `rpb` consecutive interior rows (a row = one (j,k) pair), so a thread streams rpb
+// independent cells -- the same code serves 3-D grids and 2-D grids (where the z-marching layout
+// would give one cell per thread).
+constexpr int PW_THREADS = 256;
+template <class F>
+__device__ __forceinline__ void pointwise_rows(const Geom& g, int rpb, F f) {
+    const int i = 1 + blockIdx.x * PW_THREADS + threadIdx.x;
+    const int nyi = g.ny - 2;
+    const long long rows = (long long)nyi * (g.k1 - g.k0);
+    const long long r0 = (long long)blockIdx.y * rpb;
+    const long long r1 = r0 + rpb < rows ? r0 + rpb : rows;
+    if (i >= g.nx - 1) return;
+    int j = 1 + (int)(r0 % nyi), k = g.k0 + (int)(r0 / nyi);
+    long long n = (long long)k * g.sz + (long long)j * g.sy + i;
+#pragma unroll 4
+    for (long long rr = r0; rr < r1; rr++) {
+        f(n);
+        if (++j == g.ny - 1) {  // next plane: skip the two boundary rows
+            j = 1;
+            n += 3 * g.sy;
+        } else {
+            n += g.sy;
+        }
+    }
+}
+
 // =======================================================================================
 // Krylov solvers.  A = -lap on interior cells; r, p, v, s, t keep ZERO on physical boundary
 // cells (never written), exactly as the reference's calloc'ed work vectors.
@@ -405,19 +432,14 @@ k_cg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const double
         return;
     }
     const double alpha = ctl->dot[2 * par + precond] / pAp;
-    int i, j, kb, ke;
-    const bool act = column(g, a.zchunk, i, j, kb, ke);
     double acc[2] = {0.0, 0.0};
-    if (act) {
-        long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
-        for (int k = kb; k < ke; k++, n += g.sz) {
-            x[n] += alpha * __ldg(p + n);
-            const double rv = r[n] - alpha * __ldg(Ap + n);
-            r[n] = rv;
-            acc[0] += rv * rv;
-            acc[1] += rv * (a.dinv * rv);
-        }
-    }
+    pointwise_rows(g, a.zchunk, [&](long long n) {
+        x[n] += alpha * __ldg(p + n);
+        const double rv = r[n] - alpha * __ldg(Ap + n);
+        r[n] = rv;
+        acc[0] += rv * rv;
+        acc[1] += rv * (a.dinv * rv);
+    });
     block_reduce_finish<2, false>(acc, rb, &ctl->dot[2 * (par ^ 1)]);
 }
 
@@ -579,25 +601,20 @@ k_bicg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const doub
         finish(ctl, a, POISSON_STAGNATED, a.it + 1, sn, 1, 1);
     }
     const double omega = (mode == 0) ? ctl->dot[8 + 4 * par + 1] / tt : 0.0;
-    int i, j, kb, ke;
-    const bool act = column(g, a.zchunk, i, j, kb, ke);
     double acc[2] = {0.0, 0.0};
-    if (act) {
-        long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
-        for (int k = kb; k < ke; k++, n += g.sz) {
-            if (mode == 1) {
-                x[n] += alpha * __ldg(p + n);
-            } else {
-                const double sv = __ldg(s + n);
-                x[n] += alpha * __ldg(p + n) + omega * sv;
-                const double rv = sv - omega * __ldg(t + n);
-                r[n] = rv;
-                acc[0] += rv * rv;
-                acc[1] += __ldg(rhat + n) * rv;
-            }
-        }
+    if (mode == 1) {
+        pointwise_rows(g, a.zchunk, [&](long long n) { x[n] += alpha * __ldg(p + n); });
+    } else {
+        pointwise_rows(g, a.zchunk, [&](long long n) {
+            const double sv = __ldg(s + n);
+            x[n] += alpha * __ldg(p + n) + omega * sv;
+            const double rv = sv - omega * __ldg(t + n);
+            r[n] = rv;
+            acc[0] += rv * rv;
+            acc[1] += __ldg(rhat + n) * rv;
+        });
+        block_reduce_finish<2, false>(acc, rb, &ctl->dot[2 * (par ^ 1)]);
     }
-    if (mode == 0) block_reduce_finish<2, false>(acc, rb, &ctl->dot[2 * (par ^ 1)]);
 }
 
 
@@ -612,6 +629,19 @@ dim3 LaunchCtx::grid() const {
     return dim3((g.nx + TX - 1) / TX, (g.ny + TY - 1) / TY, (nzi + zchunk - 1) / zchunk);
 }
 static inline dim3 blk() { return dim3(TX, TY); }
+// grid of the pointwise sweeps: x tiles of PW_THREADS cells, row chunks sized for ~6 waves of
+// 148 x 8 blocks, never more blocks than the partial-sum buffer has rows
+static inline dim3 pw_grid(const LaunchCtx& L, int& rpb) {
+    const long long xt = (L.g.nx - 2 + PW_THREADS - 1) / PW_THREADS;
+    const long long rows = (long long)(L.g.ny - 2) * (L.g.k1 - L.g.k0);
+    long long r = rows * xt / (148LL * 8 * 6);
+    if (r < 4) r = 4;
+    if (r > 64) r = 64;
+    const long long cap = (long long)L.rb_blocks;
+    while (xt * ((rows + r - 1) / r) > cap) r *= 2;
+    rpb = (int)r;
+    return dim3((unsigned)xt, (unsigned)((rows + r - 1) / r), 1);
+}
 static inline KArgs with_chunk(const LaunchCtx& L, KArgs a) {
     a.zchunk = L.zchunk;
     return a;
@@ -732,9 +762,9 @@ void launch_cg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const d
 }
 void launch_cg_update(const LaunchCtx& L, const KArgs& a0, double* x, double* r, const double* p,
                       const double* Ap, int precond) {
-    const KArgs a = with_chunk(L, a0);
-    if (L.g.dim3) CFDB_LAUNCH(KK_CG_UPDATE, L.st, k_cg_update<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, Ap, L.ctl, L.rb, a, precond));
-    else CFDB_LAUNCH(KK_CG_UPDATE, L.st, k_cg_update<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, Ap, L.ctl, L.rb, a, precond));
+    KArgs a = a0;
+    const dim3 gr = pw_grid(L, a.zchunk);
+    CFDB_LAUNCH(KK_CG_UPDATE, L.st, k_cg_update<true><<<gr, PW_THREADS, 0, L.st>>>(L.g, x, r, p, Ap, L.ctl, L.rb, a, precond));
 }
 void launch_bicg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const double* pold,
                      const double* vold, const double* rhat, double* pnew, double* vnew, int first,
@@ -780,9 +810,9 @@ void launch_bicg_s(const LaunchCtx& L, const KArgs& a0, const double* r, const d
 }
 void launch_bicg_update(const LaunchCtx& L, const KArgs& a0, double* x, double* r, const double* p,
                         const double* s, const double* t, const double* rhat) {
-    const KArgs a = with_chunk(L, a0);
-    if (L.g.dim3) CFDB_LAUNCH(KK_BICG_UPDATE, L.st, k_bicg_update<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, s, t, rhat, L.ctl, L.rb, a));
-    else CFDB_LAUNCH(KK_BICG_UPDATE, L.st, k_bicg_update<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, s, t, rhat, L.ctl, L.rb, a));
+    KArgs a = a0;
+    const dim3 gr = pw_grid(L, a.zchunk);
+    CFDB_LAUNCH(KK_BICG_UPDATE, L.st, k_bicg_update<true><<<gr, PW_THREADS, 0, L.st>>>(L.g, x, r, p, s, t, rhat, L.ctl, L.rb, a));
 }
 
 }  // namespace cfdb

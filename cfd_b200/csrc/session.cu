@@ -204,11 +204,21 @@ cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
         if (zc < 4) zc = 4;
         if (zc > nzi) zc = nzi;
         s->zchunk_tma = (int)(zc < 1 ? 1 : zc);
+        if (!s->g.dim3) {
+            // 2-D: the TMA kernels march along y; zchunk_tma = tiles of 16 rows per block
+            const long long tx = (s->g.nx - 2 + Tile::BX - 1) / Tile::BX, ty = (s->g.ny - 2 + Tile::BY - 1) / Tile::BY;
+            const long long nch2 = (148LL * 2 * 4 + tx - 1) / tx;
+            long long yc = (ty + nch2 - 1) / nch2;
+            if (yc > 32) yc = 32;
+            if (yc < 1) yc = 1;
+            s->zchunk_tma = (int)yc;
+        }
         if (const char* e = getenv("CFD_B200_ZCHUNK_TMA")) {  // tuning knob
             const int v = atoi(e);
             if (v >= 1) s->zchunk_tma = v > nzi ? nzi : v;
         }
-        const size_t tma_blocks = (size_t)ttiles * (size_t)((nzi + s->zchunk_tma - 1) / s->zchunk_tma);
+        const size_t tma_blocks = s->g.dim3 ? (size_t)ttiles * (size_t)((nzi + s->zchunk_tma - 1) / s->zchunk_tma)
+                                            : (size_t)ttiles;
         if (s->rb_blocks < tma_blocks) s->rb_blocks = tma_blocks;  // one partial-sum row per block
         s->tma.configure(s->g);
     }

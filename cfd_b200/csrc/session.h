@@ -70,6 +70,7 @@ struct cfd_b200_session {
         l.zchunk = zchunk;
         l.tc = const_cast<cfdb::TmaCache*>(&tma);
         l.zchunk_tma = zchunk_tma;
+        l.rb_blocks = rb_blocks;
         return l;
     }
 };

@@ -31,8 +31,90 @@ struct DirectPipe {
 
 #ifdef __CUDACC__
 
+// 2-D grids (nz == 1): the pipeline marches along y instead -- a block owns `ychunk` consecutive
+// 64 x 16 tiles of one x column of tiles and streams their {66,18,1} boxes through the same ring
+// (each box carries its own y halo; the 2 shared rows per tile come from L2).
+template <class Op>
+__device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, const Geom& g, int ychunk, Op& op) {
+    constexpr int NF = Op::NF, NPW = Op::NPW, ST = DirectPipe<NF>::ST;
+    constexpr int HX = Tile::HX, PP = Tile::PLANE_PAD;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double* ring = reinterpret_cast<double*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(ring + DirectPipe<NF>::RING);
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * Tile::BX;
+    const int tiles_y = (g.ny - 2 + Tile::BY - 1) / Tile::BY;
+    const int ty0 = blockIdx.y * ychunk;
+    const int nt = min(ychunk, tiles_y - ty0);
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < ST; s++) mbar_init(&full[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    int next_q = 0;
+    auto issue = [&](int q) {
+        const int slot = q % ST;
+        mbar_expect_tx(&full[slot], NF * Tile::PLANE_BYTES);
+#pragma unroll
+        for (int f = 0; f < NF; f++)
+            tma_load_plane(ring + (slot * NF + f) * PP, &tm.m[f], x0, (ty0 + q) * Tile::BY, 0, &full[slot]);
+    };
+    if (tid == 0)
+        for (; next_q < ST && next_q < nt; next_q++) issue(next_q);
+    const int lx = tid & (Tile::BX - 1), ly = tid >> 6;
+    const int i = x0 + 1 + lx;
+    const bool actx = i < g.nx - 1;
+    int o[2];
+#pragma unroll
+    for (int c = 0; c < 2; c++) o[c] = Tile::OWN0(lx, ly + 8 * c);
+    double pwn[2][NPW];
+    auto jrow = [&](int t, int c) { return (ty0 + t) * Tile::BY + 1 + ly + 8 * c; };
+#pragma unroll
+    for (int c = 0; c < 2; c++)
+        if (actx && jrow(0, c) < g.ny - 1) op.pw_load((long long)jrow(0, c) * g.sy + i, pwn[c]);
+    for (int t = 0; t < nt; t++) {
+        double pw[2][NPW];
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+#pragma unroll
+            for (int v = 0; v < NPW; v++) pw[c][v] = pwn[c][v];
+            if (t + 1 < nt && actx && jrow(t + 1, c) < g.ny - 1) op.pw_load((long long)jrow(t + 1, c) * g.sy + i, pwn[c]);
+        }
+        const int slot = t % ST;
+        mbar_wait(&full[slot], (t / ST) & 1);
+        const double* cur = ring + slot * NF * PP;
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+            const int j = jrow(t, c);
+            if (!(actx && j < g.ny - 1)) continue;
+            St<NF> s;
+#pragma unroll
+            for (int f = 0; f < NF; f++) {
+                const double* pl = cur + f * PP + o[c];
+                s.c[f] = pl[0];
+                s.e[f] = pl[1];
+                s.w[f] = pl[-1];
+                s.n[f] = pl[HX];
+                s.s[f] = pl[-HX];
+                s.m[f] = s.p[f] = 0.0;
+            }
+            op.cell(s, pw[c], (long long)j * g.sy + i, i, j, 0);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            fence_proxy_async();
+            while (next_q < nt && next_q - ST <= t) issue(next_q++);
+        }
+    }
+}
+
 template <bool D3, class Op>
 __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const Geom& g, int zchunk, Op& op) {
+    if (!D3) {
+        tma_direct_sweep_2d(tm, g, zchunk, op);
+        return;
+    }
     constexpr int NF = Op::NF, NPW = Op::NPW, ST = DirectPipe<NF>::ST;
     constexpr int HX = Tile::HX, PP = Tile::PLANE_PAD;
     extern __shared__ __align__(128) unsigned char smem_raw[];

@@ -1,0 +1,84 @@
+#!/usr/bin/env python
+"""Per-kernel roofline table for any grid shape / stepper on ONE GPU (exploration companion of
+bench.py; same timing method: per-launch CUDA events on the session stream, inputs larger than L2
+unless the grid itself is small -- flagged as cache-resident then).
+
+    python tools/kernel_table.py --shape 4096,4096,1 --method pcg --iters 100
+    python tools/kernel_table.py --shape 128,128,128 --stepper rk4 --steps 20
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--shape", default="512,512,512")
+    ap.add_argument("--stepper", default="projection", choices=["projection", "rk2", "rk4"])
+    ap.add_argument("--method", default="bicgstab")
+    ap.add_argument("--iters", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--energy", action="store_true", help="alpha > 0, beta != 0 (natural-convection kernels)")
+    a = ap.parse_args()
+    import torch
+    from cfd_b200 import abi, api, lib
+    nx, ny, nz = (int(v) for v in a.shape.split(","))
+    hx, hy, hz = 1.0 / (nx - 1), 1.0 / (ny - 1), (1.0 / (nz - 1) if nz > 1 else 0.0)
+    s = api.Session(nx, ny, nz, hx, hy, hz)
+    s.init_synthetic(12345, 0, nz)
+    p = abi.ns_params_default()
+    p.dt, p.mu = 1e-4, 0.01
+    p.source_amplitude_u = p.source_amplitude_v = 0.0
+    if a.energy:
+        p.alpha, p.beta, p.T_ref = 3.035e-2, 3.333e-3, 300.0
+        p.gravity[1] = -9.81
+        p.dt = 2.5e-7
+    pc = abi.poisson_config(a.method, max_iterations=a.iters, on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
+
+    def run(k):
+        if a.stepper == "projection":
+            rc, _ = s.projection(p, pc, k)
+        else:
+            rc, _ = s.rk(int(a.stepper[2]), p, k)
+        if rc != 0:
+            raise RuntimeError("step failed rc=%d: %s" % (rc, lib.last_error()))
+
+    run(a.warmup)
+    s.reset_kernel_stats()
+    s.profile(True)
+    st = torch.cuda.ExternalStream(s.stream())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(st)
+    run(a.steps)
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    s.profile(False)
+    interior = (nx - 2) * (ny - 2) * ((nz - 2) if nz > 1 else 1)
+    peak = 6548.2
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        pass
+    rows = []
+    for k in sorted(s.kernel_stats(), key=lambda k: -k["total_ms"]):
+        if k["total_ms"] <= 0:
+            continue
+        avg = k["total_ms"] / k["launches"]
+        gbs = k["bytes_per_cell"] * interior / (avg * 1e-3) / 1e9
+        rows.append({"kernel": k["name"], "launches": k["launches"], "avg_us": round(avg * 1e3, 2),
+                     "bytes_per_cell": k["bytes_per_cell"], "GBps": round(gbs, 1), "frac_of_measured_peak": round(gbs / peak, 4)})
+    out = {"shape": [nx, ny, nz], "stepper": a.stepper, "method": a.method, "iters": a.iters, "steps": a.steps,
+           "ms_per_step": ms / a.steps, "MLUPS": nx * ny * nz * a.steps / (ms * 1e-3) / 1e6,
+           "field_MB": 8 * nx * ny * nz / 1e6, "cache_resident": 8 * nx * ny * nz * 6 < 126e6, "kernels": rows}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
