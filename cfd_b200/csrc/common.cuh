@@ -177,6 +177,33 @@ __device__ __forceinline__ void block_reduce_finish(double (&v)[NV], const RedBu
     }
 }
 
+// ---- boundary-cell enumeration: x faces, y faces, physical z faces (edges visited twice) ----
+__device__ __forceinline__ long long face_cell(const Geom& g, long long t) {
+    const long long nyz = (long long)g.ny * g.nz, nxz = (long long)g.nx * g.nz, nxy = (long long)g.nx * g.ny;
+    if (t < 2 * nyz) {  // x faces
+        const int side = (int)(t / nyz);
+        const long long r = t % nyz;
+        return (r / g.ny) * nxy + (r % g.ny) * g.nx + (side ? g.nx - 1 : 0);
+    }
+    t -= 2 * nyz;
+    if (t < 2 * nxz) {  // y faces
+        const int side = (int)(t / nxz);
+        const long long r = t % nxz;
+        return (r / g.nx) * nxy + (long long)(side ? g.ny - 1 : 0) * g.nx + (r % g.nx);
+    }
+    t -= 2 * nxz;
+    if (g.dim3 && t < 2 * nxy) {  // z faces (physical ones only: halo planes belong to the exchange)
+        const int side = (int)(t / nxy);
+        if ((side == 0 && !g.glo[2]) || (side == 1 && !g.ghi[2])) return -1;
+        return (long long)(side ? g.nz - 1 : 0) * nxy + (t % nxy);
+    }
+    return -1;
+}
+__host__ __device__ __forceinline__ long long face_cells(const Geom& g) {
+    return 2LL * ((long long)g.ny * g.nz + (long long)g.nx * g.nz + (g.dim3 ? (long long)g.nx * g.ny : 0));
+}
+
+
 #endif  // __CUDACC__
 
 }  // namespace cfdb

@@ -100,6 +100,7 @@ void launch_energy(const LaunchCtx& L, const NsConst& c, const double* u, const 
                    const double* T, double* Tn);
 void launch_thermal_bc(const LaunchCtx& L, const ns_thermal_bc_config_t& bc, double* T);
 void launch_periodic_bc(const LaunchCtx& L, double* f, int wrap_y, int wrap_z);
+void launch_periodic_faces(const LaunchCtx& L, double* const* f, int nf, int wrap_y, int wrap_z);
 void launch_field_stats(const LaunchCtx& L, const double* u, const double* v, const double* w,
                         const double* p, const double* T);
 void launch_rk_stage(const LaunchCtx& L, const NsConst& c, const RkArgs& ra, const P4& qin, const P4& q0,

@@ -3,6 +3,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "ns_args.h"
+#include "stencil_tma.cuh"
 
 #include <limits.h>
 
@@ -102,6 +103,126 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
         }
     }
     if (bad && ra.last) ctl->nonfinite = 1;
+}
+
+
+// ---------------------------------------------------------------------------------------
+// TMA plane-pipeline version of the RK stage.  The reference RHS reads periodic-WRAPPED neighbour
+// indices (ns_momentum_rhs_scalar.h:80-90), i.e. never the boundary cells; here the boundary cells
+// of every stage input are first set to their periodic images (k_periodic_faces, O(N^(2/3))), so
+// the plain halo of the TMA box delivers exactly the wrapped values.  Same arithmetic and
+// operation order as k_rk_stage above.
+// ---------------------------------------------------------------------------------------
+struct RkOp {
+    static constexpr int NF = 4, NPW = 2;  // prefetched pointwise operands: rho, T (Q0, acc are loaded in cell())
+    const Geom& g;
+    const NsConst& c;
+    const RkArgs& ra;
+    const P4& q0;
+    const W4& acc;
+    const W4& qout;
+    const double* __restrict__ rho;
+    const double* __restrict__ T;
+    const double* __restrict__ su_tab;
+    const double* __restrict__ sv_tab;
+    bool bad;
+    __device__ __forceinline__ void pw_load(long long n, double (&pw)[2]) const {
+        pw[0] = __ldg(rho + n);
+        pw[1] = (c.beta != 0.0) ? __ldg(T + n) : 0.0;
+    }
+    __device__ __forceinline__ void cell(const St<4>& s, const double (&pw)[2], long long n, int i, int j, int) {
+        double b0[4], a0[4];  // Q0 and the running sum: issued first, consumed after the RHS arithmetic
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            b0[q] = ra.first ? 0.0 : __ldg(q0.a[q] + n);
+            a0[q] = ra.first ? 0.0 : acc.a[q][n];
+        }
+        double d1[4][3], d2[3][3];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const double cc = s.c[q];
+            d1[q][0] = clampv(100.0, ediv(s.e[q] - s.w[q], g.two_dx, g.inv_2dx));
+            d1[q][1] = clampv(100.0, ediv(s.n[q] - s.s[q], g.two_dy, g.inv_2dy));
+            d1[q][2] = clampv(100.0, (s.p[q] - s.m[q]) * g.inv_2dz);
+            if (q < 3) {
+                d2[q][0] = clampv(1000.0, ediv(s.e[q] - 2.0 * cc + s.w[q], g.dx2, g.inv_dx2));
+                d2[q][1] = clampv(1000.0, ediv(s.n[q] - 2.0 * cc + s.s[q], g.dy2, g.inv_dy2));
+                d2[q][2] = clampv(1000.0, (s.p[q] - 2.0 * cc + s.m[q]) * g.inv_dz2);
+            }
+        }
+        const double rh = pw[0];
+        double kq[4] = {0.0, 0.0, 0.0, 0.0};
+        if (rh > 1e-10) {
+            const double nu = fmin(c.mu / fmax(rh, 1e-10), 1.0);
+            double fu = c.src_on ? su_tab[j] * ra.src_decay : 0.0, fv = c.src_on ? sv_tab[i] * ra.src_decay : 0.0, fw = 0.0;
+            if (c.beta != 0.0) {
+                const double dT = pw[1] - c.T_ref;
+                fu += -c.beta * dT * c.gx;
+                fv += -c.beta * dT * c.gy;
+                fw += -c.beta * dT * c.gz;
+            }
+            const double uc = s.c[0], vc = s.c[1], wc = s.c[2];
+            const double src[3] = {fu, fv, fw};
+#pragma unroll
+            for (int q = 0; q < 3; q++)
+                kq[q] = -uc * d1[q][0] - vc * d1[q][1] - wc * d1[q][2] - d1[3][q] / rh +
+                        nu * (d2[q][0] + d2[q][1] + d2[q][2]) + src[q];
+            const double div = clampv(10.0, d1[0][0] + d1[1][1] + d1[2][2]);
+            kq[3] = -0.1 * rh * div;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const double base = ra.first ? s.c[q] : b0[q];
+            double out;
+            if (ra.last) {
+                const double a_ = ra.first ? 0.0 : a0[q];
+                out = base + ra.w_final * (a_ + kq[q]);
+            } else {
+                acc.a[q][n] = ra.first ? kq[q] : a0[q] + ra.w_k * kq[q];
+                out = base + ra.fac_next * kq[q];
+            }
+            if (q < 3) out = clamp100(out);
+            qout.a[q][n] = out;
+            bad |= !isfinite(out);
+        }
+    }
+};
+
+template <bool D3>
+__global__ void __launch_bounds__(Tile::THREADS, 1)
+k_rk_stage_tma(const __grid_constant__ TmaSet<4> tm, Geom g, NsConst c, RkArgs ra, int zchunk, P4 q0, W4 acc,
+               W4 qout, const double* __restrict__ rho, const double* __restrict__ T,
+               const double* __restrict__ su_tab, const double* __restrict__ sv_tab, Ctl* ctl) {
+    RkOp op{g, c, ra, q0, acc, qout, rho, T, su_tab, sv_tab, false};
+    tma_direct_sweep<D3>(tm, g, zchunk, op);
+    if (op.bad && ra.last) ctl->nonfinite = 1;
+}
+
+// Periodic images on the boundary cells of up to 6 fields, one thread per face cell (closed form of
+// the sequential x, y, z wrap of solver_explicit_euler.c:231-314: boundary = wrapped interior).
+struct F6 {
+    double* a[6];
+    int n;
+};
+__global__ void k_periodic_faces(Geom g, F6 f, int wrap_y, int wrap_z) {
+    const long long n = face_cell(g, (long long)blockIdx.x * blockDim.x + threadIdx.x);
+    if (n < 0) return;
+    const long long nxy = (long long)g.nx * g.ny;
+    const int i = (int)(n % g.nx), j = (int)((n / g.nx) % g.ny), k = (int)(n / nxy);
+    int ci = i, cj = j, ck = k;
+    if (i == 0) ci = g.nx - 2;
+    if (i == g.nx - 1) ci = 1;
+    if (wrap_y) {
+        if (j == 0) cj = g.ny - 2;
+        if (j == g.ny - 1) cj = 1;
+    }
+    if (g.dim3 && wrap_z) {
+        if (k == 0) ck = g.nz - 2;
+        if (k == g.nz - 1) ck = 1;
+    }
+    if (ci == i && cj == j && ck == k) return;
+    const long long src = (long long)ck * nxy + (long long)cj * g.nx + ci;
+    for (int q = 0; q < f.n; q++) f.a[q][n] = f.a[q][src];
 }
 
 // Periodic wrap of one field on every physical boundary (solver_explicit_euler.c:231-314):

@@ -123,8 +123,8 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * Tile::BX, y0 = blockIdx.y * Tile::BY;
     const int kb = g.k0 + blockIdx.z * zchunk, ke = min(kb + zchunk, g.k1);
-    const int np = D3 ? (ke - kb + 2) : 1;  // planes kb-1 .. ke
-    const int pz0 = D3 ? kb - 1 : 0;
+    const int np = ke - kb + 2;  // planes kb-1 .. ke
+    const int pz0 = kb - 1;
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < ST; s++) mbar_init(&full[s], 1);
@@ -153,39 +153,27 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
         act[c] = (i < g.nx - 1) && (j[c] < g.ny - 1);
         n[c] = (long long)kb * g.sz + (long long)j[c] * g.sy + i;
     }
-    St<NF> s[2];
+    double zm[2][NF], zc[2][NF];  // z-1 and centre values of the own cells, carried in registers
     double pwn[2][NPW];
 #pragma unroll
-    for (int c = 0; c < 2; c++) {
+    for (int c = 0; c < 2; c++)
         if (act[c]) op.pw_load(n[c], pwn[c]);
-#pragma unroll
-        for (int f = 0; f < NF; f++) s[c].m[f] = s[c].p[f] = 0.0;
-    }
     auto wait_q = [&](int q) -> const double* {
         const int slot = q % ST;
         mbar_wait(&full[slot], (q / ST) & 1);
         return ring + slot * NF * PP;
     };
-    const double* cur;  // shared plane k
-    if (D3) {
-        const double* p0 = wait_q(0);
-        cur = wait_q(1);
+    const double* p0 = wait_q(0);
+    const double* cur = wait_q(1);  // shared plane k
 #pragma unroll
-        for (int c = 0; c < 2; c++)
+    for (int c = 0; c < 2; c++)
 #pragma unroll
-            for (int f = 0; f < NF; f++) {
-                s[c].m[f] = p0[f * PP + o[c]];
-                s[c].c[f] = cur[f * PP + o[c]];
-            }
-    } else {
-        cur = wait_q(0);
-#pragma unroll
-        for (int c = 0; c < 2; c++)
-#pragma unroll
-            for (int f = 0; f < NF; f++) s[c].c[f] = cur[f * PP + o[c]];
-    }
+        for (int f = 0; f < NF; f++) {
+            zm[c][f] = p0[f * PP + o[c]];
+            zc[c][f] = cur[f * PP + o[c]];
+        }
     for (int k = kb; k < ke; k++) {
-        const int q = k - kb + 2;  // raw plane k+1 (3-D)
+        const int q = k - kb + 2;  // raw plane k+1
         double pw[2][NPW];
 #pragma unroll
         for (int c = 0; c < 2; c++) {
@@ -193,35 +181,32 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
             for (int v = 0; v < NPW; v++) pw[c][v] = pwn[c][v];
             if (act[c] && k + 1 < ke) op.pw_load(n[c] + g.sz, pwn[c]);
         }
-        const double* nxt = cur;
-        if (D3) nxt = wait_q(q);
+        const double* nxt = wait_q(q);
 #pragma unroll
         for (int c = 0; c < 2; c++) {
+            St<NF> s;
 #pragma unroll
             for (int f = 0; f < NF; f++) {
                 const double* pl = cur + f * PP + o[c];
-                if (D3) s[c].p[f] = nxt[f * PP + o[c]];
-                s[c].e[f] = pl[1];
-                s[c].w[f] = pl[-1];
-                s[c].n[f] = pl[HX];
-                s[c].s[f] = pl[-HX];
+                s.m[f] = zm[c][f];
+                s.c[f] = zc[c][f];
+                s.p[f] = nxt[f * PP + o[c]];
+                s.e[f] = pl[1];
+                s.w[f] = pl[-1];
+                s.n[f] = pl[HX];
+                s.s[f] = pl[-HX];
+                zm[c][f] = s.c[f];
+                zc[c][f] = s.p[f];
             }
-            if (act[c]) op.cell(s[c], pw[c], n[c], i, j[c], k);
-#pragma unroll
-            for (int f = 0; f < NF; f++) {
-                s[c].m[f] = s[c].c[f];
-                s[c].c[f] = s[c].p[f];
-            }
+            if (act[c]) op.cell(s, pw[c], n[c], i, j[c], k);
             n[c] += g.sz;
         }
-        if (D3) {
-            __syncthreads();  // every thread is done with shared plane k (stage of q-1) and older
-            if (tid == 0) {
-                fence_proxy_async();
-                while (next_q < np && next_q - ST <= q - 1) issue(next_q++);
-            }
-            cur = nxt;
+        __syncthreads();  // every thread is done with shared plane k (stage of q-1) and older
+        if (tid == 0) {
+            fence_proxy_async();
+            while (next_q < np && next_q - ST <= q - 1) issue(next_q++);
         }
+        cur = nxt;
     }
 }
 

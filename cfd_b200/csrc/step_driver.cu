@@ -202,19 +202,25 @@ cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* pr
         ra.wrap_y = wrap_y;
         ra.wrap_z = wrap_z;
         ra.src_decay = exp(-prm->source_decay_rate * iter * dt);
+        // stage inputs carry their periodic images on the boundary cells (the TMA stage kernel reads
+        // plain halos; the reference reads wrapped indices -- same values)
+        launch_periodic_faces(L, Aq, 4, wrap_y, wrap_z);
         if (R > 1) halo_exchange(s, Aq, 4, true);
         if (order == 4) {
             // stage 1: k1 = f(Q0); acc = k1; B = Q0 + dt/2 k1
             ra.first = 1; ra.last = 0; ra.fac_next = 0.5 * dt; ra.w_k = 1.0;
             launch_rk_stage(L, c, ra, P(Aq), P(Aq), W(ACC), W(B), s->rho, s->T, s->su_tab, s->sv_tab);
+            launch_periodic_faces(L, B, 4, wrap_y, wrap_z);
             if (R > 1) halo_exchange(s, B, 4, true);
             // stage 2: k2 = f(B); acc += 2 k2; C = Q0 + dt/2 k2
             ra.first = 0; ra.w_k = 2.0;
             launch_rk_stage(L, c, ra, P(B), P(Aq), W(ACC), W(C), s->rho, s->T, s->su_tab, s->sv_tab);
+            launch_periodic_faces(L, C, 4, wrap_y, wrap_z);
             if (R > 1) halo_exchange(s, C, 4, true);
             // stage 3: k3 = f(C); acc += 2 k3; B = Q0 + dt k3
             ra.fac_next = dt;
             launch_rk_stage(L, c, ra, P(C), P(Aq), W(ACC), W(B), s->rho, s->T, s->su_tab, s->sv_tab);
+            launch_periodic_faces(L, B, 4, wrap_y, wrap_z);
             if (R > 1) halo_exchange(s, B, 4, true);
             // stage 4: k4 = f(B); Q = Q0 + dt/6 (acc + k4)
             ra.last = 1; ra.w_final = dt / 6.0;
@@ -222,6 +228,7 @@ cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* pr
         } else {
             ra.first = 1; ra.last = 0; ra.fac_next = dt; ra.w_k = 1.0;
             launch_rk_stage(L, c, ra, P(Aq), P(Aq), W(ACC), W(B), s->rho, s->T, s->su_tab, s->sv_tab);
+            launch_periodic_faces(L, B, 4, wrap_y, wrap_z);
             if (R > 1) halo_exchange(s, B, 4, true);
             ra.first = 0; ra.last = 1; ra.w_final = 0.5 * dt;
             launch_rk_stage(L, c, ra, P(B), P(Aq), W(ACC), W(Aq), s->rho, s->T, s->su_tab, s->sv_tab);
@@ -234,7 +241,7 @@ cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* pr
         // apply_boundary_conditions: periodic wrap of u,v,w,p,rho,T (solver_explicit_euler.c:231-314)
         double* all[6] = {s->u, s->v, s->w, s->p, s->rho, s->T};
         const int nall = s->T ? 6 : 5;  // a T that never reached the device stays on the host untouched
-        for (int q = 0; q < nall; q++) launch_periodic_bc(L, all[q], wrap_y, wrap_z);
+        launch_periodic_faces(L, all, nall, wrap_y, wrap_z);
         if (R > 1) halo_exchange(s, all, nall, true);
         if (energy) launch_thermal_bc(s->L(), prm->thermal_bc, s->T);
         int bad = 0;
