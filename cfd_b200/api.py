@@ -165,6 +165,13 @@ class Session:
     def download(self, field, mask=FM_ALL):
         check(self.L.cfd_b200_session_download_mask(self.h, C.byref(field.c), mask), "session_download")
 
+    def set_coords(self, x=None, y=None):
+        """Exact cell coordinates of this slab (slices of the global grid arrays)."""
+        self._xy = (np.ascontiguousarray(x, dtype=np.float64) if x is not None else None,
+                    np.ascontiguousarray(y, dtype=np.float64) if y is not None else None)
+        check(self.L.cfd_b200_session_set_coords(self.h, abi._ptr(self._xy[0]) if x is not None else None,
+                                                 abi._ptr(self._xy[1]) if y is not None else None), "set_coords")
+
     def init_synthetic(self, seed=12345, global_k0=0, global_nz=None):
         check(self.L.cfd_b200_session_init_synthetic(self.h, seed, global_k0,
                                                      global_nz or self.desc.nz), "init_synthetic")

@@ -169,6 +169,10 @@ cfd_status_t cfd_b200_session_init_comm(cfd_b200_session_t* s, const char* nccl_
     return CFD_SUCCESS;
 }
 
+cfd_status_t cfd_b200_session_set_coords(cfd_b200_session_t* s, const double* x, const double* y) {
+    if (!s) return CFD_ERROR_INVALID;
+    return session_set_coords(s, x, y);
+}
 cfd_status_t cfd_b200_session_upload(cfd_b200_session_t* s, const flow_field* host) {
     return session_upload(s, host, FM_ALL);
 }

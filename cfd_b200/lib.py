@@ -73,6 +73,7 @@ def load():
     proto("cfd_b200_session_upload_mask", i32, [vp, FF, i32])
     proto("cfd_b200_session_download_mask", i32, [vp, FF, i32])
     proto("cfd_b200_session_init_synthetic", i32, [vp, C.c_uint64, C.c_size_t, C.c_size_t])
+    proto("cfd_b200_session_set_coords", i32, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)])
     proto("cfd_b200_session_projection", i32, [vp, NP, PC, i32, NS])
     proto("cfd_b200_session_rk", i32, [vp, i32, NP, i32, NS])
     proto("cfd_b200_session_poisson", i32, [vp, PC, PS])
@@ -104,7 +105,7 @@ DECLARED_SYMBOLS = [
     "cfd_b200_session_create", "cfd_b200_session_destroy", "cfd_b200_nccl_unique_id",
     "cfd_b200_session_init_comm", "cfd_b200_session_upload", "cfd_b200_session_download",
     "cfd_b200_session_upload_mask", "cfd_b200_session_download_mask",
-    "cfd_b200_session_init_synthetic", "cfd_b200_session_projection", "cfd_b200_session_rk",
+    "cfd_b200_session_init_synthetic", "cfd_b200_session_set_coords", "cfd_b200_session_projection", "cfd_b200_session_rk",
     "cfd_b200_session_poisson", "cfd_b200_session_upload_poisson", "cfd_b200_session_download_poisson",
     "cfd_b200_session_last_poisson_stats", "cfd_b200_session_profile", "cfd_b200_session_kernel_stats",
     "cfd_b200_session_reset_kernel_stats", "cfd_b200_session_stream", "cfd_b200_session_sync",

@@ -431,6 +431,11 @@ CFD_B200_API cfd_status_t cfd_b200_session_upload_mask(cfd_b200_session_t* s, co
 CFD_B200_API cfd_status_t cfd_b200_session_download_mask(cfd_b200_session_t* s, flow_field* host, int mask);
 /* Fill the device fields with the deterministic synthetic state of SURVEY 8(d) config C5
  * (sinusoidal velocity + splitmix64 perturbation); no host traffic. */
+/* Cell coordinates x[nx], y[ny] of this slab for the default source term (A_u sin(pi y) ...,
+ * cpu/solver_explicit_euler.c:326-331).  Default: xmin + i*dx, ymin + j*dy; a decomposed run
+ * passes the slice of the GLOBAL grid arrays so every rank sees bit-identical coordinates. */
+CFD_B200_API cfd_status_t cfd_b200_session_set_coords(cfd_b200_session_t* s, const double* x, const double* y);
+
 CFD_B200_API cfd_status_t cfd_b200_session_init_synthetic(cfd_b200_session_t* s, uint64_t seed,
                                                           size_t global_k0, size_t global_nz);
 

@@ -58,6 +58,12 @@ def main():
         s = api.Session(lg.nx, lg.ny, lg.nz, dx, dy, dz, float(lg.x[0]), float(lg.y[0]),
                         float(lg.z[0]) if nzg > 1 else 0.0, rank=rank, nranks=world, device=local)
         dist.attach_comm(s, rank, world)
+        # bit-identical coordinates on every rank: the slice of the GLOBAL grid arrays
+        if nzg > 1:
+            s.set_coords(g.x, g.y)
+        else:
+            lo, hi = dist.slab_range(ny, world, rank)
+            s.set_coords(g.x, g.y[lo:hi])
         s.upload(loc)
         if stepper == "projection":
             rc, _ = s.projection(p, pc, nsteps)

@@ -38,7 +38,8 @@ def main():
         p.alpha, p.beta, p.T_ref = 3.035e-2, 3.333e-3, 300.0
         p.gravity[1] = -9.81
         p.dt = 2.5e-7
-    pc = abi.poisson_config(a.method, max_iterations=a.iters, on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
+    pc = abi.poisson_config(a.method, max_iterations=a.iters, tolerance=0.0, absolute_tolerance=0.0,
+                            on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
 
     def run(k):
         if a.stepper == "projection":
