@@ -114,6 +114,7 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
 // operation order as k_rk_stage above.
 // ---------------------------------------------------------------------------------------
 struct RkOp {
+    static constexpr bool PRODUCER_WARP = false;  // needs > 96 registers: 512-thread variant of the pipeline
     static constexpr int NF = 4, NPW = 2;  // prefetched pointwise operands: rho, T (Q0, acc are loaded in cell())
     const Geom& g;
     const NsConst& c;
@@ -140,14 +141,14 @@ struct RkOp {
         double d1[4][3], d2[3][3];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-            const double cc = s.c[q];
-            d1[q][0] = clampv(100.0, ediv(s.e[q] - s.w[q], g.two_dx, g.inv_2dx));
-            d1[q][1] = clampv(100.0, ediv(s.n[q] - s.s[q], g.two_dy, g.inv_2dy));
-            d1[q][2] = clampv(100.0, (s.p[q] - s.m[q]) * g.inv_2dz);
+            const double cc = s.c(q);
+            d1[q][0] = clampv(100.0, ediv(s.e(q) - s.w(q), g.two_dx, g.inv_2dx));
+            d1[q][1] = clampv(100.0, ediv(s.n(q) - s.s(q), g.two_dy, g.inv_2dy));
+            d1[q][2] = clampv(100.0, (s.p(q) - s.m(q)) * g.inv_2dz);
             if (q < 3) {
-                d2[q][0] = clampv(1000.0, ediv(s.e[q] - 2.0 * cc + s.w[q], g.dx2, g.inv_dx2));
-                d2[q][1] = clampv(1000.0, ediv(s.n[q] - 2.0 * cc + s.s[q], g.dy2, g.inv_dy2));
-                d2[q][2] = clampv(1000.0, (s.p[q] - 2.0 * cc + s.m[q]) * g.inv_dz2);
+                d2[q][0] = clampv(1000.0, ediv(s.e(q) - 2.0 * cc + s.w(q), g.dx2, g.inv_dx2));
+                d2[q][1] = clampv(1000.0, ediv(s.n(q) - 2.0 * cc + s.s(q), g.dy2, g.inv_dy2));
+                d2[q][2] = clampv(1000.0, (s.p(q) - 2.0 * cc + s.m(q)) * g.inv_dz2);
             }
         }
         const double rh = pw[0];
@@ -161,7 +162,7 @@ struct RkOp {
                 fv += -c.beta * dT * c.gy;
                 fw += -c.beta * dT * c.gz;
             }
-            const double uc = s.c[0], vc = s.c[1], wc = s.c[2];
+            const double uc = s.c(0), vc = s.c(1), wc = s.c(2);
             const double src[3] = {fu, fv, fw};
 #pragma unroll
             for (int q = 0; q < 3; q++)
@@ -172,7 +173,7 @@ struct RkOp {
         }
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-            const double base = ra.first ? s.c[q] : b0[q];
+            const double base = ra.first ? s.c(q) : b0[q];
             double out;
             if (ra.last) {
                 const double a_ = ra.first ? 0.0 : a0[q];

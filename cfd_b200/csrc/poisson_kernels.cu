@@ -255,6 +255,21 @@ __device__ __forceinline__ void pointwise_rows(const Geom& g, int rpb, F f) {
     }
 }
 
+// Pointwise sweep over the interior cells: 3-D grids keep the z-marching column layout of the
+// stencil kernels (all blocks stream the same few planes at a time -- measured 10 % faster than
+// row chunks at 512^3, fewer concurrent DRAM streams); 2-D grids use row chunks.
+template <bool D3, class F>
+__device__ __forceinline__ void pointwise_cells(const Geom& g, int chunk, F f) {
+    if (D3) {
+        int i, j, kb, ke;
+        if (!column(g, chunk, i, j, kb, ke)) return;
+        long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+        for (int k = kb; k < ke; k++, n += g.sz) f(n);
+    } else {
+        pointwise_rows(g, chunk, f);
+    }
+}
+
 // =======================================================================================
 // Krylov solvers.  A = -lap on interior cells; r, p, v, s, t keep ZERO on physical boundary
 // cells (never written), exactly as the reference's calloc'ed work vectors.
@@ -433,7 +448,7 @@ k_cg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const double
     }
     const double alpha = ctl->dot[2 * par + precond] / pAp;
     double acc[2] = {0.0, 0.0};
-    pointwise_rows(g, a.zchunk, [&](long long n) {
+    pointwise_cells<D3>(g, a.zchunk, [&](long long n) {
         x[n] += alpha * __ldg(p + n);
         const double rv = r[n] - alpha * __ldg(Ap + n);
         r[n] = rv;
@@ -603,9 +618,9 @@ k_bicg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const doub
     const double omega = (mode == 0) ? ctl->dot[8 + 4 * par + 1] / tt : 0.0;
     double acc[2] = {0.0, 0.0};
     if (mode == 1) {
-        pointwise_rows(g, a.zchunk, [&](long long n) { x[n] += alpha * __ldg(p + n); });
+        pointwise_cells<D3>(g, a.zchunk, [&](long long n) { x[n] += alpha * __ldg(p + n); });
     } else {
-        pointwise_rows(g, a.zchunk, [&](long long n) {
+        pointwise_cells<D3>(g, a.zchunk, [&](long long n) {
             const double sv = __ldg(s + n);
             x[n] += alpha * __ldg(p + n) + omega * sv;
             const double rv = sv - omega * __ldg(t + n);
@@ -666,7 +681,7 @@ void launch_jacobi(const LaunchCtx& L, const KArgs& a0, const double* xin, doubl
             static bool once = (tma_optin(k_jacobi_tma<true, true>, SM), tma_optin(k_jacobi_tma<true, false>, SM),
                                 tma_optin(k_jacobi_tma<false, true>, SM), tma_optin(k_jacobi_tma<false, false>, SM), true);
             (void)once;
-#define CFDB_JACT(D3, RES) CFDB_LAUNCH(KK_JACOBI, L.st, (k_jacobi_tma<D3, RES><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, xout, rhs, L.ctl, L.rb, at)))
+#define CFDB_JACT(D3, RES) CFDB_LAUNCH(KK_JACOBI, L.st, (k_jacobi_tma<D3, RES><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, xout, rhs, L.ctl, L.rb, at)))
             if (L.g.dim3) { if (res) CFDB_JACT(true, true); else CFDB_JACT(true, false); }
             else { if (res) CFDB_JACT(false, true); else CFDB_JACT(false, false); }
 #undef CFDB_JACT
@@ -688,8 +703,8 @@ void launch_redblack(const LaunchCtx& L, const KArgs& a0, double* x, const doubl
             constexpr size_t SM = DirectPipe<1>::SMEM;
             static bool once = (tma_optin(k_redblack_tma<true>, SM), tma_optin(k_redblack_tma<false>, SM), true);
             (void)once;
-            if (L.g.dim3) CFDB_LAUNCH(KK_REDBLACK, L.st, (k_redblack_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, x, rhs, L.ctl, at, colour, decide)));
-            else CFDB_LAUNCH(KK_REDBLACK, L.st, (k_redblack_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, x, rhs, L.ctl, at, colour, decide)));
+            if (L.g.dim3) CFDB_LAUNCH(KK_REDBLACK, L.st, (k_redblack_tma<true><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, x, rhs, L.ctl, at, colour, decide)));
+            else CFDB_LAUNCH(KK_REDBLACK, L.st, (k_redblack_tma<false><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, x, rhs, L.ctl, at, colour, decide)));
             return;
         }
     }
@@ -707,8 +722,8 @@ void launch_linf_residual(const LaunchCtx& L, const KArgs& a0, const double* x, 
             constexpr size_t SM = DirectPipe<1>::SMEM;
             static bool once = (tma_optin(k_linf_residual_tma<true>, SM), tma_optin(k_linf_residual_tma<false>, SM), true);
             (void)once;
-            if (L.g.dim3) CFDB_LAUNCH(KK_LINF, L.st, (k_linf_residual_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhs, L.ctl, L.rb, at, slot)));
-            else CFDB_LAUNCH(KK_LINF, L.st, (k_linf_residual_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhs, L.ctl, L.rb, at, slot)));
+            if (L.g.dim3) CFDB_LAUNCH(KK_LINF, L.st, (k_linf_residual_tma<true><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, rhs, L.ctl, L.rb, at, slot)));
+            else CFDB_LAUNCH(KK_LINF, L.st, (k_linf_residual_tma<false><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, rhs, L.ctl, L.rb, at, slot)));
             return;
         }
     }
@@ -730,8 +745,8 @@ void launch_krylov_init(const LaunchCtx& L, const KArgs& a0, const double* x, co
             constexpr size_t SM = DirectPipe<1>::SMEM;
             static bool once = (tma_optin(k_krylov_init_tma<true>, SM), tma_optin(k_krylov_init_tma<false>, SM), true);
             (void)once;
-            if (L.g.dim3) CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, (k_krylov_init_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhs, r, p0, rhat, L.ctl, L.rb, at, precond)));
-            else CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, (k_krylov_init_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhs, r, p0, rhat, L.ctl, L.rb, at, precond)));
+            if (L.g.dim3) CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, (k_krylov_init_tma<true><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, rhs, r, p0, rhat, L.ctl, L.rb, at, precond)));
+            else CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, (k_krylov_init_tma<false><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, rhs, r, p0, rhat, L.ctl, L.rb, at, precond)));
             return;
         }
     }
@@ -762,9 +777,13 @@ void launch_cg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const d
 }
 void launch_cg_update(const LaunchCtx& L, const KArgs& a0, double* x, double* r, const double* p,
                       const double* Ap, int precond) {
-    KArgs a = a0;
-    const dim3 gr = pw_grid(L, a.zchunk);
-    CFDB_LAUNCH(KK_CG_UPDATE, L.st, k_cg_update<true><<<gr, PW_THREADS, 0, L.st>>>(L.g, x, r, p, Ap, L.ctl, L.rb, a, precond));
+    KArgs a = with_chunk(L, a0);
+    if (L.g.dim3) {
+        CFDB_LAUNCH(KK_CG_UPDATE, L.st, k_cg_update<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, Ap, L.ctl, L.rb, a, precond));
+    } else {
+        const dim3 gr = pw_grid(L, a.zchunk);
+        CFDB_LAUNCH(KK_CG_UPDATE, L.st, k_cg_update<false><<<gr, PW_THREADS, 0, L.st>>>(L.g, x, r, p, Ap, L.ctl, L.rb, a, precond));
+    }
 }
 void launch_bicg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const double* pold,
                      const double* vold, const double* rhat, double* pnew, double* vnew, int first,
@@ -810,9 +829,13 @@ void launch_bicg_s(const LaunchCtx& L, const KArgs& a0, const double* r, const d
 }
 void launch_bicg_update(const LaunchCtx& L, const KArgs& a0, double* x, double* r, const double* p,
                         const double* s, const double* t, const double* rhat) {
-    KArgs a = a0;
-    const dim3 gr = pw_grid(L, a.zchunk);
-    CFDB_LAUNCH(KK_BICG_UPDATE, L.st, k_bicg_update<true><<<gr, PW_THREADS, 0, L.st>>>(L.g, x, r, p, s, t, rhat, L.ctl, L.rb, a));
+    KArgs a = with_chunk(L, a0);
+    if (L.g.dim3) {
+        CFDB_LAUNCH(KK_BICG_UPDATE, L.st, k_bicg_update<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, r, p, s, t, rhat, L.ctl, L.rb, a));
+    } else {
+        const dim3 gr = pw_grid(L, a.zchunk);
+        CFDB_LAUNCH(KK_BICG_UPDATE, L.st, k_bicg_update<false><<<gr, PW_THREADS, 0, L.st>>>(L.g, x, r, p, s, t, rhat, L.ctl, L.rb, a));
+    }
 }
 
 }  // namespace cfdb

@@ -5,10 +5,14 @@
 // by the TMA unit).  For plane k a thread takes the in-plane neighbours of its 2 cells from the
 // shared plane k, the z neighbours from registers (plane k-1, k) and from the freshly landed
 // plane k+1.  Pointwise operands (centre only: rhs, u*, ...) are plain loads issued one plane
-// ahead.  One __syncthreads per plane retires plane k; thread 0 refills the stage at once.
+// ahead.  There is no block-wide barrier in the loop: a 17th warp is the PRODUCER (waits on the
+// stage's empty-barrier, re-arms the full-barrier, issues the TMA boxes), the 16 consumer warps
+// release a stage with one mbarrier arrive each, so warps drift apart by up to ST planes and
+// absorb each other's latency.
 //
 // The functor supplies the arithmetic:
 //   static constexpr int NF, NPW;                                 // NPW >= 1 (a dummy if none)
+//   static constexpr bool PRODUCER_WARP;                          // 544-thread launch (regs <= 96) or 512 (<= 128)
 //   void pw_load(long long n, double (&pw)[NPW]) const;          // pointwise operands of cell n
 //   void cell(const St<NF>& s, const double (&pw)[NPW], long long n, int i, int j, int k);
 #pragma once
@@ -17,16 +21,27 @@
 
 namespace cfdb {
 
+// Stencil values of NF fields at one cell: centre and z neighbours live in registers, the four
+// in-plane neighbours are read from the shared plane at the point of use (keeps the register
+// footprint of the multi-field kernels down).
 template <int NF>
-struct St {  // stencil values of NF fields at one cell
-    double c[NF], e[NF], w[NF], n[NF], s[NF], m[NF], p[NF];  // centre, x+1, x-1, y+1, y-1, z-1, z+1
+struct St {
+    const double* pl;     // own cell of field 0 in the shared plane k; field f at pl + f * PLANE_PAD
+    double zc[NF], zm[NF], zp[NF];
+    __device__ __forceinline__ double c(int f) const { return zc[f]; }
+    __device__ __forceinline__ double m(int f) const { return zm[f]; }
+    __device__ __forceinline__ double p(int f) const { return zp[f]; }
+    __device__ __forceinline__ double e(int f) const { return pl[f * Tile::PLANE_PAD + 1]; }
+    __device__ __forceinline__ double w(int f) const { return pl[f * Tile::PLANE_PAD - 1]; }
+    __device__ __forceinline__ double n(int f) const { return pl[f * Tile::PLANE_PAD + Tile::HX]; }
+    __device__ __forceinline__ double s(int f) const { return pl[f * Tile::PLANE_PAD - Tile::HX]; }
 };
 
 template <int NF>
 struct DirectPipe {
     static constexpr int ST = (NF == 1) ? 6 : (NF == 2 ? 4 : 3);
     static constexpr int RING = ST * NF * Tile::PLANE_PAD;
-    static constexpr size_t SMEM = (size_t)RING * sizeof(double) + ST * sizeof(uint64_t);
+    static constexpr size_t SMEM = (size_t)RING * sizeof(double) + 2 * ST * sizeof(uint64_t);  // ring + full[] + empty[]
 };
 
 #ifdef __CUDACC__
@@ -37,7 +52,7 @@ struct DirectPipe {
 template <class Op>
 __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, const Geom& g, int ychunk, Op& op) {
     constexpr int NF = Op::NF, NPW = Op::NPW, ST = DirectPipe<NF>::ST;
-    constexpr int HX = Tile::HX, PP = Tile::PLANE_PAD;
+    constexpr int PP = Tile::PLANE_PAD;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double* ring = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(ring + DirectPipe<NF>::RING);
@@ -46,12 +61,17 @@ __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, co
     const int tiles_y = (g.ny - 2 + Tile::BY - 1) / Tile::BY;
     const int ty0 = blockIdx.y * ychunk;
     const int nt = min(ychunk, tiles_y - ty0);
+    uint64_t* empty = full + ST;
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < ST; s++) mbar_init(&full[s], 1);
+        for (int s = 0; s < ST; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], Tile::WARPS);
+        }
         mbar_fence_init();
     }
     __syncthreads();
+    constexpr bool PWARP = Op::PRODUCER_WARP;
     int next_q = 0;
     auto issue = [&](int q) {
         const int slot = q % ST;
@@ -60,8 +80,20 @@ __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, co
         for (int f = 0; f < NF; f++)
             tma_load_plane(ring + (slot * NF + f) * PP, &tm.m[f], x0, (ty0 + q) * Tile::BY, 0, &full[slot]);
     };
-    if (tid == 0)
+    if (PWARP) {
+        if (tid >= Tile::THREADS) {  // producer warp
+            if (tid == Tile::THREADS) {
+                for (int q = 0; q < nt; q++) {
+                    if (q >= ST) mbar_wait(&empty[q % ST], ((q / ST) - 1) & 1);
+                    issue(q);
+                }
+            }
+            return;
+        }
+    } else if (tid == 0) {
         for (; next_q < ST && next_q < nt; next_q++) issue(next_q);
+    }
+    const int lane = tid & 31;
     const int lx = tid & (Tile::BX - 1), ly = tid >> 6;
     const int i = x0 + 1 + lx;
     const bool actx = i < g.nx - 1;
@@ -89,22 +121,23 @@ __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, co
             const int j = jrow(t, c);
             if (!(actx && j < g.ny - 1)) continue;
             St<NF> s;
+            s.pl = cur + o[c];
 #pragma unroll
             for (int f = 0; f < NF; f++) {
-                const double* pl = cur + f * PP + o[c];
-                s.c[f] = pl[0];
-                s.e[f] = pl[1];
-                s.w[f] = pl[-1];
-                s.n[f] = pl[HX];
-                s.s[f] = pl[-HX];
-                s.m[f] = s.p[f] = 0.0;
+                s.zc[f] = s.pl[f * PP];
+                s.zm[f] = s.zp[f] = 0.0;
             }
             op.cell(s, pw[c], (long long)j * g.sy + i, i, j, 0);
         }
-        __syncthreads();
-        if (tid == 0) {
-            fence_proxy_async();
-            while (next_q < nt && next_q - ST <= t) issue(next_q++);
+        if (PWARP) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[slot]);
+        } else {
+            __syncthreads();  // tile t is consumed: its stage may be refilled
+            if (tid == 0) {
+                fence_proxy_async();
+                while (next_q < nt && next_q - ST <= t) issue(next_q++);
+            }
         }
     }
 }
@@ -125,12 +158,17 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
     const int kb = g.k0 + blockIdx.z * zchunk, ke = min(kb + zchunk, g.k1);
     const int np = ke - kb + 2;  // planes kb-1 .. ke
     const int pz0 = kb - 1;
+    uint64_t* empty = full + ST;
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < ST; s++) mbar_init(&full[s], 1);
+        for (int s = 0; s < ST; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], Tile::WARPS);
+        }
         mbar_fence_init();
     }
     __syncthreads();
+    constexpr bool PWARP = Op::PRODUCER_WARP;  // false: 512 threads, thread 0 refills after a block barrier
     int next_q = 0;
     auto issue = [&](int q) {
         const int slot = q % ST;
@@ -139,8 +177,20 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
         for (int f = 0; f < NF; f++)
             tma_load_plane(ring + (slot * NF + f) * PP, &tm.m[f], x0, y0, pz0 + q, &full[slot]);
     };
-    if (tid == 0)
+    if (PWARP) {
+        if (tid >= Tile::THREADS) {  // producer warp
+            if (tid == Tile::THREADS) {
+                for (int q = 0; q < np; q++) {
+                    if (q >= ST) mbar_wait(&empty[q % ST], ((q / ST) - 1) & 1);  // all 16 warps left its previous plane
+                    issue(q);
+                }
+            }
+            return;
+        }
+    } else if (tid == 0) {
         for (; next_q < ST && next_q < np; next_q++) issue(next_q);
+    }
+    const int lane = tid & 31;
     const int lx = tid & (Tile::BX - 1), ly = tid >> 6;
     const int i = x0 + 1 + lx;
     int o[2], j[2];
@@ -172,6 +222,10 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
             zm[c][f] = p0[f * PP + o[c]];
             zc[c][f] = cur[f * PP + o[c]];
         }
+    if (PWARP) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[0]);  // plane kb-1 only fed the registers
+    }
     for (int k = kb; k < ke; k++) {
         const int q = k - kb + 2;  // raw plane k+1
         double pw[2][NPW];
@@ -185,26 +239,27 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
 #pragma unroll
         for (int c = 0; c < 2; c++) {
             St<NF> s;
+            s.pl = cur + o[c];
 #pragma unroll
             for (int f = 0; f < NF; f++) {
-                const double* pl = cur + f * PP + o[c];
-                s.m[f] = zm[c][f];
-                s.c[f] = zc[c][f];
-                s.p[f] = nxt[f * PP + o[c]];
-                s.e[f] = pl[1];
-                s.w[f] = pl[-1];
-                s.n[f] = pl[HX];
-                s.s[f] = pl[-HX];
-                zm[c][f] = s.c[f];
-                zc[c][f] = s.p[f];
+                s.zm[f] = zm[c][f];
+                s.zc[f] = zc[c][f];
+                s.zp[f] = nxt[f * PP + o[c]];
+                zm[c][f] = s.zc[f];
+                zc[c][f] = s.zp[f];
             }
             if (act[c]) op.cell(s, pw[c], n[c], i, j[c], k);
             n[c] += g.sz;
         }
-        __syncthreads();  // every thread is done with shared plane k (stage of q-1) and older
-        if (tid == 0) {
-            fence_proxy_async();
-            while (next_q < np && next_q - ST <= q - 1) issue(next_q++);
+        if (PWARP) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[(q - 1) % ST]);  // this warp is done with shared plane k
+        } else {
+            __syncthreads();  // every thread is done with shared plane k (stage of q-1) and older
+            if (tid == 0) {
+                fence_proxy_async();
+                while (next_q < np && next_q - ST <= q - 1) issue(next_q++);
+            }
         }
         cur = nxt;
     }

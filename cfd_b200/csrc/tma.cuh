@@ -21,6 +21,8 @@ struct Tile {
     static constexpr int PLANE_PAD = 1200;            // padded so every plane starts 128-B aligned
     static constexpr int PLANE_BYTES = PLANE * 8;     // bytes the TMA delivers per operand plane
     static constexpr int THREADS = 512;               // 2 cells per thread: rows ly and ly + 8
+    static constexpr int WARPS = THREADS / 32;
+    static constexpr int THREADS_PW = THREADS + 32;   // + one producer warp (stencil_tma.cuh)
     __host__ __device__ static constexpr int OWN0(int lx, int ly) { return (ly + 1) * HX + lx + 1; }
 };
 static_assert((Tile::HX * 8) % 16 == 0, "TMA box rows must be a multiple of 16 bytes");
@@ -48,6 +50,9 @@ __device__ __forceinline__ void mbar_fence_init() {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     asm volatile(
