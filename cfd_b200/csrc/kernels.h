@@ -13,9 +13,10 @@ namespace cfdb {
 struct TmaCache {
     int nx = 0, ny = 0, nz = 0;
     bool usable = false;
-    std::unordered_map<const double*, CUtensorMap> maps;
+    std::unordered_map<const double*, CUtensorMap> maps, wide_maps;
     void configure(const Geom& g);
     const CUtensorMap* get(const double* p);   // nullptr => take the direct (non-TMA) kernel
+    const CUtensorMap* get_wide(const double* p);  // {BX+6, BY+4, 1} box (two-cell halo, even x start) for the fused sweeps
 };
 
 // Everything a launcher needs besides the per-kernel operands.
@@ -36,7 +37,7 @@ enum KernelKind {
     KK_NEUMANN = 0, KK_JACOBI, KK_REDBLACK, KK_LINF, KK_STAT_FINAL, KK_KRYLOV_INIT, KK_CG_DIR,
     KK_CG_UPDATE, KK_BICG_DIR, KK_BICG_S, KK_BICG_UPDATE, KK_PREDICTOR, KK_DIVERGENCE,
     KK_CORRECTOR, KK_THERMAL_BC, KK_PERIODIC_BC, KK_RK_STAGE, KK_FIELD_STATS, KK_SYNTH_INIT,
-    KK_COPY, KK_EULER, KK_BOUNDARY, KK_COUNT
+    KK_COPY, KK_EULER, KK_BOUNDARY, KK_FILL, KK_CTL_RESET, KK_RBSOR_FUSED, KK_COUNT
 };
 extern const char* const kKernelNames[KK_COUNT];
 extern const double kKernelBytesPerCell[KK_COUNT];
@@ -62,6 +63,9 @@ extern thread_local Profiler* t_prof;
 void launch_neumann_fill(const LaunchCtx& L, double* x, int seq, int honour_skip, bool use_ctl);
 void launch_jacobi(const LaunchCtx& L, const KArgs& a, const double* xin, double* xout, const double* rhs);
 void launch_redblack(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs, int colour, int decide);
+bool rbsor_fused_available(const LaunchCtx& L);
+// whole Red-Black SOR iteration x_q -> x_{q+1} out of place (+ res(x_q)); false => not launched, use the half-sweeps
+bool launch_rbsor_fused(const LaunchCtx& L, const KArgs& a, const double* xin, double* xout, const double* rhs);
 void launch_linf_residual(const LaunchCtx& L, const KArgs& a, const double* x, const double* rhs, int slot);
 void launch_stationary_final(const LaunchCtx& L, const KArgs& a);
 void launch_krylov_init(const LaunchCtx& L, const KArgs& a, const double* x, const double* rhs, double* r,

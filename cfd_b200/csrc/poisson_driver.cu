@@ -92,6 +92,12 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
     const int method = cfg->method;
     cfd_status_t rc = CFD_SUCCESS;
 
+    // the one-pass Red-Black SOR iteration is out of place: it needs the ping-pong partner as well
+    // (no memory for it => the in-place half-sweeps below)
+    if (method == POISSON_METHOD_REDBLACK_SOR && R == 1 && pxt && !*pxt && rbsor_fused_available(L) &&
+        dalloc(s, pxt) != CFD_SUCCESS)
+        *pxt = nullptr;
+
     if (method == POISSON_METHOD_JACOBI) {
         if (!pxt || !*pxt) return CFD_ERROR_INVALID;
         double* buf[2] = {x, *pxt};
@@ -114,6 +120,26 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         launch_stationary_final(L, a);
         const Ctl& c = poll.final_state();
         if (c.result_buf == 1) {  // x lives in the ping-pong partner: swap the caller's pointers
+            *px = buf[1];
+            *pxt = buf[0];
+        }
+    } else if (method == POISSON_METHOD_REDBLACK_SOR && R == 1 && pxt && *pxt && rbsor_fused_available(L) &&
+               L.tc->get_wide(x) && L.tc->get_wide(*pxt) && L.tc->get(rhs)) {
+        // one pass per iteration, same protocol as Jacobi: sweep q reads x_q, writes x_{q+1}, leaves res(x_q)
+        double* buf[2] = {x, *pxt};
+        for (int q = 0; q <= a.max_iter;) {
+            for (int b = 0; b < B && q <= a.max_iter; b++, q++) {
+                a.seq = seq++;
+                a.it = q;
+                if (!launch_rbsor_fused(L, a, buf[q & 1], buf[(q + 1) & 1], rhs)) return CFD_ERROR;
+            }
+            if (poll.step()) break;
+        }
+        a.seq = seq++;
+        a.it = a.max_iter;
+        launch_stationary_final(L, a);
+        const Ctl& c = poll.final_state();
+        if (c.result_buf == 1) {
             *px = buf[1];
             *pxt = buf[0];
         }

@@ -635,6 +635,7 @@ k_bicg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const doub
 
 #include "poisson_tma.inc"
 #include "poisson_tma2.inc"
+#include "poisson_tma3.inc"
 
 // =======================================================================================
 // Host launchers
@@ -693,6 +694,44 @@ void launch_jacobi(const LaunchCtx& L, const KArgs& a0, const double* xin, doubl
     else { if (res) CFDB_JAC(false, true); else CFDB_JAC(false, false); }
 #undef CFDB_JAC
 }
+// One-pass Red-Black SOR iteration (poisson_tma3.inc): 3-D, TMA-capable grids (nx even), single rank.
+bool rbsor_fused_available(const LaunchCtx& L) {
+    const bool off = getenv("CFD_B200_NO_RB_FUSED") != nullptr;  // read per solve: tests toggle it
+    return !off && L.g.dim3 && L.tc && L.tc->usable && L.g.glo[2] && L.g.ghi[2];
+}
+static int rbsor_fused_zchunk(const LaunchCtx& L, dim3& grid) {
+    const int nzi = L.g.k1 - L.g.k0;
+    const int gx = (L.g.nx - 2 + Tile::BX - 1) / Tile::BX, gy = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
+    static const int forced = getenv("CFD_B200_ZCHUNK_RB") ? atoi(getenv("CFD_B200_ZCHUNK_RB")) : 0;
+    // one block per SM (154 KB of shared memory): aim at >= 20 waves, 16..128 planes per block
+    int nch = (148 * 20 + gx * gy - 1) / (gx * gy);
+    int zc = (nzi + nch - 1) / nch;
+    zc = zc < 16 ? 16 : (zc > 128 ? 128 : zc);
+    if (forced > 0) zc = forced;
+    if (zc > nzi) zc = nzi;
+    grid = dim3(gx, gy, (nzi + zc - 1) / zc);
+    return zc;
+}
+bool launch_rbsor_fused(const LaunchCtx& L, const KArgs& a0, const double* xin, double* xout, const double* rhs) {
+    if (!rbsor_fused_available(L)) return false;
+    const CUtensorMap *mx = L.tc->get_wide(xin), *mr = L.tc->get(rhs);
+    if (!mx || !mr) return false;
+    TmaSet<2> tm;
+    tm.m[0] = *mx;
+    tm.m[1] = *mr;
+    KArgs at = a0;
+    dim3 grid;
+    at.zchunk = rbsor_fused_zchunk(L, grid);
+    if ((size_t)grid.x * grid.y * grid.z > L.rb_blocks) return false;
+    const bool res = (at.it == 0) || ((at.it - 1) % at.check == 0);
+    constexpr size_t SM = RbFused::SMEM;
+    static bool once = (tma_optin(k_rbsor_fused_tma<true>, SM), tma_optin(k_rbsor_fused_tma<false>, SM), true);
+    (void)once;
+    if (res) CFDB_LAUNCH(KK_RBSOR_FUSED, L.st, (k_rbsor_fused_tma<true><<<grid, RbFused::THREADS, SM, L.st>>>(tm, L.g, xout, L.ctl, L.rb, at)));
+    else CFDB_LAUNCH(KK_RBSOR_FUSED, L.st, (k_rbsor_fused_tma<false><<<grid, RbFused::THREADS, SM, L.st>>>(tm, L.g, xout, L.ctl, L.rb, at)));
+    return true;
+}
+
 void launch_redblack(const LaunchCtx& L, const KArgs& a0, double* x, const double* rhs, int colour, int decide) {
     {
         TmaSet<1> tm;

@@ -28,6 +28,20 @@ struct Tile {
 static_assert((Tile::HX * 8) % 16 == 0, "TMA box rows must be a multiple of 16 bytes");
 static_assert((Tile::PLANE_PAD * 8) % 128 == 0, "TMA destinations must stay 128-byte aligned");
 
+// Box with a TWO-cell halo, for sweeps that apply two dependent stencil stages per pass
+// (poisson_tma3.inc): stage 1 is evaluated on the HX x HY ring-extended tile, stage 2 on the tile.
+// The innermost start coordinate of a TMA box must be 16-byte aligned (FP64: EVEN -- an odd x
+// start raises "illegal instruction" on sm_100a, measured; negative starts are fine), so the box
+// starts THREE cells left of the first own cell and is BX + 6 wide.
+struct WideTile {
+    static constexpr int WX = Tile::BX + 6, WY = Tile::BY + 4;
+    static constexpr int XOFF = 3, YOFF = 2;       // own cell (lx, ly) sits at (ly + YOFF) * WX + lx + XOFF
+    static constexpr int PLANE = WX * WY;          // 1400 doubles
+    static constexpr int PLANE_PAD = 1408;         // 88 * 128 bytes
+    static constexpr int PLANE_BYTES = PLANE * 8;
+};
+static_assert((WideTile::WX * 8) % 16 == 0 && (WideTile::PLANE_PAD * 8) % 128 == 0, "wide box alignment");
+
 // Up to 4 tensor maps by value in kernel parameter space (must be __grid_constant__).
 template <int N>
 struct TmaSet {

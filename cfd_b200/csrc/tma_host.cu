@@ -24,14 +24,26 @@ static PFN_cuTensorMapEncodeTiled encode_fn() {
     return fn;
 }
 
+static const CUtensorMap* lookup(TmaCache& tc, std::unordered_map<const double*, CUtensorMap>& maps, const double* p,
+                                 int bx, int by);
+
 void TmaCache::configure(const Geom& g) {
     nx = g.nx; ny = g.ny; nz = g.nz;
     maps.clear();
+    wide_maps.clear();
     // TMA needs 16-byte global strides: nx even (the odd-nx grids, e.g. 129^2, take the direct kernels)
     usable = (nx % 2 == 0) && nx >= 4 && encode_fn() != nullptr && !getenv("CFD_B200_NO_TMA");
 }
 
-const CUtensorMap* TmaCache::get(const double* p) {
+const CUtensorMap* TmaCache::get(const double* p) { return lookup(*this, maps, p, Tile::HX, Tile::HY); }
+const CUtensorMap* TmaCache::get_wide(const double* p) {
+    return lookup(*this, wide_maps, p, WideTile::WX, WideTile::WY);
+}
+
+static const CUtensorMap* lookup(TmaCache& tc, std::unordered_map<const double*, CUtensorMap>& maps, const double* p,
+                                 int bx, int by) {
+    const int nx = tc.nx, ny = tc.ny, nz = tc.nz;
+    bool& usable = tc.usable;
     if (!usable || !p) return nullptr;
     auto it = maps.find(p);
     if (it != maps.end()) return &it->second;
@@ -39,7 +51,7 @@ const CUtensorMap* TmaCache::get(const double* p) {
     CUtensorMap m;
     const cuuint64_t dims[3] = {(cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)nz};
     const cuuint64_t strides[2] = {(cuuint64_t)nx * 8, (cuuint64_t)nx * ny * 8};
-    const cuuint32_t box[3] = {(cuuint32_t)Tile::HX, (cuuint32_t)Tile::HY, 1};
+    const cuuint32_t box[3] = {(cuuint32_t)bx, (cuuint32_t)by, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     CUresult r = encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, (void*)p, dims, strides, box, estr,
                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,

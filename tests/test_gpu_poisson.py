@@ -85,6 +85,27 @@ def test_poisson_matches_oracle(orc, shape, name):
         assert abs(st_g.final_residual - st_o.final_residual) <= 1e-6 * max(st_o.final_residual, pp.absolute_tolerance)
 
 
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("check", [1, 3])
+@pytest.mark.parametrize("shape", [(130, 40, 37), (66, 18, 21), (200, 52, 70), (64, 16, 150)])
+def test_rbsor_one_pass_iteration_is_bit_exact(orc, shape, check, fused, monkeypatch):
+    """3-D Red-Black SOR on TMA-capable grids runs one fused pass per iteration (both half-sweeps +
+    ghosts + residual, poisson_tma3.inc); multi-tile / multi-chunk shapes, capped iteration count.
+    fused=False forces the two half-sweep kernels on the same grids."""
+    if not fused:
+        monkeypatch.setenv("CFD_B200_NO_RB_FUSED", "1")
+    nx, ny, nz = shape
+    g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=11)
+    pp = pparams("rbsor", max_iterations=24, check_interval=check, tolerance=1e-30, absolute_tolerance=1e-300)
+    xo = x.copy()
+    dx, dy, dz = g.spacing
+    rc_o, st_o = orc.poisson(METH["rbsor"], nx, ny, nz, dx, dy, dz, pp, xo, rhs, np.zeros_like(x))
+    rc_g, st_g = gpu_solve("rbsor", g, x, rhs, pp)
+    assert (rc_g, st_g.status, st_g.iterations) == (rc_o, st_o.status, st_o.iterations)
+    assert st_g.initial_residual == st_o.initial_residual and st_g.final_residual == st_o.final_residual
+    assert np.array_equal(x, xo)
+
+
 @pytest.mark.parametrize("shape", [(33, 33, 1), (34, 20, 18), (129, 129, 1)])
 def test_bicgstab_default_tolerance(orc, shape):
     """Default 1e-6 tolerance: same status, iteration count within 30 %, and the GPU result
