@@ -703,8 +703,8 @@ static int rbsor_fused_zchunk(const LaunchCtx& L, dim3& grid) {
     const int nzi = L.g.k1 - L.g.k0;
     const int gx = (L.g.nx - 2 + Tile::BX - 1) / Tile::BX, gy = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
     static const int forced = getenv("CFD_B200_ZCHUNK_RB") ? atoi(getenv("CFD_B200_ZCHUNK_RB")) : 0;
-    // one block per SM (154 KB of shared memory): aim at >= 20 waves, 16..128 planes per block
-    int nch = (148 * 20 + gx * gy - 1) / (gx * gy);
+    // one block per SM (154 KB of shared memory): aim at >= 10 waves (measured flat between 64 and 128 planes), 16..128 planes per block
+    int nch = (148 * 10 + gx * gy - 1) / (gx * gy);
     int zc = (nzi + nch - 1) / nch;
     zc = zc < 16 ? 16 : (zc > 128 ? 128 : zc);
     if (forced > 0) zc = forced;

@@ -12,6 +12,7 @@
 //
 // The functor supplies the arithmetic:
 //   static constexpr int NF, NPW;                                 // NPW >= 1 (a dummy if none)
+//   static constexpr bool STAGED;                                 // op.prime(n, c) is called once per own cell (3-D only)
 //   static constexpr bool PRODUCER_WARP;                          // 544-thread launch (regs <= 96) or 512 (<= 128)
 //   void pw_load(long long n, double (&pw)[NPW]) const;          // pointwise operands of cell n
 //   void cell(const St<NF>& s, const double (&pw)[NPW], long long n, int i, int j, int k);
@@ -207,7 +208,10 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
     double pwn[2][NPW];
 #pragma unroll
     for (int c = 0; c < 2; c++)
-        if (act[c]) op.pw_load(n[c], pwn[c]);
+        if (act[c]) {
+            op.pw_load(n[c], pwn[c]);
+            if constexpr (Op::STAGED) op.prime(n[c], c);  // asynchronous staging of further pointwise operands
+        }
     auto wait_q = [&](int q) -> const double* {
         const int slot = q % ST;
         mbar_wait(&full[slot], (q / ST) & 1);

@@ -95,6 +95,16 @@ __device__ __forceinline__ void tma_load_plane(void* dst, const CUtensorMap* map
         "l"(map), "r"(x0), "r"(y0), "r"(z), "r"(smem_u32(bar))
         : "memory");
 }
+// 8-byte asynchronous global -> shared copy (LDGSTS): no destination register, so a thread can keep
+// many loads in flight without register pressure; completion per thread via commit / wait groups.
+__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
