@@ -87,14 +87,24 @@ extern unsigned long long g_launches;  // kernels launched by this library
 // ---------------------------------------------------------------------------------------
 #ifdef __CUDACC__
 
-// The reference's fmax(-lim, fmin(lim, v)) (NaN -> +lim) as two compares and selects: sm_100a has no
-// FP64 min/max instruction and the library fmin/fmax expand to ~7 instructions each (measured: a
-// quarter of the RK stage's instruction stream); identical results for every input incl. NaN, +-0.
-__device__ __forceinline__ double clampv(double lim, double v) {
-    const double r = !(v <= lim) ? lim : v;  // v > lim, or NaN
-    return (r < -lim) ? -lim : r;
+// The reference clamps with fmax(-lim, fmin(lim, v)) (NaN -> +lim).  sm_100a has no FP64 min/max
+// instruction: each fmin/fmax expands to ~7 instructions, two of them on the FP64 pipe, plus a live
+// predicate (measured: a quarter of the RK stage's instruction stream).  For limits whose low word
+// is zero (10, 100, 1000) the same function is 8 integer instructions on the bit pattern:
+// |v| >= lim or NaN  <=>  (high word without sign) >= (high word of lim); the result is then +-lim
+// with v's sign, +lim for NaN.  Identical results for every input (tests/test_gpu_steppers.py).
+constexpr unsigned HI_10 = 0x40240000u, HI_100 = 0x40590000u, HI_1000 = 0x408f4000u, HI_INF = 0x7ff00000u;
+__device__ __forceinline__ unsigned abs_hi(double v) { return (unsigned)__double2hiint(v) & 0x7fffffffu; }
+template <unsigned LIM_HI>
+__device__ __forceinline__ double clampb(double v) {
+    const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+    const unsigned a = hi & 0x7fffffffu;
+    const bool over = a >= LIM_HI;
+    const bool nan = (a > HI_INF) || (a == HI_INF && lo != 0u);
+    const unsigned sgn = nan ? 0u : (hi & 0x80000000u);
+    return __hiloint2double((int)(over ? (LIM_HI | sgn) : hi), (int)(over ? 0u : lo));
 }
-__device__ __forceinline__ double clamp100(double v) { return clampv(100.0, v); }
+__device__ __forceinline__ double clamp100(double v) { return clampb<HI_100>(v); }
 
 // a / b, correctly rounded, from y = RN(1/b) computed once on the host: q = a*y, one exact
 // residual, one correction (Markstein).  Same result as the IEEE division the reference performs

@@ -54,13 +54,13 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
             const double* f = qin.a[q];
             if (D3) F[q].p = f[zp];
             const double e = f[n + oxp], w_ = f[n + oxm], nn = f[n + oyp], s_ = f[n + oym], cc = F[q].c;
-            d1[q][0] = clampv(100.0, ediv(e - w_, g.two_dx, g.inv_2dx));
-            d1[q][1] = clampv(100.0, ediv(nn - s_, g.two_dy, g.inv_2dy));
-            d1[q][2] = clampv(100.0, (F[q].p - F[q].m) * g.inv_2dz);
+            d1[q][0] = clampb<HI_100>(ediv(e - w_, g.two_dx, g.inv_2dx));
+            d1[q][1] = clampb<HI_100>(ediv(nn - s_, g.two_dy, g.inv_2dy));
+            d1[q][2] = clampb<HI_100>((F[q].p - F[q].m) * g.inv_2dz);
             if (q < 3) {
-                d2[q][0] = clampv(1000.0, ediv(e - 2.0 * cc + w_, g.dx2, g.inv_dx2));
-                d2[q][1] = clampv(1000.0, ediv(nn - 2.0 * cc + s_, g.dy2, g.inv_dy2));
-                d2[q][2] = clampv(1000.0, (F[q].p - 2.0 * cc + F[q].m) * g.inv_dz2);
+                d2[q][0] = clampb<HI_1000>(ediv(e - 2.0 * cc + w_, g.dx2, g.inv_dx2));
+                d2[q][1] = clampb<HI_1000>(ediv(nn - 2.0 * cc + s_, g.dy2, g.inv_dy2));
+                d2[q][2] = clampb<HI_1000>((F[q].p - 2.0 * cc + F[q].m) * g.inv_dz2);
             }
         }
         const double rh = __ldg(rho + n);
@@ -80,7 +80,7 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
             for (int q = 0; q < 3; q++)
                 kq[q] = -uc * d1[q][0] - vc * d1[q][1] - wc * d1[q][2] - d1[3][q] / rh +
                         nu * (d2[q][0] + d2[q][1] + d2[q][2]) + src[q];
-            const double div = clampv(10.0, d1[0][0] + d1[1][1] + d1[2][2]);
+            const double div = clampb<HI_10>(d1[0][0] + d1[1][1] + d1[2][2]);
             kq[3] = -0.1 * rh * div;
         }
 #pragma unroll
@@ -172,13 +172,13 @@ struct RkOp {
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const double cc = s.c(q);
-            d1[q][0] = clampv(100.0, ediv(s.e(q) - s.w(q), g.two_dx, g.inv_2dx));
-            d1[q][1] = clampv(100.0, ediv(s.n(q) - s.s(q), g.two_dy, g.inv_2dy));
-            d1[q][2] = clampv(100.0, (s.p(q) - s.m(q)) * g.inv_2dz);
+            d1[q][0] = clampb<HI_100>(ediv(s.e(q) - s.w(q), g.two_dx, g.inv_2dx));
+            d1[q][1] = clampb<HI_100>(ediv(s.n(q) - s.s(q), g.two_dy, g.inv_2dy));
+            d1[q][2] = clampb<HI_100>((s.p(q) - s.m(q)) * g.inv_2dz);
             if (q < 3) {
-                d2[q][0] = clampv(1000.0, ediv(s.e(q) - 2.0 * cc + s.w(q), g.dx2, g.inv_dx2));
-                d2[q][1] = clampv(1000.0, ediv(s.n(q) - 2.0 * cc + s.s(q), g.dy2, g.inv_dy2));
-                d2[q][2] = clampv(1000.0, (s.p(q) - 2.0 * cc + s.m(q)) * g.inv_dz2);
+                d2[q][0] = clampb<HI_1000>(ediv(s.e(q) - 2.0 * cc + s.w(q), g.dx2, g.inv_dx2));
+                d2[q][1] = clampb<HI_1000>(ediv(s.n(q) - 2.0 * cc + s.s(q), g.dy2, g.inv_dy2));
+                d2[q][2] = clampb<HI_1000>((s.p(q) - 2.0 * cc + s.m(q)) * g.inv_dz2);
             }
         }
         const double rh = pw[0];
@@ -198,7 +198,7 @@ struct RkOp {
             for (int q = 0; q < 3; q++)
                 kq[q] = -uc * d1[q][0] - vc * d1[q][1] - wc * d1[q][2] - d1[3][q] / rh +
                         nu * (d2[q][0] + d2[q][1] + d2[q][2]) + src[q];
-            const double div = clampv(10.0, d1[0][0] + d1[1][1] + d1[2][2]);
+            const double div = clampb<HI_10>(d1[0][0] + d1[1][1] + d1[2][2]);
             kq[3] = -0.1 * rh * div;
         }
         const int cs = (j - 1 - y0) >> 3;  // which of the thread's two cells (rows ly and ly + 8)
@@ -224,9 +224,9 @@ struct RkOp {
                 acc.a[q][n] = ra.first ? kq[q] : a0[q] + ra.w_k * kq[q];
                 out = base + ra.fac_next * kq[q];
             }
-            if (q < 3) out = clamp100(out);
+            if (q < 3) out = clamp100(out);  // (always finite afterwards)
+            else bad |= (abs_hi(out) >= HI_INF);
             qout.a[q][n] = out;
-            bad |= !isfinite(out);
         }
         // the slot's values are in registers (consumed above): refill it with the next plane's
         if (STG && !ra.first && has_next) issue(n + g.sz, cs);

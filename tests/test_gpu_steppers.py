@@ -95,6 +95,29 @@ def test_rk_step_by_step(orc, order, shape):
         slv.close()
 
 
+@pytest.mark.parametrize("order", [2, 4])
+@pytest.mark.parametrize("shape", [(20, 18, 12), (130, 20, 11), (34, 20, 1), (21, 17, 9)])
+def test_rk_clamps_engage_like_the_reference(orc, order, shape):
+    """Large-amplitude fields: the derivative clamps (+-100, +-1000), the divergence clamp (+-10) and
+    the velocity clamp (+-100) of ns_momentum_rhs_scalar.h all engage.  The kernels take an
+    exponent-word fast path when nothing is near a limit; this drives the exact-clamp path."""
+    g, f = cases.random_field(*shape, seed=21, scale=40.0)
+    f.rho[...] = 1.0 + 0.1 * np.random.default_rng(2).random(f.rho.shape)
+    p = cases.params(dt=1e-3, amp=(0.1, 0.05))
+    fo = f.copy()
+    slv = api.GpuSolver("rk%d_gpu" % order)
+    try:
+        for step in range(2):
+            rc_g, _ = slv.step(f, g, p)
+            rc_o = orc.rk(fo, g, p, order, 1)
+            assert rc_g == rc_o
+            for name in ("u", "v", "w", "p"):
+                np.testing.assert_array_equal(getattr(f, name), getattr(fo, name), err_msg="%s step %d" % (name, step))
+        assert np.abs(f.u).max() == 100.0  # the velocity clamp really engaged
+    finally:
+        slv.close()
+
+
 @pytest.mark.parametrize("nz", [1, 9])
 @pytest.mark.parametrize("kind", ["projection", "rk4"])
 def test_energy_buoyancy_and_thermal_bcs(orc, poisson_cfg, nz, kind):
