@@ -105,6 +105,11 @@ __device__ __forceinline__ double clampb(double v) {
     return __hiloint2double((int)(over ? (LIM_HI | sgn) : hi), (int)(over ? 0u : lo));
 }
 __device__ __forceinline__ double clamp100(double v) { return clampb<HI_100>(v); }
+// running maximum in the reference's own form `if (r > m) m = r;` (linear_solver.c:304-346): a NaN
+// candidate is ignored like with fmax, without fmax's NaN-selection sequence
+__device__ __forceinline__ void max_into(double& m, double r) {
+    if (r > m) m = r;
+}
 
 // a / b, correctly rounded, from y = RN(1/b) computed once on the host: q = a*y, one exact
 // residual, one correction (Markstein).  Same result as the IEEE division the reference performs

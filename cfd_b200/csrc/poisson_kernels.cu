@@ -64,6 +64,19 @@ __device__ __forceinline__ void store_with_ghosts(const Geom& g, double* x, int 
     }
 }
 
+// Same, for the tiled 3-D kernels: `inner` (block-uniform) says that no cell of the block's tile
+// touches an x/y ghost, so only the two z-boundary planes take the ghost-writing path.
+template <bool D3>
+__device__ __forceinline__ void store_with_ghosts_tile(const Geom& g, double* x, int i, int j, int k, long long n,
+                                                       double v, bool inner) {
+    if (D3 && inner && k != 1 && k != g.nz - 2) x[n] = v;
+    else store_with_ghosts<D3>(g, x, i, j, k, n, v);
+}
+// (3-D tile grids: blockIdx.x / .y index the tile)
+__device__ __forceinline__ bool tile_is_inner() {
+    return blockIdx.x != 0 && blockIdx.x != gridDim.x - 1 && blockIdx.y != 0 && blockIdx.y != gridDim.y - 1;
+}
+
 // ---------------------------------------------------------------------------------------
 // Neumann ghost fill as a stand-alone pass ("apply BC" at the start/end of the Krylov solves).
 // One thread per cell of the local slab; ghost cells read their clamped interior source.
@@ -167,7 +180,7 @@ k_jacobi(Geom g, const double* __restrict__ xin, double* __restrict__ xout,
             if (RES) {
                 const double lap = ediv(xe - 2.0 * zc + xw, g.dx2, g.inv_dx2) + ediv(yn - 2.0 * zc + ys, g.dy2, g.inv_dy2) +
                                    (zp + zm - 2.0 * zc) * g.inv_dz2;
-                rmax[0] = fmax(rmax[0], fabs(lap - f));
+                max_into(rmax[0], fabs(lap - f));
             }
             const double v = -(f - ediv(xe + xw, g.dx2, g.inv_dx2) - ediv(yn + ys, g.dy2, g.inv_dy2) -
                                (zp + zm) * g.inv_dz2) * g.inv_factor;
@@ -219,7 +232,7 @@ k_linf_residual(Geom g, const double* __restrict__ x, const double* __restrict__
             const double lap = ediv(x[n + 1] - 2.0 * zc + x[n - 1], g.dx2, g.inv_dx2) +
                                ediv(x[n + g.sy] - 2.0 * zc + x[n - g.sy], g.dy2, g.inv_dy2) +
                                (zp + zm - 2.0 * zc) * g.inv_dz2;
-            rmax[0] = fmax(rmax[0], fabs(lap - __ldg(rhs + n)));
+            max_into(rmax[0], fabs(lap - __ldg(rhs + n)));
             zm = zc;
             zc = zp;
         }
