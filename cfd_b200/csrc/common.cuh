@@ -90,19 +90,19 @@ extern unsigned long long g_launches;  // kernels launched by this library
 // The reference clamps with fmax(-lim, fmin(lim, v)) (NaN -> +lim).  sm_100a has no FP64 min/max
 // instruction: each fmin/fmax expands to ~7 instructions, two of them on the FP64 pipe, plus a live
 // predicate (measured: a quarter of the RK stage's instruction stream).  For limits whose low word
-// is zero (10, 100, 1000) the same function is 8 integer instructions on the bit pattern:
+// is zero (10, 100, 1000) the same function is 6 instructions (5 integer + one FP64 compare):
 // |v| >= lim or NaN  <=>  (high word without sign) >= (high word of lim); the result is then +-lim
 // with v's sign, +lim for NaN.  Identical results for every input (tests/test_gpu_steppers.py).
+// (Quotients come from ediv(), which maps an INFINITE numerator to NaN where a / b is +-inf: with
+// +-inf in a field the clamp can return +lim where the reference returns -lim.  NaN inputs are exact.)
 constexpr unsigned HI_10 = 0x40240000u, HI_100 = 0x40590000u, HI_1000 = 0x408f4000u, HI_INF = 0x7ff00000u;
 __device__ __forceinline__ unsigned abs_hi(double v) { return (unsigned)__double2hiint(v) & 0x7fffffffu; }
 template <unsigned LIM_HI>
 __device__ __forceinline__ double clampb(double v) {
     const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
-    const unsigned a = hi & 0x7fffffffu;
-    const bool over = a >= LIM_HI;
-    const bool nan = (a > HI_INF) || (a == HI_INF && lo != 0u);
-    const unsigned sgn = nan ? 0u : (hi & 0x80000000u);
-    return __hiloint2double((int)(over ? (LIM_HI | sgn) : hi), (int)(over ? 0u : lo));
+    const bool over = (hi & 0x7fffffffu) >= LIM_HI;                     // |v| >= lim, or NaN
+    const unsigned lim = (v < 0.0) ? (LIM_HI | 0x80000000u) : LIM_HI;  // -lim only for a real negative: NaN -> +lim
+    return __hiloint2double((int)(over ? lim : hi), (int)(over ? 0u : lo));
 }
 __device__ __forceinline__ double clamp100(double v) { return clampb<HI_100>(v); }
 // running maximum in the reference's own form `if (r > m) m = r;` (linear_solver.c:304-346): a NaN

@@ -70,9 +70,9 @@ k_predictor(Geom g, NsConst c, int zchunk, const double* __restrict__ u, const d
     }
     const double su = c.src_on ? su_tab[j] * c.src_decay : 0.0, sv = c.src_on ? sv_tab[i] * c.src_decay : 0.0;
     March U, V, W;
-    U.m = D3 ? u[n - g.sz] : 0.0; U.c = u[n]; U.p = 0.0;
-    V.m = D3 ? v[n - g.sz] : 0.0; V.c = v[n]; V.p = 0.0;
-    W.m = D3 ? w[n - g.sz] : 0.0; W.c = w[n]; W.p = 0.0;
+    U.m = D3 ? u[n - g.sz] : u[n]; U.c = u[n]; U.p = u[n];  // nz = 1: z neighbours = the cell itself
+    V.m = D3 ? v[n - g.sz] : v[n]; V.c = v[n]; V.p = v[n];
+    W.m = D3 ? w[n - g.sz] : w[n]; W.c = w[n]; W.p = w[n];
     for (int k = kb; k < ke; k++, n += g.sz) {
         if (D3) {
             U.p = u[n + g.sz];
@@ -170,9 +170,9 @@ k_corrector(Geom g, NsConst c, int zchunk, const double* __restrict__ us, const 
             if (ENERGY) { Tn[b] = T[b]; bad |= !isfinite(T[b]); }
         }
         March P, Q;
-        P.m = D3 ? p[n - g.sz] : 0.0; P.c = p[n]; P.p = 0.0;
+        P.c = p[n]; P.m = D3 ? p[n - g.sz] : P.c; P.p = P.c;  // nz = 1: z neighbours = the cell itself
         Q.m = Q.c = Q.p = 0.0;
-        if (ENERGY) { Q.m = D3 ? T[n - g.sz] : 0.0; Q.c = T[n]; }
+        if (ENERGY) { Q.c = T[n]; Q.m = D3 ? T[n - g.sz] : Q.c; Q.p = Q.c; }
         for (int k = kb; k < ke; k++, n += g.sz) {
             if (D3) {
                 P.p = p[n + g.sz];
@@ -226,7 +226,7 @@ k_energy(Geom g, NsConst c, int zchunk, const double* __restrict__ u, const doub
         long long n = (long long)kb * g.sz + col;
         if (D3 && kb == g.k0) { Tn[n - g.sz] = T[n - g.sz]; bad |= !isfinite(T[n - g.sz]); }
         March Q;
-        Q.m = D3 ? T[n - g.sz] : 0.0; Q.c = T[n]; Q.p = 0.0;
+        Q.c = T[n]; Q.m = D3 ? T[n - g.sz] : Q.c; Q.p = Q.c;
         for (int k = kb; k < ke; k++, n += g.sz) {
             if (D3) Q.p = T[n + g.sz];
             const double Te = T[n + 1], Tw = T[n - 1], Tnn = T[n + g.sy], Ts = T[n - g.sy], Tc = Q.c;

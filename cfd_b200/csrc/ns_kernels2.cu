@@ -41,9 +41,9 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
 #pragma unroll
     for (int q = 0; q < 4; q++) {
         const long long zm = (kb > 1 || !ra.wrap_z) ? n - g.sz : n + (long long)(g.nz - 3) * g.sz;
-        F[q].m = D3 ? qin.a[q][zm] : 0.0;
         F[q].c = qin.a[q][n];
-        F[q].p = 0.0;
+        F[q].m = D3 ? qin.a[q][zm] : F[q].c;  // nz = 1: the reference's k wraps onto k itself
+        F[q].p = F[q].c;
     }
     bool bad = false;
     for (int k = kb; k < ke; k++, n += g.sz) {

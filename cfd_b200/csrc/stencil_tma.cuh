@@ -126,7 +126,9 @@ __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, co
 #pragma unroll
             for (int f = 0; f < NF; f++) {
                 s.zc[f] = s.pl[f * PP];
-                s.zm[f] = s.zp[f] = 0.0;
+                // nz = 1: the reference's z neighbours are the cell itself (sz = 0 / k wraps onto k), so a
+                // z-difference is (c - c) * 0 -- zero for finite c but NaN for a non-finite one
+                s.zm[f] = s.zp[f] = s.zc[f];
             }
             op.cell(s, pw[c], (long long)j * g.sy + i, i, j, 0);
         }

@@ -76,6 +76,35 @@ def test_projection_step_by_step(orc, poisson_cfg, method, tol, case):
         slv.close()
 
 
+@pytest.mark.parametrize("shape", [(34, 20, 1), (20, 18, 12), (21, 17, 9)])
+def test_projection_launders_non_finite_velocities_like_the_reference(orc, poisson_cfg, shape):
+    """NaN in INTERIOR velocity cells: the reference's velocity clamp turns it into +100
+    (solver_projection.c:180-182) and the step goes on.  Bitwise against the oracle (Jacobi pressure
+    solve, capped).  (+-inf inputs are outside the parity claim: the 3-instruction quotient turns an
+    infinite numerator into NaN, so a clamp can return +100 where the reference returns -100.)"""
+    g, f = cases.random_field(*shape, seed=13, scale=0.05)
+    kz = shape[2] // 2
+    f.u[kz, 5, 7] = np.nan
+    f.v[kz, 9, 4] = -np.nan
+    f.u[kz, 8, 11] = np.frombuffer(np.uint64(0xFFF0000000000001).tobytes(), dtype=np.float64)[0]
+    if shape[2] > 1:
+        f.w[kz, 7, 13] = np.nan
+    p = cases.params(dt=1e-3, amp=(0.1, 0.05))
+    pc = abi.poisson_config("jacobi", on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE, max_iterations=30)
+    api.set_poisson(pc)
+    fo = f.copy()
+    slv = api.GpuSolver("projection_gpu")
+    try:
+        for step in range(2):
+            rc_g, _ = slv.step(f, g, p)
+            rc_o, _ = orc.projection(fo, g, p, pc, 1)
+            assert rc_g == rc_o
+            for name in ("u", "v", "w", "p"):
+                np.testing.assert_array_equal(getattr(f, name), getattr(fo, name), err_msg="%s step %d" % (name, step))
+    finally:
+        slv.close()
+
+
 @pytest.mark.parametrize("order", [2, 4])
 @pytest.mark.parametrize("shape", [(16, 16, 1), (12, 10, 9), (3, 3, 3), (33, 20, 1)])
 def test_rk_step_by_step(orc, order, shape):
@@ -95,14 +124,22 @@ def test_rk_step_by_step(orc, order, shape):
         slv.close()
 
 
+@pytest.mark.parametrize("poison", [False, True])
 @pytest.mark.parametrize("order", [2, 4])
 @pytest.mark.parametrize("shape", [(20, 18, 12), (130, 20, 11), (34, 20, 1), (21, 17, 9)])
-def test_rk_clamps_engage_like_the_reference(orc, order, shape):
+def test_rk_clamps_engage_like_the_reference(orc, order, shape, poison):
     """Large-amplitude fields: the derivative clamps (+-100, +-1000), the divergence clamp (+-10) and
     the velocity clamp (+-100) of ns_momentum_rhs_scalar.h all engage.  The kernels take an
     exponent-word fast path when nothing is near a limit; this drives the exact-clamp path."""
     g, f = cases.random_field(*shape, seed=21, scale=40.0)
     f.rho[...] = 1.0 + 0.1 * np.random.default_rng(2).random(f.rho.shape)
+    if poison:  # NaN -> +limit in every clamp (fmax(-L, fmin(L, v)) semantics): both signs, odd payloads
+        kz = shape[2] // 2
+        f.u[kz, 5, 7] = np.nan
+        f.u[kz, 9, 4] = -np.nan
+        f.v[kz, 3, 3] = np.frombuffer(np.uint64(0xFFF0000000000001).tobytes(), dtype=np.float64)[0]
+        f.w[kz, 7, 11] = np.frombuffer(np.uint64(0x7FF0000000000001).tobytes(), dtype=np.float64)[0]
+        f.p[kz, 6, 9] = np.nan
     p = cases.params(dt=1e-3, amp=(0.1, 0.05))
     fo = f.copy()
     slv = api.GpuSolver("rk%d_gpu" % order)
@@ -113,7 +150,7 @@ def test_rk_clamps_engage_like_the_reference(orc, order, shape):
             assert rc_g == rc_o
             for name in ("u", "v", "w", "p"):
                 np.testing.assert_array_equal(getattr(f, name), getattr(fo, name), err_msg="%s step %d" % (name, step))
-        assert np.abs(f.u).max() == 100.0  # the velocity clamp really engaged
+        assert np.nanmax(np.abs(f.u)) == 100.0  # the velocity clamp really engaged
     finally:
         slv.close()
 
