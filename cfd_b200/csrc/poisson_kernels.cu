@@ -79,14 +79,16 @@ __device__ __forceinline__ bool tile_is_inner() {
 
 // ---------------------------------------------------------------------------------------
 // Neumann ghost fill as a stand-alone pass ("apply BC" at the start/end of the Krylov solves).
-// One thread per cell of the local slab; ghost cells read their clamped interior source.
+// One thread per BOUNDARY cell of the local slab; ghost cells read their clamped interior source.
 // Halo planes (non-physical sides) are left untouched.
 // ---------------------------------------------------------------------------------------
 __global__ void k_neumann_fill(Geom g, double* x, const Ctl* ctl, int seq, int honour_skip) {
     if (ctl && seq > ctl->done_seq && !honour_skip) return;
     if (ctl && honour_skip && ctl->skip_final_bc) return;
-    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= g.ncell) return;
+    // one thread per boundary cell (edge / corner cells appear in two or three face lists: they read
+    // the same interior source and store the same value)
+    const long long t = face_cell(g, (long long)blockIdx.x * blockDim.x + threadIdx.x);
+    if (t < 0) return;
     int i = (int)(t % g.nx);
     int j = (int)((t / g.nx) % g.ny);
     int k = (int)(t / ((long long)g.nx * g.ny));
@@ -677,7 +679,7 @@ static inline KArgs with_chunk(const LaunchCtx& L, KArgs a) {
 }
 
 void launch_neumann_fill(const LaunchCtx& L, double* x, int seq, int honour_skip, bool use_ctl) {
-    const int nb = (int)((L.g.ncell + 255) / 256);
+    const int nb = (int)((face_cells(L.g) + 255) / 256);
     CFDB_LAUNCH(KK_NEUMANN, L.st,
                 k_neumann_fill<<<nb, 256, 0, L.st>>>(L.g, x, use_ctl ? L.ctl : nullptr, seq, honour_skip));
 }
