@@ -64,6 +64,36 @@ class DirichletValues(C.Structure):
     _fields_ = [(n, C.c_double) for n in ("left", "right", "top", "bottom", "front", "back")]
 
 
+# boundary_conditions.h:64-68, 85-89, 96-103
+BC_INLET_PROFILE_UNIFORM, BC_INLET_PROFILE_PARABOLIC, BC_INLET_PROFILE_CUSTOM = 0, 1, 2
+BC_INLET_SPEC_VELOCITY, BC_INLET_SPEC_MAGNITUDE_DIR, BC_INLET_SPEC_MASS_FLOW = 0, 1, 2
+BC_EDGE_LEFT, BC_EDGE_RIGHT, BC_EDGE_BOTTOM, BC_EDGE_TOP, BC_EDGE_FRONT, BC_EDGE_BACK = 1, 2, 4, 8, 16, 32
+
+INLET_PROFILE_FN = C.CFUNCTYPE(None, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_void_p)
+
+
+class _TimeParams(C.Union):
+    _fields_ = [("sinusoidal", C.c_double * 4), ("ramp", C.c_double * 4), ("step", C.c_double * 3)]
+
+
+class BcTimeConfig(C.Structure):
+    """boundary_conditions.h:183-198"""
+    _fields_ = [("profile", C.c_int), ("params", _TimeParams), ("custom_fn", C.c_void_p),
+                ("custom_user_data", C.c_void_p)]
+
+
+class _InletSpec(C.Union):
+    _fields_ = [("velocity", C.c_double * 2), ("magnitude_dir", C.c_double * 2), ("mass_flow", C.c_double * 3)]
+
+
+class BcInletConfig(C.Structure):
+    """boundary_conditions.h:233-267"""
+    _fields_ = [("edge", C.c_int), ("profile", C.c_int), ("spec_type", C.c_int), ("spec", _InletSpec),
+                ("custom_profile", INLET_PROFILE_FN), ("custom_profile_user_data", C.c_void_p),
+                ("time_config", BcTimeConfig), ("custom_profile_time", C.c_void_p),
+                ("custom_profile_time_user_data", C.c_void_p)]
+
+
 class ThermalBC(C.Structure):
     """navier_stokes_solver.h:108-116"""
     _fields_ = [(n, C.c_int) for n in ("left", "right", "bottom", "top", "front", "back")] + [

@@ -55,6 +55,16 @@ def load():
     for n in ("cfd_b200_create_projection_gpu_solver", "cfd_b200_create_rk2_gpu_solver",
               "cfd_b200_create_rk4_gpu_solver"):
         proto(n, C.POINTER(abi.NSSolver), [])
+    # GPU boundary-condition API on device pointers (boundary_conditions_gpu.cuh)
+    sz, dp, DV = C.c_size_t, C.c_void_p, C.POINTER(abi.DirichletValues)
+    proto("bc_apply_neumann_gpu", None, [dp, sz, sz, vp])
+    proto("bc_apply_scalar_gpu", None, [dp, sz, sz, i32, vp])
+    proto("bc_apply_velocity_gpu", None, [dp, dp, sz, sz, i32, vp])
+    proto("bc_apply_dirichlet_scalar_gpu", None, [dp, sz, sz, DV, vp])
+    proto("bc_apply_dirichlet_velocity_gpu", None, [dp, dp, sz, sz, DV, DV, vp])
+    proto("bc_apply_inlet_gpu", i32, [dp, dp, sz, sz, C.POINTER(abi.BcInletConfig), vp])
+    proto("bc_apply_scalar_3d_gpu", None, [dp, sz, sz, sz, i32, vp])
+    proto("bc_apply_velocity_3d_gpu", None, [dp, dp, dp, sz, sz, sz, i32, vp])
     # Part 3: extensions
     proto("cfd_b200_poisson_config_default", abi.PoissonConfig, [])
     proto("cfd_b200_set_poisson_config", i32, [PC])
@@ -98,6 +108,8 @@ DECLARED_SYMBOLS = [
     "gpu_get_device_info", "gpu_select_device", "gpu_should_use", "solve_navier_stokes_gpu",
     "gpu_solver_create", "gpu_solver_destroy", "gpu_solver_upload", "gpu_solver_download",
     "gpu_solver_step", "gpu_solver_get_stats", "gpu_solver_reset_stats",
+    "bc_apply_neumann_gpu", "bc_apply_scalar_gpu", "bc_apply_velocity_gpu", "bc_apply_dirichlet_scalar_gpu",
+    "bc_apply_dirichlet_velocity_gpu", "bc_apply_inlet_gpu", "bc_apply_scalar_3d_gpu", "bc_apply_velocity_3d_gpu",
     "cfd_b200_create_projection_gpu_solver", "cfd_b200_create_rk2_gpu_solver",
     "cfd_b200_create_rk4_gpu_solver", "cfd_b200_poisson_config_default", "cfd_b200_set_poisson_config",
     "cfd_b200_get_poisson_config", "cfd_b200_last_error", "cfd_b200_version",

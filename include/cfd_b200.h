@@ -85,6 +85,62 @@ typedef struct {
     double left, right, top, bottom, front, back;
 } bc_dirichlet_values_t;
 
+/* boundary_conditions.h:64-68, 85-89, 96-103: inlet profile / specification / edge */
+typedef enum { BC_INLET_PROFILE_UNIFORM, BC_INLET_PROFILE_PARABOLIC, BC_INLET_PROFILE_CUSTOM } bc_inlet_profile_t;
+typedef enum { BC_INLET_SPEC_VELOCITY, BC_INLET_SPEC_MAGNITUDE_DIR, BC_INLET_SPEC_MASS_FLOW } bc_inlet_spec_type_t;
+typedef enum {
+    BC_EDGE_LEFT = 0x01,
+    BC_EDGE_RIGHT = 0x02,
+    BC_EDGE_BOTTOM = 0x04,
+    BC_EDGE_TOP = 0x08,
+    BC_EDGE_FRONT = 0x10,
+    BC_EDGE_BACK = 0x20
+} bc_edge_t;
+
+/* boundary_conditions.h:117-198: time variation of an inlet (carried in bc_inlet_config_t; the
+ * steady entry point bc_apply_inlet_gpu does not evaluate it, as in the reference) */
+typedef enum {
+    BC_TIME_PROFILE_CONSTANT,
+    BC_TIME_PROFILE_SINUSOIDAL,
+    BC_TIME_PROFILE_RAMP,
+    BC_TIME_PROFILE_STEP,
+    BC_TIME_PROFILE_CUSTOM
+} bc_time_profile_t;
+typedef struct { double frequency, amplitude, phase, offset; } bc_time_sinusoidal_t;
+typedef struct { double t_start, t_end, value_start, value_end; } bc_time_ramp_t;
+typedef struct { double t_step, value_before, value_after; } bc_time_step_t;
+typedef double (*bc_time_custom_fn)(double time, double dt, void* user_data);
+typedef struct {
+    bc_time_profile_t profile;
+    union {
+        bc_time_sinusoidal_t sinusoidal;
+        bc_time_ramp_t ramp;
+        bc_time_step_t step;
+    } params;
+    bc_time_custom_fn custom_fn;
+    void* custom_user_data;
+} bc_time_config_t;
+typedef void (*bc_inlet_profile_fn)(double position, double* u_out, double* v_out, void* user_data);
+typedef void (*bc_inlet_profile_time_fn)(double position, double time, double dt, double* u_out, double* v_out,
+                                         void* user_data);
+
+/* boundary_conditions.h:233-267 */
+typedef struct {
+    bc_edge_t edge;
+    bc_inlet_profile_t profile;
+    bc_inlet_spec_type_t spec_type;
+    union {
+        struct { double u, v; } velocity;
+        struct { double magnitude, direction; } magnitude_dir;
+        struct { double mass_flow_rate, density, inlet_length; } mass_flow;
+    } spec;
+    bc_inlet_profile_fn custom_profile;
+    void* custom_profile_user_data;
+    bc_time_config_t time_config;
+    bc_inlet_profile_time_fn custom_profile_time;
+    void* custom_profile_time_user_data;
+} bc_inlet_config_t;
+
 /* lib/include/cfd/solvers/navier_stokes_solver.h:54-64 */
 typedef struct {
     double* u;
@@ -335,6 +391,31 @@ CFD_B200_API poisson_solver_t* create_jacobi_gpu_solver(void);   /* linear_solve
 CFD_B200_API poisson_solver_t* create_redblack_gpu_solver(void); /* linear_solver.c:194-197 */
 CFD_B200_API poisson_solver_t* create_cg_gpu_solver(void);       /* linear_solver.c:212-215 */
 CFD_B200_API poisson_solver_t* create_bicgstab_gpu_solver(void); /* linear_solver.c:226-229 */
+
+/* GPU boundary-condition API on DEVICE pointers (cfd/boundary/boundary_conditions_gpu.cuh).
+ * `stream` is a cudaStream_t (void* when no CUDA header was included before this one).  Results
+ * are those of the reference's CPU passes (x, then y, then z faces), race-free; types other than
+ * PERIODIC act as NEUMANN in the generic entry points, as in the reference. */
+#if defined(__DRIVER_TYPES_H__) || defined(__CUDA_RUNTIME_H__)
+typedef cudaStream_t cfd_b200_stream_t;
+#else
+typedef void* cfd_b200_stream_t;
+#endif
+CFD_B200_API void bc_apply_neumann_gpu(double* d_field, size_t nx, size_t ny, cfd_b200_stream_t stream); /* :32 */
+CFD_B200_API void bc_apply_scalar_gpu(double* d_field, size_t nx, size_t ny, bc_type_t type, cfd_b200_stream_t stream); /* :43 */
+CFD_B200_API void bc_apply_velocity_gpu(double* d_u, double* d_v, size_t nx, size_t ny, bc_type_t type,
+                                        cfd_b200_stream_t stream);                                                 /* :55 */
+CFD_B200_API void bc_apply_dirichlet_scalar_gpu(double* d_field, size_t nx, size_t ny,
+                                                const bc_dirichlet_values_t* values, cfd_b200_stream_t stream);    /* :73 */
+CFD_B200_API void bc_apply_dirichlet_velocity_gpu(double* d_u, double* d_v, size_t nx, size_t ny,
+                                                  const bc_dirichlet_values_t* u_values,
+                                                  const bc_dirichlet_values_t* v_values, cfd_b200_stream_t stream); /* :88 */
+CFD_B200_API cfd_status_t bc_apply_inlet_gpu(double* d_u, double* d_v, size_t nx, size_t ny,
+                                             const bc_inlet_config_t* config, cfd_b200_stream_t stream);           /* :107 */
+CFD_B200_API void bc_apply_scalar_3d_gpu(double* d_field, size_t nx, size_t ny, size_t nz, bc_type_t type,
+                                         cfd_b200_stream_t stream);                                                /* :129 */
+CFD_B200_API void bc_apply_velocity_3d_gpu(double* d_u, double* d_v, double* d_w, size_t nx, size_t ny, size_t nz,
+                                           bc_type_t type, cfd_b200_stream_t stream);                              /* :149 */
 
 /* Remaining public GPU device surface used by the reference's tests/examples. */
 CFD_B200_API int gpu_get_device_info(gpu_device_info_t* info, int max_devices); /* gpu_device.h:111 */

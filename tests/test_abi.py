@@ -45,10 +45,12 @@ def test_ctypes_mirror_sizes():
     sizes = {C.sizeof(abi.Grid), C.sizeof(abi.NSSolverParams), C.sizeof(abi.ThermalBC),
              C.sizeof(abi.DirichletValues), C.sizeof(abi.NSSolverStats), C.sizeof(abi.NSSolver),
              C.sizeof(abi.GpuConfig), C.sizeof(abi.GpuSolverStats), C.sizeof(abi.PoissonParams),
-             C.sizeof(abi.PoissonStats), C.sizeof(abi.PoissonSolver)}
+             C.sizeof(abi.PoissonStats), C.sizeof(abi.PoissonSolver), C.sizeof(abi.BcInletConfig),
+             C.sizeof(abi.BcTimeConfig)}
     assert sizes <= set(t)
     assert abi.NSSolverParams.thermal_bc.offset in t and abi.NSSolverParams.alpha.offset in t
     assert abi.PoissonSolver.params.offset in t and abi.PoissonSolver.solve.offset in t
+    assert abi.BcInletConfig.time_config.offset in t and abi.BcInletConfig.custom_profile.offset in t
 
 
 def test_poisson_config_roundtrip_without_gpu():
