@@ -389,3 +389,54 @@ def test_dropin_through_the_reference_registry(orc, poisson_cfg, name, kind):
             rco = orc.rk(fo, g, p, int(kind[2]), 1)
         assert rco == 0
     assert_close(f, fo, 1e-8 if kind == "projection" else 1e-10, "dropin " + name)
+
+
+# Ghia, Ghia & Shin (1982), J. Comput. Phys. 48, 387-411, Re = 100: u on the vertical and v on the
+# horizontal centreline (the tables the reference validates against, tests/validation/cavity_reference_data.h)
+GHIA_Y = [0.0000, 0.0547, 0.0625, 0.0703, 0.1016, 0.1719, 0.2813, 0.4531, 0.5000, 0.6172, 0.7344, 0.8516, 0.9531,
+          0.9609, 0.9688, 0.9766, 1.0000]
+GHIA_U = [0.00000, -0.03717, -0.04192, -0.04775, -0.06434, -0.10150, -0.15662, -0.21090, -0.20581, -0.13641, 0.00332,
+          0.23151, 0.68717, 0.73722, 0.78871, 0.84123, 1.00000]
+GHIA_X = [0.0000, 0.0625, 0.0703, 0.0781, 0.0938, 0.1563, 0.2266, 0.2344, 0.5000, 0.8047, 0.8594, 0.9063, 0.9453,
+          0.9531, 0.9609, 0.9688, 1.0000]
+GHIA_V = [0.00000, 0.09233, 0.10091, 0.10890, 0.12317, 0.16077, 0.17507, 0.17527, 0.05454, -0.24533, -0.22445,
+          -0.16914, -0.10313, -0.08864, -0.07391, -0.05906, 0.00000]
+
+
+def _ghia_rms(f, n):
+    """RMS against the tables by linear interpolation of the computed centrelines
+    (tests/validation/cavity_validation_utils.h:36-65)."""
+    c = np.linspace(0.0, 1.0, n)
+    u_mid, v_mid = f.u[0, :, n // 2], f.v[0, n // 2, :]
+    ru = np.sqrt(np.mean((np.interp(GHIA_Y, c, u_mid) - np.array(GHIA_U)) ** 2))
+    rv = np.sqrt(np.mean((np.interp(GHIA_X, c, v_mid) - np.array(GHIA_V)) ** 2))
+    return ru, rv
+
+
+def test_ghia_lid_driven_cavity_re100(orc, poisson_cfg):
+    """The reference's validation run (tests/validation/test_ghia_projection_gpu.c: 33 x 33, 5000 steps,
+    dt = 5e-4, host-side cavity BCs before every step, gate RMS_u < 0.10; the reference documents
+    RMS_u 0.0382 / RMS_v 0.0440 for its CPU projection, docs/validation/cavity-backends-validation.md).
+    Run through the persistent projection_gpu solver; the first 300 steps are also taken on the oracle
+    and compared (<= 1e-8, CG reorders reductions)."""
+    n = 33
+    g, f, p = cases.cavity(n, 1, dt=5e-4)
+    api.set_poisson(abi.poisson_config("cg", on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE))
+    fo = f.copy()
+    pc = abi.poisson_config("cg", on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
+    slv = api.GpuSolver("projection_gpu")
+    try:
+        for step in range(5000):
+            cases.apply_cavity_bc(f)
+            rc, _ = slv.step(f, g, p)
+            assert rc == 0, step
+            if step < 300:
+                cases.apply_cavity_bc(fo)
+                assert orc.projection(fo, g, p, pc, 1)[0] == 0
+                if step == 299:
+                    assert_close(f, fo, 1e-8, "cavity after 300 steps")
+    finally:
+        slv.close()
+    ru, rv = _ghia_rms(f, n)
+    assert ru < 0.10 and rv < 0.10, (ru, rv)                  # the reference's gate
+    assert abs(ru - 0.0382) < 0.004 and abs(rv - 0.0440) < 0.004, (ru, rv)  # its documented result
