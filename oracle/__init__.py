@@ -51,6 +51,9 @@ class Oracle:
         L.orc_rk.restype = C.c_int
         L.orc_rk.argtypes = [C.POINTER(abi.FlowField), C.POINTER(abi.Grid),
                              C.POINTER(abi.NSSolverParams), C.c_int, C.c_int]
+        L.orc_explicit_euler.restype = C.c_int
+        L.orc_explicit_euler.argtypes = [C.POINTER(abi.FlowField), C.POINTER(abi.Grid),
+                                         C.POINTER(abi.NSSolverParams), C.c_int]
         L.orc_poisson_solve.restype = C.c_int
         L.orc_poisson_solve.argtypes = [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, C.c_double,
                                         C.c_double, C.c_double, C.POINTER(abi.PoissonParams),
@@ -75,6 +78,9 @@ class Oracle:
 
     def rk(self, field, grid, params, order, nsteps=1):
         return self.lib.orc_rk(C.byref(field.c), C.byref(grid.c), C.byref(params), order, nsteps)
+
+    def explicit_euler(self, field, grid, params, nsteps=1):
+        return self.lib.orc_explicit_euler(C.byref(field.c), C.byref(grid.c), C.byref(params), nsteps)
 
     def poisson(self, method, nx, ny, nz, dx, dy, dz, pparams, x, rhs, x_temp=None):
         st = abi.PoissonStats()

@@ -837,6 +837,85 @@ ORC_API int orc_rk(flow_field* f, const grid* gr, const ns_solver_params_t* prm,
     return rc;
 }
 
+/* ======================================================================
+ * Explicit (forward) Euler -- cpu/solver_explicit_euler.c:337-582.  Unlike the RK right-hand
+ * side it reads the PLAIN neighbours (boundary cells included, no index wrap), limits every
+ * increment to +-1 (UPDATE_LIMIT) and never steps further than 1e-4 (DT_CONSERVATIVE_LIMIT).
+ * Boundary handling per step (:527-556): the new interior goes back into the field, the energy
+ * equation advances T, every field is wrapped periodically, then the caller's boundary
+ * velocities (u, v, and w when nz > 1) are put back, the thermal BCs applied and the state
+ * scanned for NaN/Inf.
+ * ====================================================================== */
+ORC_API int orc_explicit_euler(flow_field* f, const grid* gr, const ns_solver_params_t* prm,
+                               int nsteps) {
+    if (!f || !gr || !prm) return CFD_ERROR_INVALID;
+    if (f->nx < 3 || f->ny < 3 || (f->nz > 1 && f->nz < 3)) return CFD_ERROR_INVALID;
+    if (prm->source_func || prm->heat_source_func) return CFD_ERROR_UNSUPPORTED;
+    if (f->nz > 1 && gr->dz)
+        for (size_t k = 1; k < f->nz - 1; k++)
+            if (fabs(gr->dz[k] - gr->dz[0]) > 1e-14) return CFD_ERROR_INVALID;
+    double dzv = (f->nz > 1 && gr->dz) ? gr->dz[0] : 0.0;
+    geo_t g = make_geo(f->nx, f->ny, f->nz, gr->dx[0], gr->dy[0], dzv);
+    const size_t N = g.total, bytes = N * sizeof(double), nx = g.nx, sz = g.sz;
+    double* nw[5]; /* next u, v, w, p, rho: start as copies, only interior cells are rewritten */
+    double* cur[5] = {f->u, f->v, f->w, f->p, f->rho};
+    double* Tw = calloc(N, sizeof(double));
+    for (int c = 0; c < 5; c++) {
+        nw[c] = malloc(bytes);
+        memcpy(nw[c], cur[c], bytes);
+    }
+    const double dt = fmin(prm->dt, 1e-4);
+    int rc = CFD_SUCCESS;
+    for (int iter = 0; iter < nsteps && rc == CFD_SUCCESS; iter++) {
+        const double *u = f->u, *v = f->v, *w = f->w, *p = f->p, *rho = f->rho;
+        FOR_INTERIOR_PAR(g, i, j, k, n) {
+            if (rho[n] <= 1e-10 || fabs(gr->dx[i]) < 1e-10 || fabs(gr->dy[j]) < 1e-10) continue;
+            const double hx = gr->dx[i], hy = gr->dy[j];
+            double d1[4][3], d2[3][3]; /* d1[field][axis], field 3 = p; d2 for u, v, w */
+            const double* q[4] = {u, v, w, p};
+            for (int c = 0; c < 4; c++) {
+                const double* a = q[c];
+                d1[c][0] = clampd(-100.0, 100.0, (a[n + 1] - a[n - 1]) / (2.0 * hx));
+                d1[c][1] = clampd(-100.0, 100.0, (a[n + nx] - a[n - nx]) / (2.0 * hy));
+                d1[c][2] = clampd(-100.0, 100.0, (a[n + sz] - a[n - sz]) * g.inv_2dz);
+                if (c == 3) break;
+                d2[c][0] = clampd(-1000.0, 1000.0, (a[n + 1] - 2.0 * a[n] + a[n - 1]) / (hx * hx));
+                d2[c][1] = clampd(-1000.0, 1000.0, (a[n + nx] - 2.0 * a[n] + a[n - nx]) / (hy * hy));
+                d2[c][2] = clampd(-1000.0, 1000.0, (a[n + sz] - 2.0 * a[n] + a[n - sz]) * g.inv_dz2);
+            }
+            double nu = fmin(prm->mu / fmax(rho[n], 1e-10), 1.0);
+            double src[3];
+            sources(prm, gr->x[i], gr->y[j], iter, dt, f->T[n], &src[0], &src[1], &src[2]);
+            for (int c = 0; c < 3; c++) {
+                double inc = dt * (-u[n] * d1[c][0] - v[n] * d1[c][1] - w[n] * d1[c][2] -
+                                   d1[3][c] / rho[n] + nu * (d2[c][0] + d2[c][1] + d2[c][2]) + src[c]);
+                inc = clampd(-1.0, 1.0, inc);
+                nw[c][n] = clampd(-100.0, 100.0, q[c][n] + inc);
+            }
+            double div = clampd(-10.0, 10.0, d1[0][0] + d1[1][1] + d1[2][2]);
+            double dp = clampd(-1.0, 1.0, -0.1 * dt * rho[n] * div);
+            nw[3][n] = p[n] + dp;
+            nw[4][n] = rho[n];
+        }
+        for (int c = 0; c < 5; c++) memcpy(cur[c], nw[c], bytes);
+        rc = energy_step(f, &g, prm, dt, Tw);
+        if (rc != CFD_SUCCESS) break;
+        orc_apply_periodic(f);
+        copy_vel_boundary(f->u, f->v, f->w, nw[0], nw[1], nw[2], g.nx, g.ny, g.nz);
+        rc = orc_thermal_bcs(f, prm);
+        if (rc != CFD_SUCCESS) break;
+        for (size_t n = 0; n < N; n++)
+            if (!isfinite(f->u[n]) || !isfinite(f->v[n]) || !isfinite(f->w[n]) ||
+                !isfinite(f->p[n])) {
+                rc = CFD_ERROR_DIVERGED;
+                break;
+            }
+    }
+    for (int c = 0; c < 5; c++) free(nw[c]);
+    free(Tw);
+    return rc;
+}
+
 /* Stats as the registry wrappers compute them -- solver_registry.c:31-62. */
 ORC_API void orc_field_stats(const flow_field* f, double* max_vel, double* max_p, double* max_T) {
     size_t N = f->nx * f->ny * f->nz;

@@ -32,11 +32,15 @@ def save_step(tag, solver, g, f, p, nsteps):
 
 
 def main():
-    for solver in ("projection", "rk2", "rk4"):
+    for solver in ("projection", "rk2", "rk4", "explicit_euler"):
         g, f, p = cases.golden16()
         save_step("golden16_" + solver, solver, g, f, p, 1)
     g, f, p = cases.taylor_green(12, 10, dt=1e-3)
     save_step("tg3d_rk4", "rk4", g, f, p, 3)
+    g, f, p = cases.taylor_green(12, 10, dt=1e-3)
+    save_step("tg3d_explicit_euler", "explicit_euler", g, f, p, 3)
+    g, f, p = cases.natural_convection(17, 1, dt=5e-5)
+    save_step("natconv2d_explicit_euler", "explicit_euler", g, f, p, 3)
     g, f, p = cases.taylor_green(12, 10, dt=1e-3)
     save_step("tg3d_projection", "projection", g, f, p, 2)
     g, f, p = cases.natural_convection(17, 1, dt=2e-3)

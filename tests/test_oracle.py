@@ -19,6 +19,7 @@ GOLDEN_L2 = {
     "projection": (6.84647639323831686e-02, 3.42315494726977212e-02, 1.00000039251590289e+00),
     "rk2": (6.88584742267375205e-02, 3.49775875753182836e-02, 1.00000000000000044e+00),
     "rk4": (6.88584742267390471e-02, 3.49775875752817156e-02, 1.00000000000000000e+00),
+    "explicit_euler": (6.84647305901105868e-02, 3.42314945425199885e-02, 1.00000000000000000e+00),
 }
 
 
@@ -37,6 +38,8 @@ def run_oracle(orc, solver, g, f, p, nsteps):
     for _ in range(nsteps):
         if solver == "projection":
             rc, _ = orc.projection(f, g, p, abi.poisson_config("cg"), 1)
+        elif solver == "explicit_euler":
+            rc = orc.explicit_euler(f, g, p, 1)
         else:
             rc = orc.rk(f, g, p, int(solver[2]), 1)
         if rc != 0:
@@ -44,7 +47,7 @@ def run_oracle(orc, solver, g, f, p, nsteps):
     return rc
 
 
-@pytest.mark.parametrize("solver", ["projection", "rk2", "rk4"])
+@pytest.mark.parametrize("solver", ["projection", "rk2", "rk4", "explicit_euler"])
 def test_reference_golden_l2_norms(orc, solver):
     g, f, p = cases.golden16()
     assert run_oracle(orc, solver, g, f, p, 1) == 0
@@ -63,6 +66,9 @@ def _load_step(path):
     ("golden16_projection", lambda: cases.golden16()),
     ("golden16_rk2", lambda: cases.golden16()),
     ("golden16_rk4", lambda: cases.golden16()),
+    ("golden16_explicit_euler", lambda: cases.golden16()),
+    ("tg3d_explicit_euler", lambda: cases.taylor_green(12, 10, dt=1e-3)),
+    ("natconv2d_explicit_euler", lambda: cases.natural_convection(17, 1, dt=5e-5)),
     ("tg3d_rk4", lambda: cases.taylor_green(12, 10, dt=1e-3)),
     ("tg3d_projection", lambda: cases.taylor_green(12, 10, dt=1e-3)),
     ("natconv2d_projection", lambda: cases.natural_convection(17, 1, dt=2e-3)),
@@ -105,7 +111,7 @@ def test_oracle_poisson_matches_golden_bitwise(orc, path):
 # ---- live comparison with the compiled reference (skipped where oracle/_ref is absent) ----
 
 @pytest.mark.parametrize("shape", [(9, 9, 1), (20, 13, 1), (10, 9, 8), (3, 3, 3), (5, 4, 1)])
-@pytest.mark.parametrize("solver", ["projection", "rk2", "rk4"])
+@pytest.mark.parametrize("solver", ["projection", "rk2", "rk4", "explicit_euler"])
 def test_oracle_vs_reference_steps(orc, ref, shape, solver):
     g, f = cases.random_field(*shape, seed=7)
     p = cases.params(dt=1e-3, amp=(0.1, 0.05))
@@ -127,6 +133,26 @@ def test_oracle_vs_reference_solve_multi_step(orc, ref):
     assert rc_r == rc_o == 0
     for k in f.NAMES:
         np.testing.assert_array_equal(getattr(f, k), getattr(f2, k))
+
+
+def test_oracle_vs_reference_explicit_euler_solve(orc, ref):
+    """solver_solve(max_iter=N) of explicit_euler: later iterations read the periodic pressure
+    images the previous one left on the boundary, the iteration index enters the source term,
+    buoyancy + energy + thermal BCs ride along, caller boundary velocities survive."""
+    for nz in (1, 6):
+        g, f, p = cases.natural_convection(11, nz, dt=5e-5)
+        rng = np.random.default_rng(3)
+        for a in (f.u, f.v, f.w, f.p):
+            a[...] = 0.05 * rng.standard_normal(a.shape)
+        f.rho[...] = 1.0 + 0.1 * rng.random(f.rho.shape)
+        f.rho[0, 3, 4] = 0.0  # a skipped cell keeps its state (:399-401)
+        p.source_amplitude_u, p.source_amplitude_v = 0.1, 0.05
+        f2 = f.copy()
+        rc_r, _ = ref.run_solver("explicit_euler", f, g, p, 4, use_solve=True)
+        rc_o = orc.explicit_euler(f2, g, p, 4)
+        assert rc_r == rc_o == 0
+        for k in f.NAMES:
+            np.testing.assert_array_equal(getattr(f, k), getattr(f2, k), err_msg="nz=%d %s" % (nz, k))
 
 
 @pytest.mark.parametrize("shape", [(17, 15, 1), (9, 8, 7), (3, 3, 1), (33, 33, 1)])
