@@ -34,6 +34,7 @@ class GpuSolver:
     host flow_field in, host flow_field out (navier_stokes_solver.h:227-232)."""
 
     NAMES = {"projection_gpu": "cfd_b200_create_projection_gpu_solver",
+             "explicit_euler_gpu": "cfd_b200_create_explicit_euler_gpu_solver",
              "rk2_gpu": "cfd_b200_create_rk2_gpu_solver",
              "rk4_gpu": "cfd_b200_create_rk4_gpu_solver"}
 

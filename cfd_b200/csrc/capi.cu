@@ -126,7 +126,7 @@ void wrap_host_rho(flow_field* f) {
         for (size_t n = 0; n < plane; n++) { r[n] = r[(nz - 2) * plane + n]; r[(nz - 1) * plane + n] = r[plane + n]; }
 }
 
-enum StepKind { SK_PROJECTION, SK_RK2, SK_RK4 };
+enum StepKind { SK_PROJECTION, SK_RK2, SK_RK4, SK_EULER };
 
 cfd_status_t run_on_session(cfd_b200_session* s, StepKind kind, flow_field* f, const ns_solver_params_t* prm,
                             int nsteps, ns_solver_stats_t* stats) {
@@ -145,7 +145,7 @@ cfd_status_t run_on_session(cfd_b200_session* s, StepKind kind, flow_field* f, c
     }
     rc = session_upload(s, f, FM_ALL);
     if (rc != CFD_SUCCESS) return rc;
-    rc = run_rk(s, kind == SK_RK2 ? 2 : 4, prm, nsteps, stats);
+    rc = run_rk(s, kind == SK_EULER ? 1 : (kind == SK_RK2 ? 2 : 4), prm, nsteps, stats);
     if (rc == CFD_SUCCESS || rc == CFD_ERROR_DIVERGED) {
         cfd_status_t r2 = session_download(s, f, FM_U | FM_V | FM_W | FM_P | FM_T);
         if (r2 != CFD_SUCCESS) return r2;
@@ -272,10 +272,7 @@ cfd_status_t solve_rk4_method_gpu(flow_field* f, const grid* g, const ns_solver_
 }
 cfd_status_t solve_explicit_euler_method_gpu(flow_field* f, const grid* g, const ns_solver_params_t* p,
                                              const gpu_config_t* c) {
-    (void)f; (void)g; (void)p; (void)c;
-    set_error(CFD_ERROR_UNSUPPORTED, "explicit_euler_gpu is outside the projection hot path (SURVEY 8f n4); "
-                                     "use rk2_gpu / rk4_gpu / projection_gpu");
-    return CFD_ERROR_UNSUPPORTED;
+    return dropin(SK_EULER, f, g, p, c);
 }
 
 // ---- session steppers ----

@@ -92,7 +92,7 @@ poisson_solver_t* make_ps(const char* name, const char* desc, poisson_solver_met
 // ---------------- ns_solver_t vtable (persistent context) ----------------
 struct NsCtx {
     cfd_b200_session* s;
-    int kind;  // 0 projection, 2 rk2, 4 rk4
+    int kind;  // 0 projection, 1 explicit Euler, 2 rk2, 4 rk4
 };
 
 cfd_status_t ns_ensure(ns_solver_t* slv, const flow_field* f, const grid* g) {
@@ -226,6 +226,9 @@ poisson_solver_t* create_bicgstab_gpu_solver(void) {
 
 ns_solver_t* cfd_b200_create_projection_gpu_solver(void) {
     return make_ns("projection_gpu", "B200-native projection method (predictor / Poisson / corrector on device)", 0);
+}
+ns_solver_t* cfd_b200_create_explicit_euler_gpu_solver(void) {
+    return make_ns("explicit_euler_gpu", "B200-native explicit Euler stepper (CPU-exact limiters)", 1);
 }
 ns_solver_t* cfd_b200_create_rk2_gpu_solver(void) {
     return make_ns("rk2_gpu", "B200-native RK2 (Heun) explicit stepper", 2);

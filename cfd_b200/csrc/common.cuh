@@ -90,12 +90,12 @@ extern unsigned long long g_launches;  // kernels launched by this library
 // The reference clamps with fmax(-lim, fmin(lim, v)) (NaN -> +lim).  sm_100a has no FP64 min/max
 // instruction: each fmin/fmax expands to ~7 instructions, two of them on the FP64 pipe, plus a live
 // predicate (measured: a quarter of the RK stage's instruction stream).  For limits whose low word
-// is zero (10, 100, 1000) the same function is 6 instructions (5 integer + one FP64 compare):
+// is zero (1, 10, 100, 1000) the same function is 6 instructions (5 integer + one FP64 compare):
 // |v| >= lim or NaN  <=>  (high word without sign) >= (high word of lim); the result is then +-lim
 // with v's sign, +lim for NaN.  Identical results for every input (tests/test_gpu_steppers.py).
 // (Quotients come from ediv(), which maps an INFINITE numerator to NaN where a / b is +-inf: with
 // +-inf in a field the clamp can return +lim where the reference returns -lim.  NaN inputs are exact.)
-constexpr unsigned HI_10 = 0x40240000u, HI_100 = 0x40590000u, HI_1000 = 0x408f4000u, HI_INF = 0x7ff00000u;
+constexpr unsigned HI_1 = 0x3ff00000u, HI_10 = 0x40240000u, HI_100 = 0x40590000u, HI_1000 = 0x408f4000u, HI_INF = 0x7ff00000u;
 __device__ __forceinline__ unsigned abs_hi(double v) { return (unsigned)__double2hiint(v) & 0x7fffffffu; }
 template <unsigned LIM_HI>
 __device__ __forceinline__ double clampb(double v) {

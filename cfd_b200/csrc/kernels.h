@@ -110,6 +110,12 @@ void launch_field_stats(const LaunchCtx& L, const double* u, const double* v, co
 void launch_rk_stage(const LaunchCtx& L, const NsConst& c, const RkArgs& ra, const P4& qin, const P4& q0,
                       const W4& acc, const W4& qout, const double* rho, const double* T,
                       const double* su_tab, const double* sv_tab);
+// explicit Euler step (interior cells, out of place) and the O(N^(2/3)) boundary helpers
+void launch_euler(const LaunchCtx& L, const NsConst& c, const EulerArgs& ea, const P4& qin, const W4& qout,
+                  const double* rho, const double* T, const double* su_tab, const double* sv_tab);
+void launch_boundary_carry3(const LaunchCtx& L, const double* u, const double* v, const double* w, double* us,
+                            double* vs, double* ws);
+void launch_boundary_scan(const LaunchCtx& L, const double* u, const double* v, const double* w, const double* p);
 void launch_synth_init(const LaunchCtx& L, uint64_t seed, long long gk0, long long gnz, double* u, double* v,
                        double* w, double* p, double* T, double* rho);
 void launch_copy(const LaunchCtx& L, double* dst, const double* src, size_t n);

@@ -15,4 +15,9 @@ struct RkArgs {
     int wrap_y, wrap_z;  // wrap neighbour indices locally (axis not decomposed over ranks)
     double src_decay;    // exp(-lambda * iter * dt)
 };
+struct EulerArgs {
+    double dt;         // min(params->dt, DT_CONSERVATIVE_LIMIT = 1e-4)  (solver_explicit_euler.c:395)
+    double p_factor;   // -PRESSURE_UPDATE_FACTOR * dt, the leading product of the pressure increment (:518)
+    double src_decay;  // exp(-lambda * iter * dt)
+};
 }  // namespace cfdb

@@ -285,6 +285,13 @@ void launch_predictor(const LaunchCtx& L, const NsConst& c, const double* u, con
     if (L.g.dim3) CFDB_LAUNCH(KK_PREDICTOR, L.st, k_predictor<true><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, u, v, w, T, su_tab, sv_tab, us, vs, ws));
     else CFDB_LAUNCH(KK_PREDICTOR, L.st, k_predictor<false><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, u, v, w, T, su_tab, sv_tab, us, vs, ws));
 }
+void launch_boundary_carry3(const LaunchCtx& L, const double* u, const double* v, const double* w, double* us,
+                            double* vs, double* ws) {
+    CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_carry3<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, us, vs, ws)));
+}
+void launch_boundary_scan(const LaunchCtx& L, const double* u, const double* v, const double* w, const double* p) {
+    CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_scan<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, p, nullptr, nullptr, L.ctl)));
+}
 void launch_divergence(const LaunchCtx& L, const NsConst& c, const double* us, const double* vs,
                        const double* ws, double* rhs) {
     {

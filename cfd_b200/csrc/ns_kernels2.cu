@@ -250,6 +250,140 @@ k_rk_stage_tma(const __grid_constant__ TmaSet<4> tm, Geom g, NsConst c, RkArgs r
     if (op.bad && ra.last) ctl->nonfinite = 1;
 }
 
+// ---------------------------------------------------------------------------------------
+// Explicit (forward) Euler step, cpu/solver_explicit_euler.c:396-524, one pass: the right-hand
+// side has the RK stage's terms and clamps but reads the PLAIN neighbours (boundary cells
+// included, no index wrap), every increment is limited to +-1 (UPDATE_LIMIT), the velocity to
+// +-100, and the pressure moves by clamp(-0.1 dt rho div, +-1).  Cells with rho <= 1e-10 keep
+// their state (:399-401).  Interior cells only; out of place.
+// ---------------------------------------------------------------------------------------
+struct EulerCell {
+    // d1[q][axis]: clamped first derivatives of u,v,w,p; d2[q][axis]: clamped second derivatives of u,v,w
+    __device__ __forceinline__ static bool update(const NsConst& c, const EulerArgs& ea, const double (&cc)[4],
+                                                  const double (&d1)[4][3], const double (&d2)[3][3], double rh,
+                                                  double Tc, double su, double sv, double (&out)[4]) {
+        if (rh > 1e-10) {
+            const double nu = fmin(c.mu / fmax(rh, 1e-10), 1.0);
+            double fu = su, fv = sv, fw = 0.0;
+            if (c.beta != 0.0) {
+                const double dT = Tc - c.T_ref;
+                fu += -c.beta * dT * c.gx;
+                fv += -c.beta * dT * c.gy;
+                fw += -c.beta * dT * c.gz;
+            }
+            const double src[3] = {fu, fv, fw};
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const double inc = ea.dt * (-cc[0] * d1[q][0] - cc[1] * d1[q][1] - cc[2] * d1[q][2] - d1[3][q] / rh +
+                                            nu * (d2[q][0] + d2[q][1] + d2[q][2]) + src[q]);
+                out[q] = clamp100(cc[q] + clampb<HI_1>(inc));
+            }
+            const double div = clampb<HI_10>(d1[0][0] + d1[1][1] + d1[2][2]);
+            out[3] = cc[3] + clampb<HI_1>(ea.p_factor * rh * div);
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; q++) out[q] = cc[q];
+        }
+        return (abs_hi(out[0]) >= HI_INF) | (abs_hi(out[1]) >= HI_INF) | (abs_hi(out[2]) >= HI_INF) |
+               (abs_hi(out[3]) >= HI_INF);
+    }
+};
+
+template <bool D3>
+__global__ void __launch_bounds__(TX* TY)
+k_euler(Geom g, NsConst c, EulerArgs ea, int zchunk, P4 qin, W4 qout, const double* __restrict__ rho,
+        const double* __restrict__ T, const double* __restrict__ su_tab, const double* __restrict__ sv_tab, Ctl* ctl) {
+    const int i = blockIdx.x * TX + threadIdx.x, j = blockIdx.y * TY + threadIdx.y;
+    const int kb = g.k0 + blockIdx.z * zchunk, ke = min(kb + zchunk, g.k1);
+    if (!(i >= 1 && i < g.nx - 1 && j >= 1 && j < g.ny - 1)) return;
+    long long n = (long long)kb * g.sz + (long long)j * g.sy + i;
+    const double su = c.src_on ? su_tab[j] * ea.src_decay : 0.0;
+    const double sv = c.src_on ? sv_tab[i] * ea.src_decay : 0.0;
+    March2 F[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        F[q].c = qin.a[q][n];
+        F[q].m = D3 ? qin.a[q][n - g.sz] : F[q].c;  // nz = 1: stride_z = 0, the z neighbours are the cell itself
+        F[q].p = F[q].c;
+    }
+    bool bad = false;
+    for (int k = kb; k < ke; k++, n += g.sz) {
+        double d1[4][3], d2[3][3], cc[4], out[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const double* f = qin.a[q];
+            if (D3) F[q].p = f[n + g.sz];
+            const double e = f[n + 1], w_ = f[n - 1], nn = f[n + g.sy], s_ = f[n - g.sy];
+            cc[q] = F[q].c;
+            d1[q][0] = clampb<HI_100>(ediv(e - w_, g.two_dx, g.inv_2dx));
+            d1[q][1] = clampb<HI_100>(ediv(nn - s_, g.two_dy, g.inv_2dy));
+            d1[q][2] = clampb<HI_100>((F[q].p - F[q].m) * g.inv_2dz);
+            if (q < 3) {
+                d2[q][0] = clampb<HI_1000>(ediv(e - 2.0 * cc[q] + w_, g.dx2, g.inv_dx2));
+                d2[q][1] = clampb<HI_1000>(ediv(nn - 2.0 * cc[q] + s_, g.dy2, g.inv_dy2));
+                d2[q][2] = clampb<HI_1000>((F[q].p - 2.0 * cc[q] + F[q].m) * g.inv_dz2);
+            }
+        }
+        bad |= EulerCell::update(c, ea, cc, d1, d2, __ldg(rho + n), (c.beta != 0.0) ? __ldg(T + n) : 0.0, su, sv, out);
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            qout.a[q][n] = out[q];
+            F[q].m = F[q].c;
+            F[q].c = F[q].p;
+        }
+    }
+    if (bad) ctl->nonfinite = 1;
+}
+
+struct EulerOp {
+    static constexpr bool PRODUCER_WARP = false, STAGED = false;  // 4 stencil fields: the 512-thread pipeline
+    static constexpr int NF = 4, NPW = 2;                         // pointwise: rho, T
+    const Geom& g;
+    const NsConst& c;
+    const EulerArgs& ea;
+    const W4& qout;
+    const double* __restrict__ rho;
+    const double* __restrict__ T;
+    const double* __restrict__ su_tab;
+    const double* __restrict__ sv_tab;
+    bool bad;
+    __device__ __forceinline__ void pw_load(long long n, double (&pw)[2]) const {
+        pw[0] = __ldg(rho + n);
+        pw[1] = (c.beta != 0.0) ? __ldg(T + n) : 0.0;
+    }
+    __device__ __forceinline__ void cell(const St<4>& s, const double (&pw)[2], long long n, int i, int j, int) {
+        double d1[4][3], d2[3][3], cc[4], out[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            cc[q] = s.c(q);
+            d1[q][0] = clampb<HI_100>(ediv(s.e(q) - s.w(q), g.two_dx, g.inv_2dx));
+            d1[q][1] = clampb<HI_100>(ediv(s.n(q) - s.s(q), g.two_dy, g.inv_2dy));
+            d1[q][2] = clampb<HI_100>((s.p(q) - s.m(q)) * g.inv_2dz);
+            if (q < 3) {
+                d2[q][0] = clampb<HI_1000>(ediv(s.e(q) - 2.0 * cc[q] + s.w(q), g.dx2, g.inv_dx2));
+                d2[q][1] = clampb<HI_1000>(ediv(s.n(q) - 2.0 * cc[q] + s.s(q), g.dy2, g.inv_dy2));
+                d2[q][2] = clampb<HI_1000>((s.p(q) - 2.0 * cc[q] + s.m(q)) * g.inv_dz2);
+            }
+        }
+        const double su = c.src_on ? su_tab[j] * ea.src_decay : 0.0, sv = c.src_on ? sv_tab[i] * ea.src_decay : 0.0;
+        bad |= EulerCell::update(c, ea, cc, d1, d2, pw[0], pw[1], su, sv, out);
+#pragma unroll
+        for (int q = 0; q < 4; q++) qout.a[q][n] = out[q];
+    }
+};
+
+// The halo of the TMA boxes delivers the boundary cells themselves -- exactly the plain neighbours
+// the reference reads (no periodic pre-pass, unlike the RK stage).
+template <bool D3>
+__global__ void __launch_bounds__(Tile::THREADS, 1)
+k_euler_tma(const __grid_constant__ TmaSet<4> tm, Geom g, NsConst c, EulerArgs ea, int zchunk, W4 qout,
+            const double* __restrict__ rho, const double* __restrict__ T, const double* __restrict__ su_tab,
+            const double* __restrict__ sv_tab, Ctl* ctl) {
+    EulerOp op{g, c, ea, qout, rho, T, su_tab, sv_tab, false};
+    tma_direct_sweep<D3>(tm, g, zchunk, op);
+    if (op.bad) ctl->nonfinite = 1;
+}
+
 // Periodic images on the boundary cells of up to 6 fields, one thread per face cell (closed form of
 // the sequential x, y, z wrap of solver_explicit_euler.c:231-314: boundary = wrapped interior).
 struct F6 {

@@ -22,7 +22,7 @@ const char* const kKernelNames[KK_COUNT] = {
     "field_stats", "synth_init", "copy", "euler", "boundary_cells", "fill", "ctl_reset", "rbsor_fused_iteration"};
 // Algorithmic bytes per interior cell per launch.
 const double kKernelBytesPerCell[KK_COUNT] = {0, 24, 16, 16, 0, 32, 32, 48, 48, 32, 56,
-                                              48, 32, 56, 0, 0, 136, 40, 0, 16, 0, 0, 8, 0, 24};
+                                              48, 32, 56, 0, 0, 136, 40, 0, 16, 72, 0, 8, 0, 24};
 
 // The reference keeps a thread-local error string (cfd/core/cfd_status.h:31-43).  When its core
 // library is loaded in the process we forward to it; otherwise we keep our own.

@@ -156,9 +156,85 @@ cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
     return CFD_SUCCESS;
 }
 
+// Explicit Euler, cpu/solver_explicit_euler.c:337-582 (the `explicit_euler_gpu` name).  Per step:
+// one out-of-place stencil pass over the interior; the caller's boundary velocities (u, v, and w
+// when nz > 1) are carried into the new arrays (the reference saves them, wraps, restores: :549-553);
+// energy step with the new velocity; periodic images on the boundary cells of p, rho, T (and w when
+// nz == 1, which the reference does not restore); thermal BCs; NaN/Inf scan.
+static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm, int nsteps,
+                              ns_solver_stats_t* stats) {
+    if (prm->source_func || prm->heat_source_func) {
+        set_error(CFD_ERROR_UNSUPPORTED, "host source/heat-source callbacks cannot run on the GPU");
+        return CFD_ERROR_UNSUPPORTED;
+    }
+    if (s->desc.nranks > 1) {
+        set_error(CFD_ERROR_UNSUPPORTED, "explicit Euler is single-GPU (slab-decomposed sessions: use RK2/RK4 or the projection)");
+        return CFD_ERROR_UNSUPPORTED;
+    }
+    cfd_status_t rc = check_thermal(prm, s->g.dim3);
+    if (rc != CFD_SUCCESS) return rc;
+    CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    t_prof = &s->prof;
+    for (int q = 0; q < 4; q++)
+        if ((rc = dalloc(s, &s->rk[q])) != CFD_SUCCESS) return rc;
+    if (!s->rho) {  // session extension: no density uploaded => rho = 1 everywhere
+        if ((rc = dalloc(s, &s->rho)) != CFD_SUCCESS) return rc;
+        launch_fill(s->L(), s->rho, 1.0, s->N);
+    }
+    const bool energy = prm->alpha > 0.0;
+    if ((energy || prm->beta != 0.0) && (rc = dalloc(s, &s->T)) != CFD_SUCCESS) return rc;
+    if (energy && (rc = dalloc(s, &s->Tn)) != CFD_SUCCESS) return rc;
+    if ((rc = ensure_tables(s, prm)) != CFD_SUCCESS) return rc;
+    NsConst c = make_const(s, prm);
+    EulerArgs ea;
+    ea.dt = fmin(prm->dt, 1e-4);  // DT_CONSERVATIVE_LIMIT (:395)
+    ea.p_factor = -0.1 * ea.dt;   // -PRESSURE_UPDATE_FACTOR * conservative_dt (:518)
+    c.dt = ea.dt;                 // the energy step advances by the same conservative dt (:537-539)
+    CFDB_CUDA_OK(cudaMemsetAsync(&s->ctl->nonfinite, 0, sizeof(int), s->st));
+    for (int iter = 0; iter < nsteps; iter++) {
+        const LaunchCtx L = s->L();
+        ea.src_decay = exp(-prm->source_decay_rate * iter * ea.dt);
+        P4 in;
+        W4 out;
+        double** cur[4] = {&s->u, &s->v, &s->w, &s->p};
+        for (int q = 0; q < 4; q++) { in.a[q] = *cur[q]; out.a[q] = s->rk[q]; }
+        launch_euler(L, c, ea, in, out, s->rho, s->T, s->su_tab, s->sv_tab);
+        launch_boundary_carry3(L, s->u, s->v, s->w, s->rk[0], s->rk[1], s->rk[2]);
+        for (int q = 0; q < 4; q++) std::swap(*cur[q], s->rk[q]);  // memcpy(field <- new) without the copy (:528-531)
+        if (energy) {
+            launch_energy(L, c, s->u, s->v, s->w, s->T, s->Tn);
+            std::swap(s->T, s->Tn);
+        }
+        // apply_boundary_conditions (:231-314) on everything the velocity restore does not undo
+        double* wrap[4];
+        int nw = 0;
+        wrap[nw++] = s->p;
+        wrap[nw++] = s->rho;
+        if (s->T) wrap[nw++] = s->T;  // a T that never reached the device stays on the host untouched
+        if (!s->g.dim3) wrap[nw++] = s->w;
+        launch_periodic_faces(L, wrap, nw, 1, 1);
+        if (energy) launch_thermal_bc(L, prm->thermal_bc, s->T);
+        launch_boundary_scan(L, s->u, s->v, s->w, s->p);
+        int bad = 0;
+        if ((rc = read_flags(s, &bad)) != CFD_SUCCESS) return rc;
+        if (bad) {
+            set_error(CFD_ERROR_DIVERGED, "NaN/Inf detected in explicit_euler step %d", iter);
+            return CFD_ERROR_DIVERGED;
+        }
+    }
+    cudaError_t ce = cudaGetLastError();
+    if (ce != cudaSuccess) {
+        set_error(CFD_ERROR, "CUDA failure in explicit Euler step: %s", cudaGetErrorString(ce));
+        return CFD_ERROR;
+    }
+    fill_stats(s, stats, nsteps);
+    return CFD_SUCCESS;
+}
+
 cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* prm, int nsteps,
                     ns_solver_stats_t* stats) {
     if (!s || !prm) return CFD_ERROR_INVALID;
+    if (order == 1) return run_euler(s, prm, nsteps, stats);
     if (order != 2 && order != 4) {
         set_error(CFD_ERROR_UNSUPPORTED, "RK order %d is not implemented on the GPU", order);
         return CFD_ERROR_UNSUPPORTED;

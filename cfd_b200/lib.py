@@ -52,7 +52,8 @@ def load():
     proto("gpu_solver_step", i32, [vp, GR, NP, C.POINTER(abi.GpuSolverStats)])
     proto("gpu_solver_get_stats", abi.GpuSolverStats, [vp])
     proto("gpu_solver_reset_stats", None, [vp])
-    for n in ("cfd_b200_create_projection_gpu_solver", "cfd_b200_create_rk2_gpu_solver",
+    for n in ("cfd_b200_create_projection_gpu_solver", "cfd_b200_create_explicit_euler_gpu_solver",
+              "cfd_b200_create_rk2_gpu_solver",
               "cfd_b200_create_rk4_gpu_solver"):
         proto(n, C.POINTER(abi.NSSolver), [])
     # GPU boundary-condition API on device pointers (boundary_conditions_gpu.cuh)
@@ -110,7 +111,8 @@ DECLARED_SYMBOLS = [
     "gpu_solver_step", "gpu_solver_get_stats", "gpu_solver_reset_stats",
     "bc_apply_neumann_gpu", "bc_apply_scalar_gpu", "bc_apply_velocity_gpu", "bc_apply_dirichlet_scalar_gpu",
     "bc_apply_dirichlet_velocity_gpu", "bc_apply_inlet_gpu", "bc_apply_scalar_3d_gpu", "bc_apply_velocity_3d_gpu",
-    "cfd_b200_create_projection_gpu_solver", "cfd_b200_create_rk2_gpu_solver",
+    "cfd_b200_create_projection_gpu_solver", "cfd_b200_create_explicit_euler_gpu_solver",
+    "cfd_b200_create_rk2_gpu_solver",
     "cfd_b200_create_rk4_gpu_solver", "cfd_b200_poisson_config_default", "cfd_b200_set_poisson_config",
     "cfd_b200_get_poisson_config", "cfd_b200_last_error", "cfd_b200_version",
     "cfd_b200_kernel_launch_count", "cfd_b200_host_alloc", "cfd_b200_host_free",

@@ -439,6 +439,7 @@ CFD_B200_API void gpu_solver_reset_stats(gpu_solver_context_t* ctx);
 /* Run-time registration path (navier_stokes_solver.h:333-337): factories returning a heap
  * ns_solver_t with real init/destroy (persistent device context) and fully filled stats. */
 CFD_B200_API ns_solver_t* cfd_b200_create_projection_gpu_solver(void);
+CFD_B200_API ns_solver_t* cfd_b200_create_explicit_euler_gpu_solver(void); /* solver_registry.c:1247-1291 */
 CFD_B200_API ns_solver_t* cfd_b200_create_rk2_gpu_solver(void);
 CFD_B200_API ns_solver_t* cfd_b200_create_rk4_gpu_solver(void);
 
@@ -525,7 +526,9 @@ CFD_B200_API cfd_status_t cfd_b200_session_projection(cfd_b200_session_t* s,
                                                       const ns_solver_params_t* params,
                                                       const cfd_b200_poisson_config_t* poisson,
                                                       int nsteps, ns_solver_stats_t* stats);
-/* Advance nsteps explicit RK steps, order in {1,2,4} (solver_rk2.c, solver_rk4.c). */
+/* Advance nsteps explicit steps: order 1 = explicit Euler with the CPU path's limiters
+ * (cpu/solver_explicit_euler.c:337-582; single-rank sessions), 2 = Heun, 4 = classical RK4
+ * (cpu/solver_rk2.c, cpu/solver_rk4.c). */
 CFD_B200_API cfd_status_t cfd_b200_session_rk(cfd_b200_session_t* s, int order,
                                               const ns_solver_params_t* params, int nsteps,
                                               ns_solver_stats_t* stats);

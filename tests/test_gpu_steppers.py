@@ -1,6 +1,6 @@
 """GPU parity of the time steppers against the oracle, through the C-ABI:
-the registry-style vtables (projection_gpu / rk2_gpu / rk4_gpu step + solve) and the stateless
-link-time symbols solve_{projection,rk2,rk4}_method_gpu.
+the registry-style vtables (projection_gpu / explicit_euler_gpu / rk2_gpu / rk4_gpu step + solve) and
+the stateless link-time symbols solve_{projection,explicit_euler,rk2,rk4}_method_gpu.
 
 Tolerances (north_star): rel L2 / Linf <= 1e-10 per step for projection with Jacobi / RB-SOR and
 for RK2 / RK4 (no reductions); <= 1e-8 on the final fields for projection with CG / PCG / BiCGSTAB.
@@ -124,6 +124,74 @@ def test_rk_step_by_step(orc, order, shape):
         slv.close()
 
 
+@pytest.mark.parametrize("shape", [(16, 16, 1), (12, 10, 9), (3, 3, 3), (33, 20, 1), (130, 20, 11), (66, 40, 1)])
+def test_explicit_euler_step_by_step(orc, shape):
+    """explicit_euler_gpu against cpu/solver_explicit_euler.c:337-582, bit for bit: plain (unwrapped)
+    neighbours, +-1 increment limiter, dt capped at 1e-4, caller boundary velocities preserved,
+    periodic images on p / rho / T (and on w when nz == 1), a rho <= 1e-10 cell keeps its state."""
+    g, f = cases.random_field(*shape, seed=9, scale=0.2)
+    f.rho[...] = 1.0 + 0.1 * np.random.default_rng(1).random(f.rho.shape)
+    if shape[0] > 4:
+        f.rho[shape[2] // 2, 2, 3] = 0.0
+    if shape[2] == 1:
+        f.w[...] = 0.05 * np.random.default_rng(2).standard_normal(f.w.shape)
+    p = cases.params(dt=1e-3, amp=(0.1, 0.05))
+    fo = f.copy()
+    slv = api.GpuSolver("explicit_euler_gpu")
+    try:
+        for step in range(3):
+            rc_g, _ = slv.step(f, g, p)
+            rc_o = orc.explicit_euler(fo, g, p, 1)
+            assert rc_g == rc_o == 0
+            for name in FIELDS + ("rho",):
+                np.testing.assert_array_equal(getattr(f, name), getattr(fo, name), err_msg="%s step %d" % (name, step))
+    finally:
+        slv.close()
+
+
+@pytest.mark.parametrize("poison", [False, True])
+@pytest.mark.parametrize("shape", [(20, 18, 12), (130, 20, 11), (34, 20, 1)])
+def test_explicit_euler_limiters_engage_like_the_reference(orc, shape, poison):
+    """Large amplitudes: derivative clamps, the +-1 increment limiter, the +-10 divergence clamp and
+    the +-100 velocity clamp all engage; NaNs are laundered exactly like fmax(-L, fmin(L, v))."""
+    g, f = cases.random_field(*shape, seed=22, scale=40.0)
+    f.rho[...] = 1.0 + 0.1 * np.random.default_rng(2).random(f.rho.shape)
+    if poison:
+        kz = shape[2] // 2
+        f.u[kz, 5, 7] = np.nan
+        f.v[kz, 3, 3] = np.frombuffer(np.uint64(0xFFF0000000000001).tobytes(), dtype=np.float64)[0]
+        f.w[kz, 7, 11] = -np.nan
+    p = cases.params(dt=5e-2, amp=(0.1, 0.05))  # > DT_CONSERVATIVE_LIMIT: the cap engages too
+    fo = f.copy()
+    slv = api.GpuSolver("explicit_euler_gpu")
+    try:
+        for step in range(2):
+            rc_g, _ = slv.step(f, g, p)
+            rc_o = orc.explicit_euler(fo, g, p, 1)
+            assert rc_g == rc_o
+            for name in ("u", "v", "w", "p"):
+                np.testing.assert_array_equal(getattr(f, name), getattr(fo, name), err_msg="%s step %d" % (name, step))
+    finally:
+        slv.close()
+
+
+def test_explicit_euler_multi_step_with_energy(orc):
+    """solve(max_iter = N): buoyancy, energy step at the capped dt, thermal BCs, decaying source,
+    later iterations reading the periodic pressure images left by the earlier ones."""
+    for nz in (1, 6):
+        g, f, p = cases.natural_convection(22, nz, dt=5e-5)
+        rng = np.random.default_rng(3)
+        for a in (f.u, f.v, f.w, f.p):
+            a[...] = 0.05 * rng.standard_normal(a.shape)
+        p.source_amplitude_u, p.source_amplitude_v = 0.1, 0.05
+        p.max_iter = 4
+        fo = f.copy()
+        assert api.solve_method_gpu("explicit_euler", f, g, p) == 0
+        assert orc.explicit_euler(fo, g, p, 4) == 0
+        for name in FIELDS + ("rho",):
+            np.testing.assert_array_equal(getattr(f, name), getattr(fo, name), err_msg="nz=%d %s" % (nz, name))
+
+
 @pytest.mark.parametrize("poison", [False, True])
 @pytest.mark.parametrize("order", [2, 4])
 @pytest.mark.parametrize("shape", [(20, 18, 12), (130, 20, 11), (34, 20, 1), (21, 17, 9)])
@@ -199,6 +267,9 @@ def test_stateless_entry_points_multi_step(orc, poisson_cfg, kind, order):
     ("golden16_rk2", lambda: cases.golden16(), "rk2_gpu"),
     ("golden16_rk4", lambda: cases.golden16(), "rk4_gpu"),
     ("tg3d_rk4", lambda: cases.taylor_green(12, 10, dt=1e-3), "rk4_gpu"),
+    ("golden16_explicit_euler", lambda: cases.golden16(), "explicit_euler_gpu"),
+    ("tg3d_explicit_euler", lambda: cases.taylor_green(12, 10, dt=1e-3), "explicit_euler_gpu"),
+    ("natconv2d_explicit_euler", lambda: cases.natural_convection(17, 1, dt=5e-5), "explicit_euler_gpu"),
     ("tg3d_projection", lambda: cases.taylor_green(12, 10, dt=1e-3), "projection_gpu"),
     ("natconv2d_projection", lambda: cases.natural_convection(17, 1, dt=2e-3), "projection_gpu"),
 ])
@@ -227,7 +298,8 @@ def test_reference_golden_l2_norms_on_gpu(poisson_cfg):
     path reorders CG reductions, so 1e-9 here for projection and 1e-12 for RK)."""
     gold = {"projection_gpu": (6.84647639323831686e-02, 3.42315494726977212e-02, 1.00000039251590289e+00, 1e-9),
             "rk2_gpu": (6.88584742267375205e-02, 3.49775875753182836e-02, 1.00000000000000044e+00, 1e-12),
-            "rk4_gpu": (6.88584742267390471e-02, 3.49775875752817156e-02, 1.00000000000000000e+00, 1e-12)}
+            "rk4_gpu": (6.88584742267390471e-02, 3.49775875752817156e-02, 1.00000000000000000e+00, 1e-12),
+            "explicit_euler_gpu": (6.84647305901105868e-02, 3.42314945425199885e-02, 1.00000000000000000e+00, 1e-12)}
     api.set_poisson("cg")
     for name, (gu, gv, gp, tol) in gold.items():
         g, f, p = cases.golden16()
@@ -285,8 +357,16 @@ def test_error_behaviour(poisson_cfg):
     f3 = before.copy()
     f3.p[0, 5, 5] = np.nan
     assert api.solve_method_gpu("projection", f3, g, p) == abi.CFD_ERROR_DIVERGED
-    # explicit Euler is outside the hot path
-    assert api.solve_method_gpu("explicit_euler", before, g, p) == abi.CFD_ERROR_UNSUPPORTED
+    # explicit Euler: same rules (interior NaN velocity laundered by the clamps, boundary NaN reported)
+    f4 = before.copy()
+    f4.u[0, 5, 5] = np.nan
+    assert api.solve_method_gpu("explicit_euler", f4, g, p) == abi.CFD_SUCCESS
+    f5 = before.copy()
+    f5.v[0, 0, 5] = np.nan
+    assert api.solve_method_gpu("explicit_euler", f5, g, p) == abi.CFD_ERROR_DIVERGED
+    p5 = cases.params()
+    p5.max_iter, p5.source_func = 1, 1
+    assert api.solve_method_gpu("explicit_euler", before.copy(), g, p5) == abi.CFD_ERROR_UNSUPPORTED
 
 
 def test_velocity_boundaries_are_preserved(poisson_cfg):
@@ -363,7 +443,8 @@ def test_legacy_context_api(orc, poisson_cfg):
     assert st.kernels_launched > 0 and st.poisson_iterations > 0
 
 
-@pytest.mark.parametrize("name,kind", [("projection_gpu", "projection"), ("rk4_gpu", "rk4"), ("rk2_gpu", "rk2")])
+@pytest.mark.parametrize("name,kind", [("projection_gpu", "projection"), ("rk4_gpu", "rk4"), ("rk2_gpu", "rk2"),
+                                       ("explicit_euler_gpu", "euler")])
 def test_dropin_through_the_reference_registry(orc, poisson_cfg, name, kind):
     """Link-time drop-in: the UNMODIFIED reference core/api, compiled with
     CFD_HAS_CUDA=1 and linked against libcfd_b200.so instead of libcfd_cuda.a
@@ -385,6 +466,8 @@ def test_dropin_through_the_reference_registry(orc, poisson_cfg, name, kind):
     for _ in range(2):
         if kind == "projection":
             rco, _ = orc.projection(fo, g, p, abi.poisson_config("cg"), 1)
+        elif kind == "euler":
+            rco = orc.explicit_euler(fo, g, p, 1)
         else:
             rco = orc.rk(fo, g, p, int(kind[2]), 1)
         assert rco == 0
