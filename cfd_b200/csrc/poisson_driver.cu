@@ -98,7 +98,12 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         dalloc(s, pxt) != CFD_SUCCESS)
         *pxt = nullptr;
 
-    if (method == POISSON_METHOD_JACOBI) {
+    if (method == POISSON_METHOD_JACOBI && R == 1 && a.max_iter >= 1 && jacobi_cluster_available(L) &&
+        (a.seq = seq, launch_jacobi_cluster(L, a, x, rhs))) {
+        // small 2-D grid: the whole solve ran in one cluster launch, x updated in place
+        seq++;
+        (void)poll.final_state();
+    } else if (method == POISSON_METHOD_JACOBI) {
         if (!pxt || !*pxt) return CFD_ERROR_INVALID;
         double* buf[2] = {x, *pxt};
         // sweeps q = 0..max_iter (sweep q computes res(x_q)); then the final decision

@@ -1,0 +1,230 @@
+// poisson_mini.cu -- whole Jacobi solve of a SMALL 2-D grid in one launch (sm_100a thread-block cluster).
+//
+// The 129 x 129 Ghia cavity (BASELINE config C1) runs up to 2000 Jacobi sweeps per time step on
+// 16 641 cells: one kernel per sweep costs ~10 us of launch + last-block reduction for ~1 us of
+// work.  Here ONE cluster of up to 8 CTAs keeps the whole problem on chip for the whole solve:
+//   * every CTA owns a strip of rows; x (two buffers) and rhs of the strip live in its shared memory;
+//   * a sweep reads buffer q&1 and writes buffer (q+1)&1 with the Neumann ghosts (same closed form as
+//     store_with_ghosts), then pushes its first / last row into the neighbouring CTAs' halo rows
+//     through distributed shared memory and meets the others at ONE cluster barrier;
+//   * the L-inf residual of x_q comes from the same loads (only on the sweeps where the reference
+//     computes it); every CTA writes its partial into every CTA's slot array, so after the barrier
+//     all of them take the reference's decision (linear_solver.c:415-484) on identical numbers.
+// Arithmetic, operation order, stopping rule, iteration count and status are those of k_jacobi /
+// stationary_decide (hence of linear_solver_jacobi.c:76-129): results are bit-identical to the
+// per-sweep kernels (tests/test_gpu_poisson.py::test_jacobi_cluster_solve_is_bit_exact).
+#include "common.cuh"
+#include "kernels.h"
+
+#include <cooperative_groups.h>
+#include <limits.h>
+#include <stdlib.h>
+
+namespace cg = cooperative_groups;
+
+namespace cfdb {
+
+namespace {
+
+constexpr int MINI_THREADS = 512;
+constexpr int MINI_MAX_CTAS = 8;           // portable cluster size
+constexpr size_t MINI_MAX_SMEM = 200 * 1024;
+
+struct MiniPlan {
+    int nc;        // CTAs in the cluster
+    int rows_per;  // interior rows per CTA (the last one may own fewer, never zero)
+    int bx, by;    // thread block shape
+    size_t smem;
+};
+
+// Shared memory of one CTA: A[(rows_per+2)*nx], B[(rows_per+2)*nx], rhs[rows_per*nx], slot[2][MINI_MAX_CTAS]
+static size_t mini_smem(int nx, int rows_per) {
+    return ((size_t)(2 * (rows_per + 2) + rows_per) * nx + 2 * MINI_MAX_CTAS) * sizeof(double);
+}
+
+static bool mini_plan(const Geom& g, MiniPlan& p) {
+    if (g.dim3 || g.nx < 3 || g.ny < 3) return false;
+    if (!(g.glo[0] && g.ghi[0] && g.glo[1] && g.ghi[1])) return false;  // single rank only
+    const int ni = g.ny - 2;
+    int nc = MINI_MAX_CTAS;
+    while (nc > 1 && ((ni + nc - 1) / nc) * (nc - 1) >= ni) nc >>= 1;  // every CTA owns at least one row
+    p.nc = nc;
+    p.rows_per = (ni + nc - 1) / nc;
+    p.smem = mini_smem(g.nx, p.rows_per);
+    if (p.smem > MINI_MAX_SMEM) return false;
+    int bx = 32;
+    while (bx < 128 && bx < g.nx - 2) bx <<= 1;
+    p.bx = bx;
+    p.by = MINI_THREADS / bx;
+    return true;
+}
+
+__device__ __forceinline__ double block_max(double v, double* scratch) {
+    // max in the reference's form (NaN candidates are ignored), warp shuffle -> shared -> warp 0
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x, lane = tid & 31, wid = tid >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) max_into(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if (lane == 0) scratch[wid] = v;
+    __syncthreads();
+    double r = 0.0;
+    if (wid == 0) {
+        r = (lane < (int)((blockDim.x * blockDim.y) >> 5)) ? scratch[lane] : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) max_into(r, __shfl_xor_sync(0xffffffffu, r, o));
+    }
+    return r;  // valid in thread 0
+}
+
+__global__ void __launch_bounds__(MINI_THREADS, 1)
+k_jacobi_cluster(Geom g, double* __restrict__ x, const double* __restrict__ rhs_g, Ctl* ctl, KArgs a, int rows_per) {
+    extern __shared__ __align__(16) double sm[];
+    __shared__ double red_scratch[MINI_THREADS / 32];
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank(), nc = (int)cluster.num_blocks();
+    const int nx = g.nx, ny = g.ny;
+    const int jb = 1 + rank * rows_per, je = min(jb + rows_per, ny - 1);  // owned interior rows [jb, je)
+    const int myrows = je - jb;
+    const size_t bufsz = (size_t)(rows_per + 2) * nx;
+    double* buf[2] = {sm, sm + bufsz};
+    double* rhs = sm + 2 * bufsz;
+    double* slot = rhs + (size_t)rows_per * nx;  // [2][MINI_MAX_CTAS]
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x, nthr = blockDim.x * blockDim.y;
+
+    // ---- load the strip: rows jb-1 .. je of x as the caller left them (ghosts included), rhs rows jb .. je-1
+    for (int t = tid; t < (myrows + 2) * nx; t += nthr) buf[0][t] = x[(size_t)(jb - 1) * nx + t];
+    for (int t = tid; t < myrows * nx; t += nthr) rhs[t] = rhs_g[(size_t)jb * nx + t];
+    // the other buffer's cells are all written before they are read, except nothing: every cell of the strip
+    // (own rows incl. ghost columns, ghost rows, pushed halo rows) is produced by each sweep
+    __syncthreads();
+
+    double r0 = 0.0, tol = 0.0, res_rep = 0.0;
+    int status = POISSON_ERROR, iters = 0, result = 0;
+    for (int s = 0;; s++) {
+        const double* A = buf[s & 1];
+        double* B = buf[(s + 1) & 1];
+        const bool checked = (s == 0) || ((s - 1) % a.check == 0);  // the sweeps whose residual the reference looks at
+        double rmax = 0.0;
+        for (int l = 1 + (int)threadIdx.y; l <= myrows; l += blockDim.y) {
+            const int j = jb + l - 1;
+            for (int i = 1 + (int)threadIdx.x; i < nx - 1; i += blockDim.x) {
+                const int n = l * nx + i;
+                const double zc = A[n], zm = 0.0, zp = 0.0;
+                const double xe = A[n + 1], xw = A[n - 1], yn = A[n + nx], ys = A[n - nx];
+                const double f = rhs[n - nx];
+                if (checked) {
+                    const double lap = ediv(xe - 2.0 * zc + xw, g.dx2, g.inv_dx2) + ediv(yn - 2.0 * zc + ys, g.dy2, g.inv_dy2) +
+                                       (zp + zm - 2.0 * zc) * g.inv_dz2;
+                    max_into(rmax, fabs(lap - f));
+                }
+                const double v = -(f - ediv(xe + xw, g.dx2, g.inv_dx2) - ediv(yn + ys, g.dy2, g.inv_dy2) -
+                                   (zp + zm) * g.inv_dz2) * g.inv_factor;
+                // interior cell + every Neumann ghost whose nearest interior cell it is
+                const bool xl = (i == 1), xh = (i == nx - 2), yl = (j == 1), yh = (j == ny - 2);
+                B[n] = v;
+                if (xl) B[n - 1] = v;
+                if (xh) B[n + 1] = v;
+                if (yl) {
+                    B[n - nx] = v;
+                    if (xl) B[n - nx - 1] = v;
+                    if (xh) B[n - nx + 1] = v;
+                }
+                if (yh) {
+                    B[n + nx] = v;
+                    if (xl) B[n + nx - 1] = v;
+                    if (xh) B[n + nx + 1] = v;
+                }
+            }
+        }
+        if (checked) {
+            const double m = block_max(rmax, red_scratch);
+            if (tid == 0)
+                for (int r = 0; r < nc; r++) cluster.map_shared_rank(slot, r)[(s & 1) * MINI_MAX_CTAS + rank] = m;
+        }
+        __syncthreads();  // the strip's rows of B are complete: hand the edge rows to the neighbours
+        if (rank > 0) {   // my first row -> upper halo row of the CTA below (it owns rows_per rows)
+            double* dst = cluster.map_shared_rank(buf[(s + 1) & 1], rank - 1) + (size_t)(rows_per + 1) * nx;
+            for (int t = tid; t < nx; t += nthr) dst[t] = B[nx + t];
+        }
+        if (rank < nc - 1) {  // my last row -> lower halo row of the CTA above
+            double* dst = cluster.map_shared_rank(buf[(s + 1) & 1], rank + 1);
+            for (int t = tid; t < nx; t += nthr) dst[t] = B[(size_t)myrows * nx + t];
+        }
+        cluster.sync();  // release/acquire at cluster scope: halo rows and residual slots are visible
+
+        // ---- the reference's decision about x_s (linear_solver.c:415-484), identical in every CTA
+        bool fin = false;
+        if (checked) {
+            double res = 0.0;
+            for (int r = 0; r < nc; r++) max_into(res, slot[(s & 1) * MINI_MAX_CTAS + r]);
+            res_rep = res;
+            if (s == 0) {
+                r0 = res;
+                tol = fmax(a.rel_tol * res, a.abs_tol);
+                if (res < a.abs_tol) { fin = true; status = POISSON_CONVERGED; iters = 0; }
+            } else if (res < tol || res < a.abs_tol) {
+                fin = true; status = POISSON_CONVERGED; iters = s;
+            }
+        }
+        if (!fin && s > 0 && s >= a.max_iter) {
+            fin = true; status = POISSON_MAX_ITER; iters = a.max_iter + 1;  // reference reports iter+1 (:478)
+        }
+        if (fin) { result = s & 1; break; }
+    }
+
+    // ---- x_s back to global memory: own rows, plus the ghost rows on the first / last CTA
+    {
+        const double* X = buf[result];
+        const int l0 = (rank == 0) ? 0 : 1, l1 = (rank == nc - 1) ? myrows + 1 : myrows;
+        for (int t = tid + l0 * nx; t < (l1 + 1) * nx; t += nthr) x[(size_t)(jb - 1) * nx + t] = X[t];
+    }
+    if (rank == 0 && tid == 0) {
+        ctl->r0 = r0;
+        ctl->tol = tol;
+        ctl->res = res_rep;
+        ctl->status = status;
+        ctl->iterations = iters;
+        ctl->result_buf = 0;
+        ctl->skip_final_bc = 0;
+        ctl->done_seq = 0;
+    }
+    cluster.sync();  // no CTA exits while a neighbour may still address its shared memory
+}
+
+}  // namespace
+
+bool jacobi_cluster_available(const LaunchCtx& L) {
+    if (getenv("CFD_B200_NO_CLUSTER_JACOBI")) return false;  // read per solve: tests toggle it
+    MiniPlan p;
+    return mini_plan(L.g, p);
+}
+
+// Whole solve in one launch; x is updated in place.  false => not launched (use the per-sweep kernels).
+bool launch_jacobi_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs) {
+    MiniPlan p;
+    if (!mini_plan(L.g, p)) return false;
+    static bool optin = (cudaFuncSetAttribute(k_jacobi_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)MINI_MAX_SMEM) == cudaSuccess);
+    if (!optin) { cudaGetLastError(); return false; }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(p.nc, 1, 1);
+    cfg.blockDim = dim3(p.bx, p.by, 1);
+    cfg.dynamicSmemBytes = p.smem;
+    cfg.stream = L.st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = p.nc;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaSuccess;
+    CFDB_LAUNCH(KK_JACOBI_CLUSTER, L.st, (e = cudaLaunchKernelEx(&cfg, k_jacobi_cluster, L.g, x, rhs, L.ctl, a, p.rows_per)));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return true;
+}
+
+}  // namespace cfdb

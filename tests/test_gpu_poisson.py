@@ -106,6 +106,37 @@ def test_rbsor_one_pass_iteration_is_bit_exact(orc, shape, check, fused, monkeyp
     assert np.array_equal(x, xo)
 
 
+@pytest.mark.parametrize("cluster", [True, False])
+@pytest.mark.parametrize("check,cap", [(10, 2000), (1, 37), (3, 50), (7, 1)])
+@pytest.mark.parametrize("shape", [(129, 129), (33, 33), (130, 40), (17, 15), (3, 3), (5, 4), (200, 11), (24, 150)])
+def test_jacobi_cluster_solve_is_bit_exact(orc, shape, check, cap, cluster, monkeypatch):
+    """Small 2-D grids run the whole Jacobi solve in one thread-block-cluster launch
+    (poisson_mini.cu: strips in shared memory, DSMEM halo rows, one cluster barrier per sweep).
+    Converging and capped solves, several check intervals, strips of unequal height, grids with fewer
+    rows than CTAs; cluster=False forces the per-sweep kernels.  Both equal the oracle bit for bit,
+    including iteration count, status and the reported residuals."""
+    if not cluster:
+        monkeypatch.setenv("CFD_B200_NO_CLUSTER_JACOBI", "1")
+    nx, ny = shape
+    g, x, rhs = cases.poisson_problem(nx, ny, 1, seed=13)
+    x[0, 0, :] = 0.3  # caller-set ghost values enter the first residual and the first sweep as they are
+    pp = pparams("jacobi", max_iterations=cap, check_interval=check)
+    xo = x.copy()
+    dx, dy, dz = g.spacing
+    rc_o, st_o = orc.poisson(METH["jacobi"], nx, ny, 1, dx, dy, dz, pp, xo, rhs, np.zeros_like(x))
+    L = api.load()
+    n0 = L.cfd_b200_kernel_launch_count()
+    rc_g, st_g = gpu_solve("jacobi", g, x, rhs, pp)
+    launches = L.cfd_b200_kernel_launch_count() - n0
+    assert (rc_g, st_g.status, st_g.iterations) == (rc_o, st_o.status, st_o.iterations)
+    assert st_g.initial_residual == st_o.initial_residual and st_g.final_residual == st_o.final_residual
+    assert np.array_equal(x, xo)
+    if cluster:
+        assert launches <= 3, launches  # ctl reset + the solve: not one launch per sweep
+    elif st_o.iterations > 3:
+        assert launches > 3
+
+
 @pytest.mark.parametrize("shape", [(33, 33, 1), (34, 20, 18), (129, 129, 1)])
 def test_bicgstab_default_tolerance(orc, shape):
     """Default 1e-6 tolerance: same status, iteration count within 30 %, and the GPU result
