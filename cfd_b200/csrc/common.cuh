@@ -105,6 +105,22 @@ __device__ __forceinline__ double clampb(double v) {
     return __hiloint2double((int)(over ? lim : hi), (int)(over ? 0u : lo));
 }
 __device__ __forceinline__ double clamp100(double v) { return clampb<HI_100>(v); }
+// N clamps against the same limit.  In a converged flow nothing is near a limit, so the usual case is
+// "no value of any lane of the warp is over": 2 integer instructions per value (mask + running max)
+// and one warp-uniform branch instead of 6 per value; the exact clamps run only when some lane needs
+// them.  Same results as clampb<> on every value (it is only skipped where it would return v).
+template <unsigned LIM_HI, int N>
+__device__ __forceinline__ void clamp_group(double (&v)[N]) {
+    unsigned m = 0u;
+#pragma unroll
+    for (int q = 0; q < N; q++) m = max(m, abs_hi(v[q]));
+    if (__any_sync(__activemask(), m >= LIM_HI)) {
+#pragma unroll
+        for (int q = 0; q < N; q++) v[q] = clampb<LIM_HI>(v[q]);
+    }
+}
+// fmin(v, 1.0) of the reference (NaN -> 1.0) without the FP64 min expansion
+__device__ __forceinline__ double min_one(double v) { return (v <= 1.0) ? v : 1.0; }
 // running maximum in the reference's own form `if (r > m) m = r;` (linear_solver.c:304-346): a NaN
 // candidate is ignored like with fmax, without fmax's NaN-selection sequence
 __device__ __forceinline__ void max_into(double& m, double r) {
@@ -121,6 +137,18 @@ __device__ __forceinline__ double ediv(double a, double b, double y) {
     const double r = fma(-b, q, a);
     return fma(r, y, q);
 }
+
+// Quotients a / rho for several numerators of one cell (RK / Euler right-hand side: mu/rho and the
+// three pressure-gradient terms, ns_momentum_rhs_scalar.h:118,160-175): one IEEE reciprocal
+// y = RN(1/rho), then the exact-division sequence per numerator -- 1 division + 3 instructions each
+// instead of 4 divisions (~14 instructions each).  Densities outside (1e-10, 1e100] take the plain
+// division (the reciprocal could lose bits there).
+struct RhoDiv {
+    double rh, y;
+    bool plain;
+    __device__ __forceinline__ explicit RhoDiv(double rho) : rh(rho), y(1.0 / rho), plain(!(rho <= 1e100)) {}
+    __device__ __forceinline__ double operator()(double a) const { return plain ? a / rh : ediv(a, rh, y); }
+};
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll

@@ -47,26 +47,29 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
     }
     bool bad = false;
     for (int k = kb; k < ke; k++, n += g.sz) {
-        double d1[4][3], d2[3][3];  // first derivatives of u,v,w,p; second derivatives of u,v,w
+        double d1[12], d2[9];  // d1[3q+axis]: first derivatives of u,v,w,p; d2[3q+axis]: second derivatives of u,v,w
         const long long zp = (k < g.nz - 2 || !ra.wrap_z) ? n + g.sz : n - (long long)(g.nz - 3) * g.sz;
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const double* f = qin.a[q];
             if (D3) F[q].p = f[zp];
             const double e = f[n + oxp], w_ = f[n + oxm], nn = f[n + oyp], s_ = f[n + oym], cc = F[q].c;
-            d1[q][0] = clampb<HI_100>(ediv(e - w_, g.two_dx, g.inv_2dx));
-            d1[q][1] = clampb<HI_100>(ediv(nn - s_, g.two_dy, g.inv_2dy));
-            d1[q][2] = clampb<HI_100>((F[q].p - F[q].m) * g.inv_2dz);
+            d1[3 * q + 0] = ediv(e - w_, g.two_dx, g.inv_2dx);
+            d1[3 * q + 1] = ediv(nn - s_, g.two_dy, g.inv_2dy);
+            d1[3 * q + 2] = (F[q].p - F[q].m) * g.inv_2dz;
             if (q < 3) {
-                d2[q][0] = clampb<HI_1000>(ediv(e - 2.0 * cc + w_, g.dx2, g.inv_dx2));
-                d2[q][1] = clampb<HI_1000>(ediv(nn - 2.0 * cc + s_, g.dy2, g.inv_dy2));
-                d2[q][2] = clampb<HI_1000>((F[q].p - 2.0 * cc + F[q].m) * g.inv_dz2);
+                d2[3 * q + 0] = ediv(e - 2.0 * cc + w_, g.dx2, g.inv_dx2);
+                d2[3 * q + 1] = ediv(nn - 2.0 * cc + s_, g.dy2, g.inv_dy2);
+                d2[3 * q + 2] = (F[q].p - 2.0 * cc + F[q].m) * g.inv_dz2;
             }
         }
+        clamp_group<HI_100>(d1);
+        clamp_group<HI_1000>(d2);
         const double rh = __ldg(rho + n);
         double kq[4] = {0.0, 0.0, 0.0, 0.0};
         if (rh > 1e-10) {
-            const double nu = fmin(c.mu / fmax(rh, 1e-10), 1.0);
+            const RhoDiv over_rho(rh);
+            const double nu = min_one(over_rho(c.mu));  // fmin(mu / fmax(rho, 1e-10), 1): rho > 1e-10 here
             double fu = su, fv = sv, fw = 0.0;
             if (c.beta != 0.0) {
                 const double dT = __ldg(T + n) - c.T_ref;
@@ -78,9 +81,9 @@ k_rk_stage(Geom g, NsConst c, RkArgs ra, int zchunk, P4 qin, P4 q0, W4 acc, W4 q
             const double src[3] = {fu, fv, fw};
 #pragma unroll
             for (int q = 0; q < 3; q++)
-                kq[q] = -uc * d1[q][0] - vc * d1[q][1] - wc * d1[q][2] - d1[3][q] / rh +
-                        nu * (d2[q][0] + d2[q][1] + d2[q][2]) + src[q];
-            const double div = clampb<HI_10>(d1[0][0] + d1[1][1] + d1[2][2]);
+                kq[q] = -uc * d1[3 * q] - vc * d1[3 * q + 1] - wc * d1[3 * q + 2] - over_rho(d1[9 + q]) +
+                        nu * (d2[3 * q] + d2[3 * q + 1] + d2[3 * q + 2]) + src[q];
+            const double div = clampb<HI_10>(d1[0] + d1[4] + d1[8]);
             kq[3] = -0.1 * rh * div;
         }
 #pragma unroll
@@ -168,23 +171,26 @@ struct RkOp {
                 a0[q] = ra.first ? 0.0 : acc.a[q][n];
             }
         }
-        double d1[4][3], d2[3][3];
+        double d1[12], d2[9];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const double cc = s.c(q);
-            d1[q][0] = clampb<HI_100>(ediv(s.e(q) - s.w(q), g.two_dx, g.inv_2dx));
-            d1[q][1] = clampb<HI_100>(ediv(s.n(q) - s.s(q), g.two_dy, g.inv_2dy));
-            d1[q][2] = clampb<HI_100>((s.p(q) - s.m(q)) * g.inv_2dz);
+            d1[3 * q + 0] = ediv(s.e(q) - s.w(q), g.two_dx, g.inv_2dx);
+            d1[3 * q + 1] = ediv(s.n(q) - s.s(q), g.two_dy, g.inv_2dy);
+            d1[3 * q + 2] = (s.p(q) - s.m(q)) * g.inv_2dz;
             if (q < 3) {
-                d2[q][0] = clampb<HI_1000>(ediv(s.e(q) - 2.0 * cc + s.w(q), g.dx2, g.inv_dx2));
-                d2[q][1] = clampb<HI_1000>(ediv(s.n(q) - 2.0 * cc + s.s(q), g.dy2, g.inv_dy2));
-                d2[q][2] = clampb<HI_1000>((s.p(q) - 2.0 * cc + s.m(q)) * g.inv_dz2);
+                d2[3 * q + 0] = ediv(s.e(q) - 2.0 * cc + s.w(q), g.dx2, g.inv_dx2);
+                d2[3 * q + 1] = ediv(s.n(q) - 2.0 * cc + s.s(q), g.dy2, g.inv_dy2);
+                d2[3 * q + 2] = (s.p(q) - 2.0 * cc + s.m(q)) * g.inv_dz2;
             }
         }
+        clamp_group<HI_100>(d1);
+        clamp_group<HI_1000>(d2);
         const double rh = pw[0];
         double kq[4] = {0.0, 0.0, 0.0, 0.0};
         if (rh > 1e-10) {
-            const double nu = fmin(c.mu / fmax(rh, 1e-10), 1.0);
+            const RhoDiv over_rho(rh);
+            const double nu = min_one(over_rho(c.mu));
             double fu = c.src_on ? su_tab[j] * ra.src_decay : 0.0, fv = c.src_on ? sv_tab[i] * ra.src_decay : 0.0, fw = 0.0;
             if (c.beta != 0.0) {
                 const double dT = pw[1] - c.T_ref;
@@ -196,9 +202,9 @@ struct RkOp {
             const double src[3] = {fu, fv, fw};
 #pragma unroll
             for (int q = 0; q < 3; q++)
-                kq[q] = -uc * d1[q][0] - vc * d1[q][1] - wc * d1[q][2] - d1[3][q] / rh +
-                        nu * (d2[q][0] + d2[q][1] + d2[q][2]) + src[q];
-            const double div = clampb<HI_10>(d1[0][0] + d1[1][1] + d1[2][2]);
+                kq[q] = -uc * d1[3 * q] - vc * d1[3 * q + 1] - wc * d1[3 * q + 2] - over_rho(d1[9 + q]) +
+                        nu * (d2[3 * q] + d2[3 * q + 1] + d2[3 * q + 2]) + src[q];
+            const double div = clampb<HI_10>(d1[0] + d1[4] + d1[8]);
             kq[3] = -0.1 * rh * div;
         }
         const int cs = (j - 1 - y0) >> 3;  // which of the thread's two cells (rows ly and ly + 8)
@@ -258,12 +264,15 @@ k_rk_stage_tma(const __grid_constant__ TmaSet<4> tm, Geom g, NsConst c, RkArgs r
 // their state (:399-401).  Interior cells only; out of place.
 // ---------------------------------------------------------------------------------------
 struct EulerCell {
-    // d1[q][axis]: clamped first derivatives of u,v,w,p; d2[q][axis]: clamped second derivatives of u,v,w
+    // d1[3q+axis]: raw first derivatives of u,v,w,p; d2[3q+axis]: raw second derivatives of u,v,w (clamped here)
     __device__ __forceinline__ static bool update(const NsConst& c, const EulerArgs& ea, const double (&cc)[4],
-                                                  const double (&d1)[4][3], const double (&d2)[3][3], double rh,
+                                                  double (&d1)[12], double (&d2)[9], double rh,
                                                   double Tc, double su, double sv, double (&out)[4]) {
+        clamp_group<HI_100>(d1);
+        clamp_group<HI_1000>(d2);
         if (rh > 1e-10) {
-            const double nu = fmin(c.mu / fmax(rh, 1e-10), 1.0);
+            const RhoDiv over_rho(rh);
+            const double nu = min_one(over_rho(c.mu));  // fmin(mu / fmax(rho, 1e-10), 1): rho > 1e-10 here
             double fu = su, fv = sv, fw = 0.0;
             if (c.beta != 0.0) {
                 const double dT = Tc - c.T_ref;
@@ -274,11 +283,11 @@ struct EulerCell {
             const double src[3] = {fu, fv, fw};
 #pragma unroll
             for (int q = 0; q < 3; q++) {
-                const double inc = ea.dt * (-cc[0] * d1[q][0] - cc[1] * d1[q][1] - cc[2] * d1[q][2] - d1[3][q] / rh +
-                                            nu * (d2[q][0] + d2[q][1] + d2[q][2]) + src[q]);
+                const double inc = ea.dt * (-cc[0] * d1[3 * q] - cc[1] * d1[3 * q + 1] - cc[2] * d1[3 * q + 2] - over_rho(d1[9 + q]) +
+                                            nu * (d2[3 * q] + d2[3 * q + 1] + d2[3 * q + 2]) + src[q]);
                 out[q] = clamp100(cc[q] + clampb<HI_1>(inc));
             }
-            const double div = clampb<HI_10>(d1[0][0] + d1[1][1] + d1[2][2]);
+            const double div = clampb<HI_10>(d1[0] + d1[4] + d1[8]);
             out[3] = cc[3] + clampb<HI_1>(ea.p_factor * rh * div);
         } else {
 #pragma unroll
@@ -308,20 +317,20 @@ k_euler(Geom g, NsConst c, EulerArgs ea, int zchunk, P4 qin, W4 qout, const doub
     }
     bool bad = false;
     for (int k = kb; k < ke; k++, n += g.sz) {
-        double d1[4][3], d2[3][3], cc[4], out[4];
+        double d1[12], d2[9], cc[4], out[4];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const double* f = qin.a[q];
             if (D3) F[q].p = f[n + g.sz];
             const double e = f[n + 1], w_ = f[n - 1], nn = f[n + g.sy], s_ = f[n - g.sy];
             cc[q] = F[q].c;
-            d1[q][0] = clampb<HI_100>(ediv(e - w_, g.two_dx, g.inv_2dx));
-            d1[q][1] = clampb<HI_100>(ediv(nn - s_, g.two_dy, g.inv_2dy));
-            d1[q][2] = clampb<HI_100>((F[q].p - F[q].m) * g.inv_2dz);
+            d1[3 * q + 0] = ediv(e - w_, g.two_dx, g.inv_2dx);
+            d1[3 * q + 1] = ediv(nn - s_, g.two_dy, g.inv_2dy);
+            d1[3 * q + 2] = (F[q].p - F[q].m) * g.inv_2dz;
             if (q < 3) {
-                d2[q][0] = clampb<HI_1000>(ediv(e - 2.0 * cc[q] + w_, g.dx2, g.inv_dx2));
-                d2[q][1] = clampb<HI_1000>(ediv(nn - 2.0 * cc[q] + s_, g.dy2, g.inv_dy2));
-                d2[q][2] = clampb<HI_1000>((F[q].p - 2.0 * cc[q] + F[q].m) * g.inv_dz2);
+                d2[3 * q + 0] = ediv(e - 2.0 * cc[q] + w_, g.dx2, g.inv_dx2);
+                d2[3 * q + 1] = ediv(nn - 2.0 * cc[q] + s_, g.dy2, g.inv_dy2);
+                d2[3 * q + 2] = (F[q].p - 2.0 * cc[q] + F[q].m) * g.inv_dz2;
             }
         }
         bad |= EulerCell::update(c, ea, cc, d1, d2, __ldg(rho + n), (c.beta != 0.0) ? __ldg(T + n) : 0.0, su, sv, out);
@@ -352,17 +361,17 @@ struct EulerOp {
         pw[1] = (c.beta != 0.0) ? __ldg(T + n) : 0.0;
     }
     __device__ __forceinline__ void cell(const St<4>& s, const double (&pw)[2], long long n, int i, int j, int) {
-        double d1[4][3], d2[3][3], cc[4], out[4];
+        double d1[12], d2[9], cc[4], out[4];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             cc[q] = s.c(q);
-            d1[q][0] = clampb<HI_100>(ediv(s.e(q) - s.w(q), g.two_dx, g.inv_2dx));
-            d1[q][1] = clampb<HI_100>(ediv(s.n(q) - s.s(q), g.two_dy, g.inv_2dy));
-            d1[q][2] = clampb<HI_100>((s.p(q) - s.m(q)) * g.inv_2dz);
+            d1[3 * q + 0] = ediv(s.e(q) - s.w(q), g.two_dx, g.inv_2dx);
+            d1[3 * q + 1] = ediv(s.n(q) - s.s(q), g.two_dy, g.inv_2dy);
+            d1[3 * q + 2] = (s.p(q) - s.m(q)) * g.inv_2dz;
             if (q < 3) {
-                d2[q][0] = clampb<HI_1000>(ediv(s.e(q) - 2.0 * cc[q] + s.w(q), g.dx2, g.inv_dx2));
-                d2[q][1] = clampb<HI_1000>(ediv(s.n(q) - 2.0 * cc[q] + s.s(q), g.dy2, g.inv_dy2));
-                d2[q][2] = clampb<HI_1000>((s.p(q) - 2.0 * cc[q] + s.m(q)) * g.inv_dz2);
+                d2[3 * q + 0] = ediv(s.e(q) - 2.0 * cc[q] + s.w(q), g.dx2, g.inv_dx2);
+                d2[3 * q + 1] = ediv(s.n(q) - 2.0 * cc[q] + s.s(q), g.dy2, g.inv_dy2);
+                d2[3 * q + 2] = (s.p(q) - 2.0 * cc[q] + s.m(q)) * g.inv_dz2;
             }
         }
         const double su = c.src_on ? su_tab[j] * ea.src_decay : 0.0, sv = c.src_on ? sv_tab[i] * ea.src_decay : 0.0;

@@ -251,3 +251,9 @@ def test_exact_division_sequence(orc):
     for q, h in enumerate(hs):
         for b in (2.0 * h, h * h):
             assert fn(b, 1234567 + q, 1_000_000) == 0, b
+    # the RK / Euler right-hand sides divide mu and the pressure gradient by the CELL's density with the
+    # same sequence from y = RN(1/rho) (RhoDiv in common.cuh): arbitrary divisors, not a handful of spacings
+    rng = np.random.default_rng(77)
+    for q, b in enumerate(np.concatenate([1.0 + 0.1 * rng.random(300), 10.0 ** rng.uniform(-9, 9, 300),
+                                          [1.0, 1000.0, 998.2, 1.225, 0.9999999999999999, 1.9999999999999998]])):
+        assert fn(float(b), 99 + q, 20_000) == 0, b

@@ -18,11 +18,12 @@ sys.path.insert(0, ROOT)
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shape", default="512,512,512")
-    ap.add_argument("--stepper", default="projection", choices=["projection", "rk2", "rk4"])
+    ap.add_argument("--stepper", default="projection", choices=["projection", "euler", "rk2", "rk4", "poisson"])
     ap.add_argument("--method", default="bicgstab")
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--rhs", default="random", choices=["random", "smooth"], help="--stepper poisson: right-hand side")
     ap.add_argument("--energy", action="store_true", help="alpha > 0, beta != 0 (natural-convection kernels)")
     a = ap.parse_args()
     import torch
@@ -41,9 +42,27 @@ def main():
     pc = abi.poisson_config(a.method, max_iterations=a.iters, tolerance=0.0, absolute_tolerance=0.0,
                             on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
 
+    if a.stepper == "poisson":  # stand-alone solves: x = 0 and a zero-mean rhs, uploaded once per solve
+        import numpy as np
+        rhs = abi.aligned_zeros(nx * ny * nz).reshape(nz, ny, nx)
+        sl = (slice(1, -1) if nz > 1 else slice(None), slice(1, -1), slice(1, -1))
+        if a.rhs == "random":
+            rhs[sl] = np.random.default_rng(5).standard_normal(rhs[sl].shape)
+        else:
+            xs = np.linspace(0.0, 1.0, nx)
+            rhs[sl] = (np.cos(np.pi * xs)[None, None, :] * np.ones((nz, ny, 1)))[sl]
+        rhs[sl] -= rhs[sl].mean()
+        x0 = abi.aligned_zeros(nx * ny * nz).reshape(nz, ny, nx)
+
     def run(k):
         if a.stepper == "projection":
             rc, _ = s.projection(p, pc, k)
+        elif a.stepper == "poisson":
+            rc = 0
+            for _ in range(k):
+                s.poisson(pc, x0, rhs)
+        elif a.stepper == "euler":
+            rc, _ = s.rk(1, p, k)
         else:
             rc, _ = s.rk(int(a.stepper[2]), p, k)
         if rc != 0:

@@ -73,8 +73,8 @@ def worker(impl, what, n, steps, iters):
         L.cfd_b200_set_poisson_config.argtypes = [C.POINTER(abi.PoissonConfig)]
         assert L.cfd_b200_set_poisson_config(C.byref(pc)) == 0
     out = {"impl": impl, "workload": what, "n": n, "cells": n ** 3}
-    if what in ("projection", "rk4"):
-        fn = L.solve_projection_method_gpu if what == "projection" else L.solve_rk4_method_gpu
+    if what in ("projection", "rk4", "rk2", "explicit_euler"):
+        fn = getattr(L, "solve_%s_method_gpu" % what)
         fn.restype, fn.argtypes = C.c_int, [FF, GR, NP, GC]
         g, f0 = host_state(n)
         p = abi.ns_params_default()
@@ -138,11 +138,16 @@ def worker(impl, what, n, steps, iters):
             C.CDLL(None).free(C.cast(s, C.c_void_p))
             return dt, st.iterations
         solve(2)
-        ta, ia = solve(iters)
-        tb, ib = solve(3 * iters)
-        per = (tb - ta) / max(ib - ia, 1)
-        out.update({"iterations": [ia, ib], "ms_per_iteration": per * 1e3, "mlups_per_iteration": n ** 3 / per / 1e6,
-                    "solve_ms_at_%d_iterations" % iters: ta * 1e3})
+        # solve time is linear in the iteration count: least-squares slope over four counts (two samples each)
+        counts = [iters, 2 * iters, 3 * iters, 5 * iters]
+        pts = []
+        for c in counts:
+            t, it = min(solve(c), solve(c))
+            pts.append((it, t))
+        mx, my = sum(p[0] for p in pts) / len(pts), sum(p[1] for p in pts) / len(pts)
+        per = sum((p[0] - mx) * (p[1] - my) for p in pts) / sum((p[0] - mx) ** 2 for p in pts)
+        out.update({"iterations": [p[0] for p in pts], "solve_ms": [round(p[1] * 1e3, 2) for p in pts],
+                    "ms_per_iteration": per * 1e3, "mlups_per_iteration": n ** 3 / per / 1e6})
     print("RESULT " + json.dumps(out), flush=True)
 
 
