@@ -37,7 +37,7 @@ enum KernelKind {
     KK_NEUMANN = 0, KK_JACOBI, KK_REDBLACK, KK_LINF, KK_STAT_FINAL, KK_KRYLOV_INIT, KK_CG_DIR,
     KK_CG_UPDATE, KK_BICG_DIR, KK_BICG_S, KK_BICG_UPDATE, KK_PREDICTOR, KK_DIVERGENCE,
     KK_CORRECTOR, KK_THERMAL_BC, KK_PERIODIC_BC, KK_RK_STAGE, KK_FIELD_STATS, KK_SYNTH_INIT,
-    KK_COPY, KK_EULER, KK_BOUNDARY, KK_FILL, KK_CTL_RESET, KK_RBSOR_FUSED, KK_JACOBI_CLUSTER, KK_COUNT
+    KK_COPY, KK_EULER, KK_BOUNDARY, KK_FILL, KK_CTL_RESET, KK_RBSOR_FUSED, KK_JACOBI_CLUSTER, KK_CG_CLUSTER, KK_COUNT
 };
 extern const char* const kKernelNames[KK_COUNT];
 extern const double kKernelBytesPerCell[KK_COUNT];
@@ -69,6 +69,9 @@ bool launch_rbsor_fused(const LaunchCtx& L, const KArgs& a, const double* xin, d
 // whole Jacobi solve of a small 2-D grid in one thread-block-cluster launch (poisson_mini.cu); x in place
 bool jacobi_cluster_available(const LaunchCtx& L);
 bool launch_jacobi_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs);
+// whole (P)CG solve of a small 2-D grid in one cluster launch; the caller runs the Neumann passes around it
+bool cg_cluster_available(const LaunchCtx& L);
+bool launch_cg_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs, int precond);
 void launch_linf_residual(const LaunchCtx& L, const KArgs& a, const double* x, const double* rhs, int slot);
 void launch_stationary_final(const LaunchCtx& L, const KArgs& a);
 void launch_krylov_init(const LaunchCtx& L, const KArgs& a, const double* x, const double* rhs, double* r,

@@ -174,6 +174,14 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         a.it = a.max_iter;
         launch_stationary_final(L, a);
         (void)poll.final_state();
+    } else if (method == POISSON_METHOD_CG && R == 1 && cg_cluster_available(L) &&
+               (launch_neumann_fill(L, x, 0, 0, false), a.seq = seq,
+                launch_cg_cluster(L, a, x, rhs, pp.preconditioner == POISSON_PRECOND_JACOBI))) {
+        // small 2-D grid: the whole (P)CG solve ran in one cluster launch between the two Neumann passes
+        // (a failed launch leaves only the -- idempotent -- initial pass behind and falls through)
+        seq++;
+        launch_neumann_fill(L, x, 0, 1, true);
+        (void)poll.final_state();
     } else if (method == POISSON_METHOD_CG) {
         const int pre = (pp.preconditioner == POISSON_PRECOND_JACOBI);
         for (int q = 0; q < 4; q++)

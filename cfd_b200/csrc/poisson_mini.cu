@@ -37,12 +37,15 @@ struct MiniPlan {
     size_t smem;
 };
 
-// Shared memory of one CTA: A[(rows_per+2)*nx], B[(rows_per+2)*nx], rhs[rows_per*nx], slot[2][MINI_MAX_CTAS]
-static size_t mini_smem(int nx, int rows_per) {
+// Shared memory of one CTA.
+//   Jacobi: A[(rows_per+2)*nx], B[(rows_per+2)*nx], rhs[rows_per*nx], slot[2][MINI_MAX_CTAS]
+//   CG    : p[(rows_per+2)*nx], x[rows_per*nx], r[rows_per*nx], Ap[rows_per*nx], slot[3][MINI_MAX_CTAS]
+static size_t mini_smem(int nx, int rows_per, bool cg) {
+    if (cg) return ((size_t)(4 * rows_per + 2) * nx + 3 * MINI_MAX_CTAS) * sizeof(double);
     return ((size_t)(2 * (rows_per + 2) + rows_per) * nx + 2 * MINI_MAX_CTAS) * sizeof(double);
 }
 
-static bool mini_plan(const Geom& g, MiniPlan& p) {
+static bool mini_plan(const Geom& g, MiniPlan& p, bool cg = false) {
     if (g.dim3 || g.nx < 3 || g.ny < 3) return false;
     if (!(g.glo[0] && g.ghi[0] && g.glo[1] && g.ghi[1])) return false;  // single rank only
     const int ni = g.ny - 2;
@@ -52,13 +55,20 @@ static bool mini_plan(const Geom& g, MiniPlan& p) {
     while (nc > 1 && ((ni + nc - 1) / nc) * (nc - 1) >= ni) nc >>= 1;  // every CTA owns at least one row
     p.nc = nc;
     p.rows_per = (ni + nc - 1) / nc;
-    p.smem = mini_smem(g.nx, p.rows_per);
+    p.smem = mini_smem(g.nx, p.rows_per, cg);
     if (p.smem > MINI_MAX_SMEM) return false;
     int bx = 32;
     while (bx < 128 && bx < g.nx - 2) bx <<= 1;
     p.bx = bx;
     p.by = MINI_THREADS / bx;
     return true;
+}
+
+// Barrier over the cluster; a one-CTA "cluster" only needs the block barrier (the hardware cluster barrier
+// costs about a microsecond even then).
+__device__ __forceinline__ void cluster_barrier(cg::cluster_group& cluster, int nc) {
+    if (nc > 1) cluster.sync();
+    else __syncthreads();
 }
 
 __device__ __forceinline__ double block_max(double v, double* scratch) {
@@ -97,7 +107,7 @@ k_jacobi_cluster(Geom g, double* __restrict__ x, const double* __restrict__ rhs_
     for (int t = tid; t < myrows * nx; t += nthr) rhs[t] = rhs_g[(size_t)jb * nx + t];
     // (the second buffer needs no initialisation: each sweep produces every cell of the strip it later
     // reads -- own rows with their ghost columns, the ghost rows, the halo rows pushed by the neighbours)
-    __syncthreads();
+    cluster_barrier(cluster, nc);  // all CTAs of the cluster are running before anyone addresses a neighbour's shared memory
 
     double r0 = 0.0, tol = 0.0, res_rep = 0.0;
     int status = POISSON_ERROR, iters = 0, result = 0;
@@ -151,7 +161,7 @@ k_jacobi_cluster(Geom g, double* __restrict__ x, const double* __restrict__ rhs_
             double* dst = cluster.map_shared_rank(buf[(s + 1) & 1], rank + 1);
             for (int t = tid; t < nx; t += nthr) dst[t] = B[(size_t)myrows * nx + t];
         }
-        cluster.sync();  // release/acquire at cluster scope: halo rows and residual slots are visible
+        cluster_barrier(cluster, nc);  // release/acquire at cluster scope: halo rows and residual slots are visible
 
         // ---- the reference's decision about x_s (linear_solver.c:415-484), identical in every CTA
         bool fin = false;
@@ -189,24 +199,192 @@ k_jacobi_cluster(Geom g, double* __restrict__ x, const double* __restrict__ rhs_
         ctl->skip_final_bc = 0;
         ctl->done_seq = 0;
     }
-    cluster.sync();  // no CTA exits while a neighbour may still address its shared memory
+    cluster_barrier(cluster, nc);  // no CTA exits while a neighbour may still address its shared memory
 }
 
-}  // namespace
-
-bool jacobi_cluster_available(const LaunchCtx& L) {
-    if (getenv("CFD_B200_NO_CLUSTER_JACOBI")) return false;  // read per solve: tests toggle it
-    MiniPlan p;
-    return mini_plan(L.g, p);
+// Sum of NV per-thread partials over the block (fixed order: lane tree, then warps 0..15), valid in thread 0.
+template <int NV>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double* scratch) {
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nw = (int)((blockDim.x * blockDim.y) >> 5);
+#pragma unroll
+    for (int q = 0; q < NV; q++) {
+        v[q] = warp_sum(v[q]);
+        if (lane == 0) scratch[q * 32 + wid] = v[q];
+    }
+    __syncthreads();
+    if (tid == 0) {
+#pragma unroll
+        for (int q = 0; q < NV; q++) {
+            double t = 0.0;
+            for (int w = 0; w < nw; w++) t += scratch[q * 32 + w];
+            v[q] = t;
+        }
+    }
 }
 
-// Whole solve in one launch; x is updated in place.  false => not launched (use the per-sweep kernels).
-bool launch_jacobi_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs) {
-    MiniPlan p;
-    if (!mini_plan(L.g, p)) return false;
-    static bool optin = (cudaFuncSetAttribute(k_jacobi_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)MINI_MAX_SMEM) == cudaSuccess);
-    if (!optin) { cudaGetLastError(); return false; }
+// ---------------------------------------------------------------------------------------
+// Whole (P)CG solve of a small 2-D grid in one cluster launch.  Same recurrences, decisions, status
+// codes and iteration counts as k_krylov_init / k_cg_dir / k_cg_update (linear_solver_cg.c:290-461);
+// the dot products are summed thread -> warp -> block -> cluster ranks in a fixed order (deterministic;
+// another order than the per-kernel path, so equal to the reference within the CG tolerance, not bitwise).
+// x must carry its Neumann ghosts on entry (the host runs k_neumann_fill before, and the final
+// BC pass -- which honours Ctl::skip_final_bc -- after).  Three cluster barriers per iteration: halo rows of
+// the new direction, p.Ap, {r.r, r.z}.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(MINI_THREADS, 1)
+k_cg_cluster(Geom g, double* __restrict__ x_g, const double* __restrict__ rhs_g, Ctl* ctl, KArgs a, int rows_per,
+             int precond) {
+    extern __shared__ __align__(16) double sm[];
+    __shared__ double red_scratch[2 * 32];
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank(), nc = (int)cluster.num_blocks();
+    const int nx = g.nx, ny = g.ny;
+    const int jb = 1 + rank * rows_per, je = min(jb + rows_per, ny - 1);
+    const int myrows = je - jb;
+    double* P = sm;                                   // rows jb-1 .. je (local l = 0 .. myrows+1), ghosts / halos included
+    double* X = P + (size_t)(rows_per + 2) * nx;      // own rows only: local row l-1
+    double* R = X + (size_t)rows_per * nx;
+    double* AP = R + (size_t)rows_per * nx;
+    double* slot = AP + (size_t)rows_per * nx;        // [3][MINI_MAX_CTAS]: p.Ap, r.r, r.z
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x, nthr = blockDim.x * blockDim.y;
+
+    auto share = [&](int which, double v) {           // thread 0: my partial into every CTA's slot
+        for (int r = 0; r < nc; r++) cluster.map_shared_rank(slot, r)[which * MINI_MAX_CTAS + rank] = v;
+    };
+    auto total = [&](int which) {                     // after the barrier: same sum, same order, in every CTA
+        double t = 0.0;
+        for (int r = 0; r < nc; r++) t += slot[which * MINI_MAX_CTAS + r];
+        return t;
+    };
+    auto push_halo = [&]() {                          // edge rows of P -> the neighbours' halo rows
+        if (rank > 0) {
+            double* dst = cluster.map_shared_rank(P, rank - 1) + (size_t)(rows_per + 1) * nx;
+            for (int t = tid; t < nx; t += nthr) dst[t] = P[nx + t];
+        }
+        if (rank < nc - 1) {
+            double* dst = cluster.map_shared_rank(P, rank + 1);
+            for (int t = tid; t < nx; t += nthr) dst[t] = P[(size_t)myrows * nx + t];
+        }
+    };
+
+    // ---- r = -rhs + lap(x), z = r or dinv r, p0 = z (boundary cells of p stay 0), r.r, r.z
+    for (int t = tid; t < (rows_per + 2) * nx; t += nthr) P[t] = 0.0;
+    cluster_barrier(cluster, nc);  // every CTA runs and has cleared its strip before a neighbour pushes a halo row into it
+    double acc[2] = {0.0, 0.0};
+    for (int l = 1 + (int)threadIdx.y; l <= myrows; l += blockDim.y) {
+        const size_t gn0 = (size_t)(jb + l - 1) * nx;
+        for (int i = 1 + (int)threadIdx.x; i < nx - 1; i += blockDim.x) {
+            const size_t n = gn0 + i;
+            const double zc = x_g[n], zm = 0.0, zp = 0.0;
+            const double lap = (x_g[n + 1] - 2.0 * zc + x_g[n - 1]) * g.inv_dx2 +
+                               (x_g[n + nx] - 2.0 * zc + x_g[n - nx]) * g.inv_dy2 + (zp + zm - 2.0 * zc) * g.inv_dz2;
+            const double rv = -rhs_g[n] + lap;
+            const double zv = precond ? a.dinv * rv : rv;
+            const int m = (l - 1) * nx + i;
+            X[m] = zc;
+            R[m] = rv;
+            P[l * nx + i] = zv;
+            acc[0] += rv * rv;
+            acc[1] += rv * zv;
+        }
+    }
+    block_sum<2>(acc, red_scratch);
+    if (tid == 0) { share(1, acc[0]); share(2, acc[1]); }
+    __syncthreads();
+    push_halo();
+    cluster_barrier(cluster, nc);
+    double rr = total(1), rz = total(2);
+
+    double r0 = 0.0, tol = 0.0, res_fin = 0.0, rho_old = 0.0;
+    int status = POISSON_ERROR, iters = 0, skip_bc = 0;
+    for (int it = 0;; it++) {
+        // ---- decisions at the start of iteration `it` (cg_dir_prologue)
+        const double rho_new = precond ? rz : rr;
+        const double res = sqrt(rr);
+        double beta = 0.0;
+        if (it == 0) {
+            r0 = res;
+            tol = fmax(a.rel_tol * res, a.abs_tol);
+            if (res < a.abs_tol) { status = POISSON_CONVERGED; iters = 0; res_fin = res; skip_bc = 1; break; }
+        } else {
+            const bool conv = (res < tol || res < a.abs_tol);
+            if (((it - 1) % a.check) == 0 && conv) { status = POISSON_CONVERGED; iters = it; res_fin = res; skip_bc = 0; break; }
+            if (fabs(rho_old) < 1e-30) { status = POISSON_STAGNATED; iters = it; res_fin = res; skip_bc = 1; break; }
+            if (it >= a.max_iter) {
+                status = conv ? POISSON_CONVERGED : POISSON_MAX_ITER; iters = a.max_iter; res_fin = res; skip_bc = 0;
+                break;
+            }
+            beta = rho_new / rho_old;
+            // ---- p = z + beta p on the own cells, then the halo rows
+            for (int l = 1 + (int)threadIdx.y; l <= myrows; l += blockDim.y)
+                for (int i = 1 + (int)threadIdx.x; i < nx - 1; i += blockDim.x) {
+                    const double rv = R[(l - 1) * nx + i];
+                    P[l * nx + i] = (precond ? a.dinv * rv : rv) + beta * P[l * nx + i];
+                }
+            __syncthreads();
+            push_halo();
+            cluster_barrier(cluster, nc);
+        }
+        // ---- Ap = -lap(p), p.Ap
+        double pap[1] = {0.0};
+        for (int l = 1 + (int)threadIdx.y; l <= myrows; l += blockDim.y)
+            for (int i = 1 + (int)threadIdx.x; i < nx - 1; i += blockDim.x) {
+                const int n = l * nx + i;
+                const double cc = P[n], cm = 0.0, cp = 0.0;
+                const double ce = P[n + 1], cw = P[n - 1], cn = P[n + nx], cs = P[n - nx];
+                const double Ac = -((ce - 2.0 * cc + cw) * g.inv_dx2 + (cn - 2.0 * cc + cs) * g.inv_dy2 +
+                                    (cp + cm - 2.0 * cc) * g.inv_dz2);
+                AP[n - nx] = Ac;
+                pap[0] += cc * Ac;
+            }
+        block_sum<1>(pap, red_scratch);
+        if (tid == 0) share(0, pap[0]);
+        cluster_barrier(cluster, nc);
+        const double pAp = total(0);
+        // ---- x += alpha p, r -= alpha Ap, r.r, r.z (k_cg_update)
+        if (fabs(pAp) < 1e-30) {
+            status = POISSON_STAGNATED; iters = it + 1; res_fin = (it == 0) ? r0 : sqrt(rr); skip_bc = 1;
+            break;
+        }
+        const double alpha = rho_new / pAp;
+        acc[0] = acc[1] = 0.0;
+        for (int l = 1 + (int)threadIdx.y; l <= myrows; l += blockDim.y)
+            for (int i = 1 + (int)threadIdx.x; i < nx - 1; i += blockDim.x) {
+                const int m = (l - 1) * nx + i;
+                X[m] += alpha * P[l * nx + i];
+                const double rv = R[m] - alpha * AP[m];
+                R[m] = rv;
+                acc[0] += rv * rv;
+                acc[1] += rv * (a.dinv * rv);
+            }
+        block_sum<2>(acc, red_scratch);
+        if (tid == 0) { share(1, acc[0]); share(2, acc[1]); }
+        cluster_barrier(cluster, nc);
+        rho_old = rho_new;
+        rr = total(1);
+        rz = total(2);
+    }
+
+    // ---- interior of x back to global memory; the ghosts follow in the host's final BC pass
+    for (int l = 1 + (int)threadIdx.y; l <= myrows; l += blockDim.y)
+        for (int i = 1 + (int)threadIdx.x; i < nx - 1; i += blockDim.x)
+            x_g[(size_t)(jb + l - 1) * nx + i] = X[(l - 1) * nx + i];
+    if (rank == 0 && tid == 0) {
+        ctl->r0 = r0;
+        ctl->tol = tol;
+        ctl->res = res_fin;
+        ctl->status = status;
+        ctl->iterations = iters;
+        ctl->result_buf = 0;
+        ctl->skip_final_bc = skip_bc;
+        ctl->done_seq = 0;
+    }
+    cluster_barrier(cluster, nc);
+}
+
+template <class K, class... Args>
+static bool launch_cluster(const LaunchCtx& L, const MiniPlan& p, int kind, K kernel, Args... args) {
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3(p.nc, 1, 1);
@@ -221,12 +399,46 @@ bool launch_jacobi_cluster(const LaunchCtx& L, const KArgs& a, double* x, const 
     cfg.attrs = at;
     cfg.numAttrs = 1;
     cudaError_t e = cudaSuccess;
-    CFDB_LAUNCH(KK_JACOBI_CLUSTER, L.st, (e = cudaLaunchKernelEx(&cfg, k_jacobi_cluster, L.g, x, rhs, L.ctl, a, p.rows_per)));
+    CFDB_LAUNCH(kind, L.st, (e = cudaLaunchKernelEx(&cfg, kernel, args...)));
     if (e != cudaSuccess) {
         cudaGetLastError();
         return false;
     }
     return true;
+}
+
+}  // namespace
+
+bool cg_cluster_available(const LaunchCtx& L) {
+    if (getenv("CFD_B200_NO_CLUSTER_CG")) return false;  // read per solve: tests toggle it
+    MiniPlan p;
+    return mini_plan(L.g, p, true);
+}
+
+// Whole (P)CG solve in one launch (between the host's two Neumann passes); false => not launched.
+bool launch_cg_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs, int precond) {
+    MiniPlan p;
+    if (!mini_plan(L.g, p, true)) return false;
+    static bool optin = (cudaFuncSetAttribute(k_cg_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)MINI_MAX_SMEM) == cudaSuccess);
+    if (!optin) { cudaGetLastError(); return false; }
+    return launch_cluster(L, p, KK_CG_CLUSTER, k_cg_cluster, L.g, x, rhs, L.ctl, a, p.rows_per, precond);
+}
+
+bool jacobi_cluster_available(const LaunchCtx& L) {
+    if (getenv("CFD_B200_NO_CLUSTER_JACOBI")) return false;  // read per solve: tests toggle it
+    MiniPlan p;
+    return mini_plan(L.g, p);
+}
+
+// Whole solve in one launch; x is updated in place.  false => not launched (use the per-sweep kernels).
+bool launch_jacobi_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs) {
+    MiniPlan p;
+    if (!mini_plan(L.g, p)) return false;
+    static bool optin = (cudaFuncSetAttribute(k_jacobi_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)MINI_MAX_SMEM) == cudaSuccess);
+    if (!optin) { cudaGetLastError(); return false; }
+    return launch_cluster(L, p, KK_JACOBI_CLUSTER, k_jacobi_cluster, L.g, x, rhs, L.ctl, a, p.rows_per);
 }
 
 }  // namespace cfdb

@@ -137,6 +137,44 @@ def test_jacobi_cluster_solve_is_bit_exact(orc, shape, check, cap, cluster, monk
         assert launches > 3
 
 
+@pytest.mark.parametrize("cluster", [True, False])
+@pytest.mark.parametrize("name", ["cg", "pcg"])
+@pytest.mark.parametrize("check,cap,tol", [(1, 5000, 1e-6), (3, 5000, 1e-9), (1, 7, 1e-30), (5, 1, 1e-30)])
+@pytest.mark.parametrize("shape", [(129, 129), (33, 33), (130, 40), (17, 15), (3, 3), (5, 4), (24, 150)])
+def test_cg_cluster_solve_matches_oracle(orc, shape, check, cap, tol, name, cluster, monkeypatch):
+    """Small 2-D grids run the whole (P)CG solve in one thread-block-cluster launch (poisson_mini.cu:
+    p / x / r / Ap strips in shared memory, DSMEM halo rows, three cluster barriers per iteration).
+    Converging solves, capped solves (exact iteration count and status), check intervals, unequal
+    strips, single-CTA grids; cluster=False forces the per-kernel path.  Dot products are reordered,
+    so the bar is the CG one: <= 1e-8 on x, same status, iteration count equal (+-1 at a threshold)."""
+    if not cluster:
+        monkeypatch.setenv("CFD_B200_NO_CLUSTER_CG", "1")
+    nx, ny = shape
+    g, x, rhs = cases.poisson_problem(nx, ny, 1, seed=17)
+    pp = pparams(name, max_iterations=cap, check_interval=check, tolerance=tol, absolute_tolerance=min(1e-10, tol))
+    xo = x.copy()
+    dx, dy, dz = g.spacing
+    rc_o, st_o = orc.poisson(METH[name], nx, ny, 1, dx, dy, dz, pp, xo, rhs, None)
+    L = api.load()
+    n0 = L.cfd_b200_kernel_launch_count()
+    rc_g, st_g = gpu_solve(name, g, x, rhs, pp)
+    launches = L.cfd_b200_kernel_launch_count() - n0
+    assert (rc_g, st_g.status) == (rc_o, st_o.status)
+    if tol < 1e-20:
+        assert st_g.iterations == st_o.iterations
+    else:
+        assert abs(st_g.iterations - st_o.iterations) <= 1
+    assert abs(st_g.initial_residual - st_o.initial_residual) <= 1e-9 * st_o.initial_residual
+    if st_g.iterations == st_o.iterations:
+        l2, li = cases.rel_err(x, xo)
+        assert l2 <= 1e-8 and li <= 1e-8, (l2, li)
+        assert abs(st_g.final_residual - st_o.final_residual) <= 1e-6 * max(st_o.final_residual, pp.absolute_tolerance)
+    if cluster:
+        assert launches <= 5, launches  # ctl reset, two Neumann passes, the solve
+    elif st_o.iterations > 3:
+        assert launches > 5
+
+
 @pytest.mark.parametrize("shape", [(33, 33, 1), (34, 20, 18), (129, 129, 1)])
 def test_bicgstab_default_tolerance(orc, shape):
     """Default 1e-6 tolerance: same status, iteration count within 30 %, and the GPU result
