@@ -80,6 +80,10 @@ void set_spacing(Geom& g, double dx, double dy, double dz);
 cfd_status_t dalloc(cfd_b200_session* s, double** p);           // zero-filled N doubles
 cfd_status_t session_upload(cfd_b200_session* s, const flow_field* f, int mask);
 cfd_status_t session_download(cfd_b200_session* s, flow_field* f, int mask);
+// whole-field host <-> device copies: pinned host memory directly, pageable memory through a multi-threaded
+// pinned staging pipeline (xfer.cu); returns when the data has arrived
+cfd_status_t xfer_fields(cfd_b200_session* s, double* const* dev, double* const* host, int n, size_t bytes,
+                         bool to_device);
 cfd_status_t session_set_coords(cfd_b200_session* s, const double* x, const double* y);
 cfd_status_t halo_exchange(cfd_b200_session* s, double* const* fields, int nf, bool periodic_ring);
 cfd_status_t allreduce(cfd_b200_session* s, double* dev, int n, bool is_max);

@@ -32,15 +32,13 @@ cfd_status_t session_upload(cfd_b200_session* s, const flow_field* f, int mask) 
     }
     double* dv[6];
     field_ptrs(s, dv);
-    const double* hv[6] = {f->u, f->v, f->w, f->p, f->rho, f->T};
+    double* hv[6] = {f->u, f->v, f->w, f->p, f->rho, f->T};
     for (int q = 0; q < 6; q++) {
-        if (!(mask & (1 << q))) continue;
+        if (!(mask & (1 << q))) { dv[q] = nullptr; continue; }
         if (!hv[q]) return CFD_ERROR_INVALID;
-        CFDB_CUDA_OK(cudaMemcpyAsync(dv[q], hv[q], s->N * sizeof(double), cudaMemcpyHostToDevice, s->st));
     }
     if (f->rho) s->rho0 = f->rho[0];
-    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
-    return CFD_SUCCESS;
+    return xfer_fields(s, dv, hv, 6, s->N * sizeof(double), true);
 }
 
 cfd_status_t session_download(cfd_b200_session* s, flow_field* f, int mask) {
@@ -50,12 +48,9 @@ cfd_status_t session_download(cfd_b200_session* s, flow_field* f, int mask) {
     double* dv[6];
     field_ptrs(s, dv);
     double* hv[6] = {f->u, f->v, f->w, f->p, f->rho, f->T};
-    for (int q = 0; q < 6; q++) {
-        if (!(mask & (1 << q)) || !dv[q] || !hv[q]) continue;
-        CFDB_CUDA_OK(cudaMemcpyAsync(hv[q], dv[q], s->N * sizeof(double), cudaMemcpyDeviceToHost, s->st));
-    }
-    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
-    return CFD_SUCCESS;
+    for (int q = 0; q < 6; q++)
+        if (!(mask & (1 << q))) dv[q] = nullptr;
+    return xfer_fields(s, dv, hv, 6, s->N * sizeof(double), false);
 }
 
 cfd_status_t session_set_coords(cfd_b200_session* s, const double* x, const double* y) {
@@ -203,17 +198,15 @@ cfd_status_t cfd_b200_session_upload_poisson(cfd_b200_session_t* s, const double
     CFDB_CUDA_OK(cudaSetDevice(s->dev));
     cfd_status_t rc = dalloc(s, &s->rhs);
     if (rc != CFD_SUCCESS) return rc;
-    if (x) CFDB_CUDA_OK(cudaMemcpyAsync(s->p, x, s->N * sizeof(double), cudaMemcpyHostToDevice, s->st));
-    if (rhs) CFDB_CUDA_OK(cudaMemcpyAsync(s->rhs, rhs, s->N * sizeof(double), cudaMemcpyHostToDevice, s->st));
-    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
-    return CFD_SUCCESS;
+    double* dv[2] = {x ? s->p : nullptr, rhs ? s->rhs : nullptr};
+    double* hv[2] = {const_cast<double*>(x), const_cast<double*>(rhs)};
+    return xfer_fields(s, dv, hv, 2, s->N * sizeof(double), true);
 }
 cfd_status_t cfd_b200_session_download_poisson(cfd_b200_session_t* s, double* x) {
     if (!s || !x) return CFD_ERROR_INVALID;
-    CFDB_CUDA_OK(cudaSetDevice(s->dev));
-    CFDB_CUDA_OK(cudaMemcpyAsync(x, s->p, s->N * sizeof(double), cudaMemcpyDeviceToHost, s->st));
-    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
-    return CFD_SUCCESS;
+    double* dv[1] = {s->p};
+    double* hv[1] = {x};
+    return xfer_fields(s, dv, hv, 1, s->N * sizeof(double), false);
 }
 
 }  // extern "C"
