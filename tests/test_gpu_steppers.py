@@ -523,3 +523,28 @@ def test_ghia_lid_driven_cavity_re100(orc, poisson_cfg):
     ru, rv = _ghia_rms(f, n)
     assert ru < 0.10 and rv < 0.10, (ru, rv)                  # the reference's gate
     assert abs(ru - 0.0382) < 0.004 and abs(rv - 0.0440) < 0.004, (ru, rv)  # its documented result
+
+
+def test_c1_ghia_129_jacobi_per_step_bitwise(orc):
+    """BASELINE config C1: 129 x 129 lid-driven cavity, Re = 100, dt = 2e-4, projection with the Jacobi
+    pressure solve under the reference rule (1e-6 relative, cap 2000, check every 10 sweeps; early steps
+    hit the cap and go on, as the reference GPU path does).  Odd nx: no TMA; the pressure solve is the
+    whole-solve cluster kernel.  Every step equals the oracle bit for bit, sweep counts included."""
+    n = 129
+    g, f, p = cases.cavity(n, 1, dt=2e-4)
+    pc = abi.poisson_config("jacobi", on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
+    api.set_poisson(pc)
+    fo = f.copy()
+    slv = api.GpuSolver("projection_gpu")
+    try:
+        for step in range(40):
+            cases.apply_cavity_bc(f)
+            cases.apply_cavity_bc(fo)
+            rc, _ = slv.step(f, g, p)
+            rco, sto = orc.projection(fo, g, p, pc, 1)
+            assert rc == rco == 0, step
+            for k in ("u", "v", "p"):
+                np.testing.assert_array_equal(getattr(f, k), getattr(fo, k), err_msg="%s step %d" % (k, step))
+    finally:
+        slv.close()
+        api.set_poisson("cg")
