@@ -15,6 +15,7 @@
 // per-sweep kernels (tests/test_gpu_poisson.py::test_jacobi_cluster_solve_is_bit_exact).
 #include "common.cuh"
 #include "kernels.h"
+#include "tma.cuh"
 
 #include <cooperative_groups.h>
 #include <limits.h>
@@ -90,10 +91,64 @@ __device__ __forceinline__ double block_max(double v, double* scratch) {
     return r;  // valid in thread 0
 }
 
+// One Jacobi sweep over a thread's cells: reads A (ghosts / halos valid), writes B with its Neumann ghosts,
+// optionally the L-inf residual of A.  Same expressions as k_jacobi (poisson_kernels.cu).
+template <int CPT>
+__device__ __forceinline__ void jacobi_cells(const Geom& g, const double* A, double* B, const int (&cell)[CPT],
+                                             const double (&f)[CPT], bool checked, double& rmax) {
+    const int nx = g.nx;
+    constexpr int BATCH = CPT < 4 ? CPT : 4;  // cells whose loads are in flight together
+#pragma unroll
+        for (int c0 = 0; c0 < CPT; c0 += BATCH) {
+            double xe[BATCH], xw[BATCH], yn[BATCH], ys[BATCH], zc[BATCH];
+#pragma unroll
+            for (int b = 0; b < BATCH; b++) {
+                const int n = cell[c0 + b] < 0 ? nx + 1 : (cell[c0 + b] & 0xffffff);  // idle slots read a valid cell, store nothing
+                zc[b] = A[n];
+                xe[b] = A[n + 1];
+                xw[b] = A[n - 1];
+                yn[b] = A[n + nx];
+                ys[b] = A[n - nx];
+            }
+#pragma unroll
+            for (int b = 0; b < BATCH; b++) {
+                const int c = c0 + b;
+                const double zm = 0.0, zp = 0.0;
+                if (checked && cell[c] >= 0) {
+                    const double lap = ediv(xe[b] - 2.0 * zc[b] + xw[b], g.dx2, g.inv_dx2) +
+                                       ediv(yn[b] - 2.0 * zc[b] + ys[b], g.dy2, g.inv_dy2) + (zp + zm - 2.0 * zc[b]) * g.inv_dz2;
+                    max_into(rmax, fabs(lap - f[c]));
+                }
+                const double v = -(f[c] - ediv(xe[b] + xw[b], g.dx2, g.inv_dx2) - ediv(yn[b] + ys[b], g.dy2, g.inv_dy2) -
+                                   (zp + zm) * g.inv_dz2) * g.inv_factor;
+                if (cell[c] >= 0) {
+                    // interior cell + every Neumann ghost whose nearest interior cell it is
+                    const int n = cell[c] & 0xffffff, d = cell[c] >> 24;
+                    B[n] = v;
+                    if (d) {
+                        const bool xl = d & 1, xh = d & 2, yl = d & 4, yh = d & 8;
+                        if (xl) B[n - 1] = v;
+                        if (xh) B[n + 1] = v;
+                        if (yl) {
+                            B[n - nx] = v;
+                            if (xl) B[n - nx - 1] = v;
+                            if (xh) B[n - nx + 1] = v;
+                        }
+                        if (yh) {
+                            B[n + nx] = v;
+                            if (xl) B[n + nx - 1] = v;
+                            if (xh) B[n + nx + 1] = v;
+                        }
+                    }
+                }
+            }
+        }
+}
+
 // CPT = cells per thread (compile time): a thread's cells, their ghost duties and their rhs values are fixed
 // for the whole solve and live in registers, so a sweep is straight-line code -- all shared loads of the
 // thread's cells in flight together, no index arithmetic, no inner loops (the loop-nest version spent ~500
-// instructions per warp and sweep on a 129^2 grid; ncu: issue-bound at 2.4 us per sweep).
+// instructions per warp and sweep on a 129^2 grid; ncu: latency-bound at 2.4 us per sweep).
 template <int CPT>
 __global__ void __launch_bounds__(MINI_THREADS, 1)
 k_jacobi_cluster(Geom g, double* __restrict__ x, const double* __restrict__ rhs_g, Ctl* ctl, KArgs a, int rows_per) {
@@ -143,52 +198,7 @@ k_jacobi_cluster(Geom g, double* __restrict__ x, const double* __restrict__ rhs_
         if (checked) until_check = (s == 0) ? 1 : a.check;
         until_check--;
         double rmax = 0.0;
-        constexpr int BATCH = CPT < 4 ? CPT : 4;  // cells whose loads are in flight together
-#pragma unroll
-        for (int c0 = 0; c0 < CPT; c0 += BATCH) {
-            double xe[BATCH], xw[BATCH], yn[BATCH], ys[BATCH], zc[BATCH];
-#pragma unroll
-            for (int b = 0; b < BATCH; b++) {
-                const int n = cell[c0 + b] < 0 ? nx + 1 : (cell[c0 + b] & 0xffffff);  // idle slots read a valid cell, store nothing
-                zc[b] = A[n];
-                xe[b] = A[n + 1];
-                xw[b] = A[n - 1];
-                yn[b] = A[n + nx];
-                ys[b] = A[n - nx];
-            }
-#pragma unroll
-            for (int b = 0; b < BATCH; b++) {
-                const int c = c0 + b;
-                const double zm = 0.0, zp = 0.0;
-                if (checked && cell[c] >= 0) {
-                    const double lap = ediv(xe[b] - 2.0 * zc[b] + xw[b], g.dx2, g.inv_dx2) +
-                                       ediv(yn[b] - 2.0 * zc[b] + ys[b], g.dy2, g.inv_dy2) + (zp + zm - 2.0 * zc[b]) * g.inv_dz2;
-                    max_into(rmax, fabs(lap - f[c]));
-                }
-                const double v = -(f[c] - ediv(xe[b] + xw[b], g.dx2, g.inv_dx2) - ediv(yn[b] + ys[b], g.dy2, g.inv_dy2) -
-                                   (zp + zm) * g.inv_dz2) * g.inv_factor;
-                if (cell[c] >= 0) {
-                    // interior cell + every Neumann ghost whose nearest interior cell it is
-                    const int n = cell[c] & 0xffffff, d = cell[c] >> 24;
-                    B[n] = v;
-                    if (d) {
-                        const bool xl = d & 1, xh = d & 2, yl = d & 4, yh = d & 8;
-                        if (xl) B[n - 1] = v;
-                        if (xh) B[n + 1] = v;
-                        if (yl) {
-                            B[n - nx] = v;
-                            if (xl) B[n - nx - 1] = v;
-                            if (xh) B[n - nx + 1] = v;
-                        }
-                        if (yh) {
-                            B[n + nx] = v;
-                            if (xl) B[n + nx - 1] = v;
-                            if (xh) B[n + nx + 1] = v;
-                        }
-                    }
-                }
-            }
-        }
+        jacobi_cells<CPT>(g, A, B, cell, f, checked, rmax);
         if (checked) {
             const double m = block_max(rmax, red_scratch);
             if (tid == 0)
@@ -239,6 +249,157 @@ k_jacobi_cluster(Geom g, double* __restrict__ x, const double* __restrict__ rhs_
         ctl->done_seq = 0;
     }
     cluster_barrier(cluster, nc);  // no CTA exits while a neighbour may still address its shared memory
+}
+
+// ---- neighbour-only signalling instead of a cluster barrier per sweep (opt-in: CFD_B200_CLUSTER_ASYNC=1) ----
+// cluster.sync() releases with MEMBAR.ALL.GPU and acquires with CCTL.IVALL: most of a microsecond per sweep.
+// Here every halo value travels as one st.async (STAS) that lands in the neighbour's shared memory AND
+// completes 8 bytes of transaction count on the neighbour's mbarrier; a CTA starts sweep s+1 when the two
+// halo rows of sweep s have arrived.  No other synchronisation is needed: a neighbour can only overwrite a
+// halo row of buffer b after it received my push of the sweep in which I last read b.  Residual partials of
+// the checked sweeps go the same way to every CTA's slot array (second mbarrier pair).
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_async_f64(uint32_t remote_addr, double v, uint32_t remote_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(remote_addr),
+                 "l"(__double_as_longlong(v)), "r"(remote_bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAITC_%=:\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONEC_%=;\n"
+        "bra WAITC_%=;\n"
+        "DONEC_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+template <int CPT>
+__global__ void __launch_bounds__(MINI_THREADS, 1)
+k_jacobi_cluster_async(Geom g, double* __restrict__ x, const double* __restrict__ rhs_g, Ctl* ctl, KArgs a, int rows_per) {
+    extern __shared__ __align__(16) double sm[];
+    __shared__ double red_scratch[MINI_THREADS / 32];
+    __shared__ __align__(8) uint64_t bars[4];  // [0,1] halo rows of even / odd sweeps, [2,3] residual partials
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank(), nc = (int)cluster.num_blocks();
+    const int nx = g.nx, ny = g.ny;
+    const int jb = 1 + rank * rows_per, je = min(jb + rows_per, ny - 1);
+    const int myrows = je - jb;
+    const size_t bufsz = (size_t)(rows_per + 2) * nx;
+    double* const buf0 = sm;
+    double* const buf1 = sm + bufsz;
+    double* slot = sm + 2 * bufsz;  // [2][MINI_MAX_CTAS]
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const uint32_t halo_bytes = (uint32_t)(((rank > 0) ? nx : 0) + ((rank < nc - 1) ? nx : 0)) * 8u;
+    if (tid == 0) {
+        for (int q = 0; q < 4; q++) mbar_init(&bars[q], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_expect_tx(&bars[0], halo_bytes);
+        mbar_expect_tx(&bars[1], halo_bytes);
+        mbar_expect_tx(&bars[2], (uint32_t)nc * 8u);
+        mbar_expect_tx(&bars[3], (uint32_t)nc * 8u);
+    }
+    for (int t = tid; t < (myrows + 2) * nx; t += nthr) buf0[t] = x[(size_t)(jb - 1) * nx + t];
+    int cell[CPT];
+    double f[CPT];
+    const int wi = nx - 2, mine = myrows * wi;
+#pragma unroll
+    for (int c = 0; c < CPT; c++) {
+        const int idx = tid + c * nthr;
+        cell[c] = -1;
+        f[c] = 0.0;
+        if (idx < mine) {
+            const int l = 1 + idx / wi, i = 1 + idx % wi, j = jb + l - 1;
+            cell[c] = (l * nx + i) | ((i == 1 ? 1 : 0) | (i == nx - 2 ? 2 : 0) | (j == 1 ? 4 : 0) | (j == ny - 2 ? 8 : 0)) << 24;
+            f[c] = rhs_g[(size_t)j * nx + i];
+        }
+    }
+    cluster.sync();  // strips loaded, barriers initialised and armed in every CTA
+
+    const uint32_t sm_lo = (rank > 0) ? mapa_u32(smem_u32(sm), rank - 1) : 0u;
+    const uint32_t sm_hi = (rank < nc - 1) ? mapa_u32(smem_u32(sm), rank + 1) : 0u;
+    const uint32_t bar_lo = (rank > 0) ? mapa_u32(smem_u32(&bars[0]), rank - 1) : 0u;
+    const uint32_t bar_hi = (rank < nc - 1) ? mapa_u32(smem_u32(&bars[0]), rank + 1) : 0u;
+    double r0 = 0.0, tol = 0.0, res_rep = 0.0;
+    int status = POISSON_ERROR, iters = 0, result = 0;
+    int until_check = 0, nchk = 0;
+    for (int s = 0;; s++) {
+        const double* A = (s & 1) ? buf1 : buf0;
+        double* B = (s & 1) ? buf0 : buf1;
+        const bool checked = (until_check == 0);
+        if (checked) until_check = (s == 0) ? 1 : a.check;
+        until_check--;
+        double rmax = 0.0;
+        jacobi_cells<CPT>(g, A, B, cell, f, checked, rmax);
+        if (checked) {
+            const double m = block_max(rmax, red_scratch);
+            if (tid == 0) {
+                const uint32_t so = smem_u32(slot + (nchk & 1) * MINI_MAX_CTAS + rank), bo = smem_u32(&bars[2 + (nchk & 1)]);
+                for (int r = 0; r < nc; r++) st_async_f64(mapa_u32(so, r), m, mapa_u32(bo, r));
+            }
+        }
+        __syncthreads();  // every thread is done reading A and writing B
+        {
+            const uint32_t boff = (uint32_t)(((s & 1) ? 0 : bufsz) * 8);
+            const uint32_t hb = (uint32_t)((s & 1) * 8);  // which halo barrier: sweep parity
+            if (rank > 0)
+                for (int t = tid; t < nx; t += nthr)
+                    st_async_f64(sm_lo + boff + (uint32_t)(((size_t)(rows_per + 1) * nx + t) * 8), B[nx + t], bar_lo + hb);
+            if (rank < nc - 1)
+                for (int t = tid; t < nx; t += nthr)
+                    st_async_f64(sm_hi + boff + (uint32_t)(t * 8), B[(size_t)myrows * nx + t], bar_hi + hb);
+        }
+        if (halo_bytes) {
+            mbar_wait_cluster(&bars[s & 1], (uint32_t)((s >> 1) & 1));
+            if (tid == 0) mbar_expect_tx(&bars[s & 1], halo_bytes);  // re-arm for sweep s + 2
+        }
+        bool fin = false;
+        if (checked) {
+            mbar_wait_cluster(&bars[2 + (nchk & 1)], (uint32_t)((nchk >> 1) & 1));
+            double res = 0.0;
+            for (int r = 0; r < nc; r++) max_into(res, slot[(nchk & 1) * MINI_MAX_CTAS + r]);
+            __syncwarp();
+            if (tid == 0) mbar_expect_tx(&bars[2 + (nchk & 1)], (uint32_t)nc * 8u);
+            nchk++;
+            res_rep = res;
+            if (s == 0) {
+                r0 = res;
+                tol = fmax(a.rel_tol * res, a.abs_tol);
+                if (res < a.abs_tol) { fin = true; status = POISSON_CONVERGED; iters = 0; }
+            } else if (res < tol || res < a.abs_tol) {
+                fin = true; status = POISSON_CONVERGED; iters = s;
+            }
+        }
+        if (!fin && s > 0 && s >= a.max_iter) {
+            fin = true; status = POISSON_MAX_ITER; iters = a.max_iter + 1;
+        }
+        if (fin) { result = s & 1; break; }
+    }
+    __syncthreads();
+    {
+        const double* X = result ? buf1 : buf0;
+        const int l0 = (rank == 0) ? 0 : 1, l1 = (rank == nc - 1) ? myrows + 1 : myrows;
+        for (int t = tid + l0 * nx; t < (l1 + 1) * nx; t += nthr) x[(size_t)(jb - 1) * nx + t] = X[t];
+    }
+    if (rank == 0 && tid == 0) {
+        ctl->r0 = r0;
+        ctl->tol = tol;
+        ctl->res = res_rep;
+        ctl->status = status;
+        ctl->iterations = iters;
+        ctl->result_buf = 0;
+        ctl->skip_final_bc = 0;
+        ctl->done_seq = 0;
+    }
+    cluster.sync();  // no CTA exits while a neighbour may still address its shared memory
 }
 
 // Sum of NV per-thread partials over the block (fixed order: lane tree, then warps 0..15), valid in thread 0.
@@ -478,6 +639,12 @@ static bool launch_jacobi_cluster_cpt(const LaunchCtx& L, MiniPlan p, const KArg
     if (!optin) { cudaGetLastError(); return false; }
     p.bx = MINI_THREADS;  // 1-D block: cells are dealt out by linear index
     p.by = 1;
+    if (p.nc > 1 && getenv("CFD_B200_CLUSTER_ASYNC")) {  // neighbour-only signalling (experimental, see above)
+        static bool optin2 = (cudaFuncSetAttribute(k_jacobi_cluster_async<CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   (int)MINI_MAX_SMEM) == cudaSuccess);
+        if (!optin2) { cudaGetLastError(); return false; }
+        return launch_cluster(L, p, KK_JACOBI_CLUSTER, k_jacobi_cluster_async<CPT>, L.g, x, rhs, L.ctl, a, p.rows_per);
+    }
     return launch_cluster(L, p, KK_JACOBI_CLUSTER, k_jacobi_cluster<CPT>, L.g, x, rhs, L.ctl, a, p.rows_per);
 }
 bool launch_jacobi_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs) {
