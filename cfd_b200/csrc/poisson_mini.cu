@@ -28,7 +28,7 @@ namespace cfdb {
 namespace {
 
 constexpr int MINI_THREADS = 512;
-constexpr int MINI_MAX_CTAS = 8;           // portable cluster size
+constexpr int MINI_MAX_CTAS = 16;          // slot-array stride; clusters above 8 CTAs are the non-portable size (opt-in)
 constexpr size_t MINI_MAX_SMEM = 200 * 1024;
 
 struct MiniPlan {
@@ -53,7 +53,14 @@ static bool mini_plan(const Geom& g, MiniPlan& p, bool cg = false) {
     const int ni = g.ny - 2;
     // measured on B200: a cluster barrier costs ~1.2 us per sweep, a strip ~0.3 us per cell-per-thread round:
     // grids up to ~1500 interior cells are faster on ONE CTA (block barrier only)
-    int nc = ((long long)ni * (g.nx - 2) <= 1536) ? 1 : MINI_MAX_CTAS;
+    // 16 CTAs (the non-portable cluster size, opted into per launch) halve the work per SM: measured 25-30 %
+    // faster than 8 on 129^2 / 200^2.  CFD_B200_CLUSTER_CTAS=8|4|2 selects a smaller cluster (read per solve).
+    int want = 16;
+    if (const char* e = getenv("CFD_B200_CLUSTER_CTAS")) {
+        const int v = atoi(e);
+        if (v == 16 || v == 8 || v == 4 || v == 2) want = v;
+    }
+    int nc = ((long long)ni * (g.nx - 2) <= 1536) ? 1 : want;
     while (nc > 1 && ((ni + nc - 1) / nc) * (nc - 1) >= ni) nc >>= 1;  // every CTA owns at least one row
     p.nc = nc;
     p.rows_per = (ni + nc - 1) / nc;
@@ -251,7 +258,7 @@ k_jacobi_cluster(Geom g, double* __restrict__ x, const double* __restrict__ rhs_
     cluster_barrier(cluster, nc);  // no CTA exits while a neighbour may still address its shared memory
 }
 
-// ---- neighbour-only signalling instead of a cluster barrier per sweep (opt-in: CFD_B200_CLUSTER_ASYNC=1) ----
+// ---- neighbour-only signalling instead of a cluster barrier per sweep (default; CFD_B200_CLUSTER_SYNC=1 = barrier) ----
 // cluster.sync() releases with MEMBAR.ALL.GPU and acquires with CCTL.IVALL: most of a microsecond per sweep.
 // Here every halo value travels as one st.async (STAS) that lands in the neighbour's shared memory AND
 // completes 8 bytes of transaction count on the neighbour's mbarrier; a CTA starts sweep s+1 when the two
@@ -599,6 +606,10 @@ static bool launch_cluster(const LaunchCtx& L, const MiniPlan& p, int kind, K ke
     cfg.attrs = at;
     cfg.numAttrs = 1;
     cudaError_t e = cudaSuccess;
+    if (p.nc > 8 && cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
     CFDB_LAUNCH(kind, L.st, (e = cudaLaunchKernelEx(&cfg, kernel, args...)));
     if (e != cudaSuccess) {
         cudaGetLastError();
@@ -639,7 +650,7 @@ static bool launch_jacobi_cluster_cpt(const LaunchCtx& L, MiniPlan p, const KArg
     if (!optin) { cudaGetLastError(); return false; }
     p.bx = MINI_THREADS;  // 1-D block: cells are dealt out by linear index
     p.by = 1;
-    if (p.nc > 1 && getenv("CFD_B200_CLUSTER_ASYNC")) {  // neighbour-only signalling (experimental, see above)
+    if (p.nc > 1 && !getenv("CFD_B200_CLUSTER_SYNC")) {  // neighbour-only signalling (default); _SYNC=1: cluster.sync() per sweep
         static bool optin2 = (cudaFuncSetAttribute(k_jacobi_cluster_async<CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                    (int)MINI_MAX_SMEM) == cudaSuccess);
         if (!optin2) { cudaGetLastError(); return false; }

@@ -106,17 +106,24 @@ def test_rbsor_one_pass_iteration_is_bit_exact(orc, shape, check, fused, monkeyp
     assert np.array_equal(x, xo)
 
 
-@pytest.mark.parametrize("cluster", [True, False])
+@pytest.mark.parametrize("cluster", ["async16", "sync8", "sync16", "async2", False])
 @pytest.mark.parametrize("check,cap", [(10, 2000), (1, 37), (3, 50), (7, 1)])
 @pytest.mark.parametrize("shape", [(129, 129), (33, 33), (130, 40), (17, 15), (3, 3), (5, 4), (200, 11), (24, 150)])
 def test_jacobi_cluster_solve_is_bit_exact(orc, shape, check, cap, cluster, monkeypatch):
     """Small 2-D grids run the whole Jacobi solve in one thread-block-cluster launch
     (poisson_mini.cu: strips in shared memory, DSMEM halo rows, one cluster barrier per sweep).
     Converging and capped solves, several check intervals, strips of unequal height, grids with fewer
-    rows than CTAs; cluster=False forces the per-sweep kernels.  Both equal the oracle bit for bit,
-    including iteration count, status and the reported residuals."""
+    rows than CTAs; 16 / 8 / 2 CTAs, halo rows signalled neighbour to neighbour (st.async + mbarrier,
+    the default) or through a cluster barrier per sweep; cluster=False forces the per-sweep kernels.  All
+    equal the oracle bit for bit, including iteration count, status and the reported residuals."""
+    for k in ("CFD_B200_NO_CLUSTER_JACOBI", "CFD_B200_CLUSTER_SYNC", "CFD_B200_CLUSTER_CTAS"):
+        monkeypatch.delenv(k, raising=False)
     if not cluster:
         monkeypatch.setenv("CFD_B200_NO_CLUSTER_JACOBI", "1")
+    else:
+        if cluster.startswith("sync"):
+            monkeypatch.setenv("CFD_B200_CLUSTER_SYNC", "1")
+        monkeypatch.setenv("CFD_B200_CLUSTER_CTAS", "".join(ch for ch in cluster if ch.isdigit()))
     nx, ny = shape
     g, x, rhs = cases.poisson_problem(nx, ny, 1, seed=13)
     x[0, 0, :] = 0.3  # caller-set ghost values enter the first residual and the first sweep as they are
@@ -137,7 +144,7 @@ def test_jacobi_cluster_solve_is_bit_exact(orc, shape, check, cap, cluster, monk
         assert launches > 3
 
 
-@pytest.mark.parametrize("cluster", [True, False])
+@pytest.mark.parametrize("cluster", [16, 8, False])
 @pytest.mark.parametrize("name", ["cg", "pcg"])
 @pytest.mark.parametrize("check,cap,tol", [(1, 5000, 1e-6), (3, 5000, 1e-9), (1, 7, 1e-30), (5, 1, 1e-30)])
 @pytest.mark.parametrize("shape", [(129, 129), (33, 33), (130, 40), (17, 15), (3, 3), (5, 4), (24, 150)])
@@ -147,8 +154,11 @@ def test_cg_cluster_solve_matches_oracle(orc, shape, check, cap, tol, name, clus
     Converging solves, capped solves (exact iteration count and status), check intervals, unequal
     strips, single-CTA grids; cluster=False forces the per-kernel path.  Dot products are reordered,
     so the bar is the CG one: <= 1e-8 on x, same status, iteration count equal (+-1 at a threshold)."""
+    monkeypatch.delenv("CFD_B200_NO_CLUSTER_CG", raising=False)
     if not cluster:
         monkeypatch.setenv("CFD_B200_NO_CLUSTER_CG", "1")
+    else:
+        monkeypatch.setenv("CFD_B200_CLUSTER_CTAS", str(cluster))
     nx, ny = shape
     g, x, rhs = cases.poisson_problem(nx, ny, 1, seed=17)
     pp = pparams(name, max_iterations=cap, check_interval=check, tolerance=tol, absolute_tolerance=min(1e-10, tol))
