@@ -167,10 +167,6 @@ static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm
         set_error(CFD_ERROR_UNSUPPORTED, "host source/heat-source callbacks cannot run on the GPU");
         return CFD_ERROR_UNSUPPORTED;
     }
-    if (s->desc.nranks > 1) {
-        set_error(CFD_ERROR_UNSUPPORTED, "explicit Euler is single-GPU (slab-decomposed sessions: use RK2/RK4 or the projection)");
-        return CFD_ERROR_UNSUPPORTED;
-    }
     cfd_status_t rc = check_thermal(prm, s->g.dim3);
     if (rc != CFD_SUCCESS) return rc;
     CFDB_CUDA_OK(cudaSetDevice(s->dev));
@@ -191,6 +187,11 @@ static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm
     ea.p_factor = -0.1 * ea.dt;   // -PRESSURE_UPDATE_FACTOR * conservative_dt (:518)
     c.dt = ea.dt;                 // the energy step advances by the same conservative dt (:537-539)
     CFDB_CUDA_OK(cudaMemsetAsync(&s->ctl->nonfinite, 0, sizeof(int), s->st));
+    // slabs: the stencil reads the neighbours' edge layers (plain halos; the caller's boundary velocities
+    // must survive, so velocities are never ring-wrapped), the periodic images of p / rho / T along the
+    // decomposed axis come from the ring exchange, as in the RK steppers
+    const int R = s->desc.nranks;
+    const int wrap_y = !(R > 1 && s->dec_axis == 1), wrap_z = !(R > 1 && s->dec_axis == 2);
     for (int iter = 0; iter < nsteps; iter++) {
         const LaunchCtx L = s->L();
         ea.src_decay = exp(-prm->source_decay_rate * iter * ea.dt);
@@ -198,11 +199,15 @@ static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm
         W4 out;
         double** cur[4] = {&s->u, &s->v, &s->w, &s->p};
         for (int q = 0; q < 4; q++) { in.a[q] = *cur[q]; out.a[q] = s->rk[q]; }
+        if (R > 1) {
+            double* f[6] = {s->u, s->v, s->w, s->p, s->rho, s->T};
+            halo_exchange(s, f, s->T ? 6 : 5, false);
+        }
         launch_euler(L, c, ea, in, out, s->rho, s->T, s->su_tab, s->sv_tab);
         launch_boundary_carry3(L, s->u, s->v, s->w, s->rk[0], s->rk[1], s->rk[2]);
         for (int q = 0; q < 4; q++) std::swap(*cur[q], s->rk[q]);  // memcpy(field <- new) without the copy (:528-531)
         if (energy) {
-            launch_energy(L, c, s->u, s->v, s->w, s->T, s->Tn);
+            launch_energy(L, c, s->u, s->v, s->w, s->T, s->Tn);  // (the halo of T is current: exchanged above)
             std::swap(s->T, s->Tn);
         }
         // apply_boundary_conditions (:231-314) on everything the velocity restore does not undo
@@ -212,7 +217,8 @@ static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm
         wrap[nw++] = s->rho;
         if (s->T) wrap[nw++] = s->T;  // a T that never reached the device stays on the host untouched
         if (!s->g.dim3) wrap[nw++] = s->w;
-        launch_periodic_faces(L, wrap, nw, 1, 1);
+        launch_periodic_faces(L, wrap, nw, wrap_y, wrap_z);
+        if (R > 1) halo_exchange(s, wrap, nw, true);
         if (energy) launch_thermal_bc(L, prm->thermal_bc, s->T);
         launch_boundary_scan(L, s->u, s->v, s->w, s->p);
         int bad = 0;

@@ -5,8 +5,8 @@
 
 Every rank builds the same global problem, takes its z-slab (y-slab for 2-D), steps it on its own
 GPU with halo exchange / all-reduce over NCCL inside libcfd_b200, and rank 0 compares the gathered
-result with the UNDECOMPOSED oracle: bitwise equal for Jacobi, Red-Black SOR and
-RK2/RK4 (no reduction order changes), <= 1e-8 for CG / PCG, BiCGSTAB at a fixed iteration count.
+result with the UNDECOMPOSED oracle: bitwise equal for Jacobi, Red-Black SOR,
+RK2/RK4 and explicit Euler (no reduction order changes), <= 1e-8 for CG / PCG, BiCGSTAB at a fixed iteration count.
 Prints one line per case and "MULTIGPU PARITY OK" at the end; exit code 1 on any mismatch.
 """
 import os
@@ -49,6 +49,8 @@ def main():
         pc = abi.poisson_config(method or "cg", on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE, **pkw)
         if stepper == "projection":
             rc_o, _ = orc.projection(fo, g, p, pc, nsteps)
+        elif stepper == "euler":
+            rc_o = orc.explicit_euler(fo, g, p, nsteps)
         else:
             rc_o = orc.rk(fo, g, p, int(stepper[2]), nsteps)
         loc = dist.scatter(f, world, rank)
@@ -67,6 +69,8 @@ def main():
         s.upload(loc)
         if stepper == "projection":
             rc, _ = s.projection(p, pc, nsteps)
+        elif stepper == "euler":
+            rc, _ = s.rk(1, p, nsteps)
         else:
             rc, _ = s.rk(int(stepper[2]), p, nsteps)
         s.download(loc)
@@ -111,6 +115,10 @@ def main():
     run_case("projection+rbsor 2d y-slabs", "random", (22, nyg, 1), "projection", "rbsor", max_iterations=30)
     run_case("projection+pcg 2d y-slabs", "random", (22, nyg, 1), "projection", "pcg", tol=1e-8)
     run_case("rk4 2d y-slabs", "random", (22, nyg, 1), "rk4")
+    run_case("explicit euler 3d", "random", (20, 14, nzg), "euler", nsteps=3)
+    run_case("explicit euler 3d nx odd", "random", (21, 14, nzg), "euler", nsteps=3)
+    run_case("explicit euler 2d y-slabs", "random", (22, nyg, 1), "euler", nsteps=3)
+    run_case("explicit euler + energy 3d", "natconv", (14, 14, nzg), "euler", nsteps=3)
     # even nx: the TMA kernels (odd-nx grids above take the direct kernels... 20/22 are even: both covered)
     run_case("projection+jacobi 3d nx odd", "random", (21, 14, nzg), "projection", "jacobi", max_iterations=25)
     run_case("projection+cg 3d nx odd", "random", (21, 14, nzg), "projection", "cg", tol=1e-8)
