@@ -527,7 +527,7 @@ CFD_B200_API cfd_status_t cfd_b200_session_projection(cfd_b200_session_t* s,
                                                       const cfd_b200_poisson_config_t* poisson,
                                                       int nsteps, ns_solver_stats_t* stats);
 /* Advance nsteps explicit steps: order 1 = explicit Euler with the CPU path's limiters
- * (cpu/solver_explicit_euler.c:337-582; single-rank sessions), 2 = Heun, 4 = classical RK4
+ * (cpu/solver_explicit_euler.c:337-582), 2 = Heun, 4 = classical RK4
  * (cpu/solver_rk2.c, cpu/solver_rk4.c). */
 CFD_B200_API cfd_status_t cfd_b200_session_rk(cfd_b200_session_t* s, int order,
                                               const ns_solver_params_t* params, int nsteps,
