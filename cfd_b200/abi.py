@@ -299,14 +299,17 @@ def poisson_params_default():
 
 
 def poisson_config(method="cg", **kw):
-    """Build a cfd_b200_poisson_config_t. method in {jacobi, rbsor, cg, pcg, bicgstab}."""
+    """Build a cfd_b200_poisson_config_t. method in {jacobi, rbsor, cg, pcg, bicgstab, multigrid}."""
     names = {"jacobi": POISSON_METHOD_JACOBI, "rbsor": POISSON_METHOD_REDBLACK_SOR,
-             "cg": POISSON_METHOD_CG, "pcg": POISSON_METHOD_CG, "bicgstab": POISSON_METHOD_BICGSTAB}
+             "cg": POISSON_METHOD_CG, "pcg": POISSON_METHOD_CG, "bicgstab": POISSON_METHOD_BICGSTAB,
+             "multigrid": POISSON_METHOD_MULTIGRID}
     cfg = PoissonConfig()
     cfg.method = names[method]
     cfg.params = poisson_params_default()
     if method == "jacobi":
         cfg.params.max_iterations = 2000  # linear_solver.c:275-278
+    if method == "multigrid":
+        cfg.params.max_iterations = 100  # V-cycles
     if method == "pcg":
         cfg.params.preconditioner = POISSON_PRECOND_JACOBI
     cfg.on_nonconvergence = CFD_B200_NONCONV_ERROR

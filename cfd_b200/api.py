@@ -98,7 +98,8 @@ class PoissonGpuSolver:
     FACTORIES = {abi.POISSON_METHOD_JACOBI: "create_jacobi_gpu_solver",
                  abi.POISSON_METHOD_REDBLACK_SOR: "create_redblack_gpu_solver",
                  abi.POISSON_METHOD_CG: "create_cg_gpu_solver",
-                 abi.POISSON_METHOD_BICGSTAB: "create_bicgstab_gpu_solver"}
+                 abi.POISSON_METHOD_BICGSTAB: "create_bicgstab_gpu_solver",
+                 abi.POISSON_METHOD_MULTIGRID: "cfd_b200_create_multigrid_gpu_solver"}
 
     def __init__(self, method, nx, ny, nz, dx, dy, dz, params=None):
         L = load()

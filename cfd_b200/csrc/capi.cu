@@ -39,6 +39,7 @@ void init_pcfg_locked() {
         else if (!strcmp(e, "rbsor")) g_pcfg.method = POISSON_METHOD_REDBLACK_SOR;
         else if (!strcmp(e, "pcg")) g_pcfg.params.preconditioner = POISSON_PRECOND_JACOBI;
         else if (!strcmp(e, "bicgstab")) g_pcfg.method = POISSON_METHOD_BICGSTAB;
+        else if (!strcmp(e, "multigrid")) { g_pcfg.method = POISSON_METHOD_MULTIGRID; g_pcfg.params.max_iterations = 100; }
     }
     const char* c = getenv("CFD_B200_NONCONV");
     if (c && !strcmp(c, "continue")) g_pcfg.on_nonconvergence = CFD_B200_NONCONV_CONTINUE;
@@ -241,7 +242,8 @@ cfd_b200_poisson_config_t cfd_b200_poisson_config_default(void) {
 cfd_status_t cfd_b200_set_poisson_config(const cfd_b200_poisson_config_t* cfg) {
     if (!cfg) return CFD_ERROR_INVALID;
     if (cfg->method != POISSON_METHOD_JACOBI && cfg->method != POISSON_METHOD_REDBLACK_SOR &&
-        cfg->method != POISSON_METHOD_CG && cfg->method != POISSON_METHOD_BICGSTAB)
+        cfg->method != POISSON_METHOD_CG && cfg->method != POISSON_METHOD_BICGSTAB &&
+        cfg->method != POISSON_METHOD_MULTIGRID)
         return CFD_ERROR_UNSUPPORTED;
     std::lock_guard<std::mutex> lk(g_mu);
     g_pcfg = *cfg;

@@ -224,6 +224,11 @@ poisson_solver_t* create_bicgstab_gpu_solver(void) {
     return make_ps("bicgstab_gpu", "BiCGSTAB (B200, device-resident scalars)", POISSON_METHOD_BICGSTAB, 5000);
 }
 
+// no counterpart in the reference (POISSON_METHOD_MULTIGRID is a placeholder there): same vtable, V-cycles as iterations
+poisson_solver_t* cfd_b200_create_multigrid_gpu_solver(void) {
+    return make_ps("multigrid_gpu", "Geometric multigrid, V(2,2) Red-Black Gauss-Seidel (B200)", POISSON_METHOD_MULTIGRID, 100);
+}
+
 ns_solver_t* cfd_b200_create_projection_gpu_solver(void) {
     return make_ns("projection_gpu", "B200-native projection method (predictor / Poisson / corrector on device)", 0);
 }

@@ -24,6 +24,8 @@ struct Nccl {
     int (*GroupEnd)() = nullptr;
 };
 
+struct MgState;  // multigrid hierarchy of a session (poisson_mg.cu)
+
 enum FieldMask { FM_U = 1, FM_V = 2, FM_W = 4, FM_P = 8, FM_RHO = 16, FM_T = 32, FM_ALL = 63 };
 
 }  // namespace cfdb
@@ -41,6 +43,7 @@ struct cfd_b200_session {
     double *us = nullptr, *vs = nullptr, *ws = nullptr, *pn = nullptr, *rhs = nullptr, *Tn = nullptr;
     double* xt = nullptr;     // Jacobi ping-pong buffer
     double* kv[8] = {};       // Krylov work vectors
+    cfdb::MgState* mg = nullptr;  // multigrid levels, built on the first POISSON_METHOD_MULTIGRID solve
     double* rk[12] = {};      // RK: B[4], C[4], ACC[4]
     double *su_tab = nullptr, *sv_tab = nullptr;  // device source tables [ny], [nx]
     std::vector<double> xs, ys;                   // host coordinates of local i, j
@@ -89,6 +92,11 @@ cfd_status_t halo_exchange(cfd_b200_session* s, double* const* fields, int nf, b
 cfd_status_t allreduce(cfd_b200_session* s, double* dev, int n, bool is_max);
 cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double** x,
                            double** xtmp, const double* rhs, poisson_solver_stats_t* st);
+// geometric multigrid (poisson_mg.cu): x in place, boundary cells filled at the end; one GPU only
+cfd_status_t mg_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double* x, const double* rhs,
+                      poisson_solver_stats_t* st);
+void mg_release(cfd_b200_session* s);
+int mg_level_count(cfd_b200_session* s);
 cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
                             const cfd_b200_poisson_config_t* pc, int nsteps, ns_solver_stats_t* stats);
 cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* prm, int nsteps,

@@ -41,7 +41,7 @@ def load():
               "solve_explicit_euler_method_gpu", "solve_navier_stokes_gpu"):
         proto(n, i32, [FF, GR, NP, GC])
     for n in ("create_jacobi_gpu_solver", "create_redblack_gpu_solver", "create_cg_gpu_solver",
-              "create_bicgstab_gpu_solver"):
+              "create_bicgstab_gpu_solver", "cfd_b200_create_multigrid_gpu_solver"):
         proto(n, C.POINTER(abi.PoissonSolver), [])
     proto("gpu_should_use", i32, [GC, C.c_size_t, C.c_size_t, C.c_size_t, i32])
     proto("gpu_select_device", i32, [i32])
@@ -113,7 +113,7 @@ DECLARED_SYMBOLS = [
     "bc_apply_dirichlet_velocity_gpu", "bc_apply_inlet_gpu", "bc_apply_scalar_3d_gpu", "bc_apply_velocity_3d_gpu",
     "cfd_b200_create_projection_gpu_solver", "cfd_b200_create_explicit_euler_gpu_solver",
     "cfd_b200_create_rk2_gpu_solver",
-    "cfd_b200_create_rk4_gpu_solver", "cfd_b200_poisson_config_default", "cfd_b200_set_poisson_config",
+    "cfd_b200_create_rk4_gpu_solver", "cfd_b200_create_multigrid_gpu_solver", "cfd_b200_poisson_config_default", "cfd_b200_set_poisson_config",
     "cfd_b200_get_poisson_config", "cfd_b200_last_error", "cfd_b200_version",
     "cfd_b200_kernel_launch_count", "cfd_b200_host_alloc", "cfd_b200_host_free",
     "cfd_b200_session_create", "cfd_b200_session_destroy", "cfd_b200_nccl_unique_id",

@@ -442,6 +442,10 @@ CFD_B200_API ns_solver_t* cfd_b200_create_projection_gpu_solver(void);
 CFD_B200_API ns_solver_t* cfd_b200_create_explicit_euler_gpu_solver(void); /* solver_registry.c:1247-1291 */
 CFD_B200_API ns_solver_t* cfd_b200_create_rk2_gpu_solver(void);
 CFD_B200_API ns_solver_t* cfd_b200_create_rk4_gpu_solver(void);
+/* Geometric multigrid behind the poisson_solver_t vtable (the reference reserves POISSON_METHOD_MULTIGRID,
+ * poisson_solver.h:60, without an implementation; ROADMAP.md:116,194).  iterations = V-cycles, stopping rule
+ * of linear_solver.c:397-485 on the L-infinity residual; default cap 100 cycles.  One GPU only. */
+CFD_B200_API poisson_solver_t* cfd_b200_create_multigrid_gpu_solver(void);
 
 /* ======================================================================
  * Part 3 -- backend-private extensions
@@ -464,7 +468,7 @@ typedef struct {
 
 CFD_B200_API cfd_b200_poisson_config_t cfd_b200_poisson_config_default(void);
 /* Process-wide configuration used by solve_projection_method_gpu and the factories.
- * Also settable with env CFD_B200_POISSON={jacobi,rbsor,cg,pcg,bicgstab}. */
+ * Also settable with env CFD_B200_POISSON={jacobi,rbsor,cg,pcg,bicgstab,multigrid}. */
 CFD_B200_API cfd_status_t cfd_b200_set_poisson_config(const cfd_b200_poisson_config_t* cfg);
 CFD_B200_API cfd_b200_poisson_config_t cfd_b200_get_poisson_config(void);
 

@@ -67,6 +67,8 @@ class Oracle:
         L.orc_apply_periodic.argtypes = [C.POINTER(abi.FlowField)]
         L.orc_neumann_scalar.restype = None
         L.orc_neumann_scalar.argtypes = [abi.c_double_p, C.c_size_t, C.c_size_t, C.c_size_t]
+        L.orc_mg_levels.restype = C.c_int
+        L.orc_mg_levels.argtypes = [C.c_size_t] * 3 + [C.POINTER(C.c_int)]
         L.orc_field_stats.restype = None
         L.orc_field_stats.argtypes = [C.POINTER(abi.FlowField)] + [abi.c_double_p] * 3
 
@@ -81,6 +83,17 @@ class Oracle:
 
     def explicit_euler(self, field, grid, params, nsteps=1):
         return self.lib.orc_explicit_euler(C.byref(field.c), C.byref(grid.c), C.byref(params), nsteps)
+
+    def neumann(self, x):
+        """Boundary cells = nearest interior cell, in place (orc_neumann_scalar); x is [nz, ny, nx]."""
+        nz, ny, nx = x.shape
+        self.lib.orc_neumann_scalar(abi._ptr(x), nx, ny, nz)
+
+    def mg_levels(self, nx, ny, nz):
+        """Extents (nx, ny, nz) of every level of the multigrid hierarchy (oracle_mg.inc)."""
+        ext = (C.c_int * (3 * 32))()
+        n = self.lib.orc_mg_levels(nx, ny, nz, ext)
+        return [tuple(ext[3 * l:3 * l + 3]) for l in range(n)]
 
     def poisson(self, method, nx, ny, nz, dx, dy, dz, pparams, x, rhs, x_temp=None):
         st = abi.PoissonStats()

@@ -572,10 +572,14 @@ ORC_API int orc_ref_backend_available(int method, int backend) {
 }
 #endif
 
+#include "oracle_mg.inc"
+
 ORC_API int orc_poisson_solve(int method, size_t nx, size_t ny, size_t nz, double dx, double dy,
                               double dz, const poisson_solver_params_t* prm, double* x,
                               double* x_temp, const double* rhs, poisson_solver_stats_t* stats) {
 #ifdef ORC_REF_POISSON
+    if (method != POISSON_METHOD_MULTIGRID)  /* the reference has no multigrid: the statement below runs */
+    {
     if (!g_ref_solver || g_ref_key_method != method || g_ref_key_backend != g_ref_backend ||
         g_ref_solver->nx != nx || g_ref_solver->ny != ny || g_ref_solver->nz != nz ||
         memcmp(&g_ref_key_params, prm, sizeof(*prm)) != 0) {
@@ -590,6 +594,7 @@ ORC_API int orc_poisson_solve(int method, size_t nx, size_t ny, size_t nz, doubl
         g_ref_key_params = *prm;
     }
     return poisson_solver_solve(g_ref_solver, x, x_temp, rhs, stats);
+    }
 #endif
     poisson_solver_stats_t local;
     poisson_solver_stats_t* st = stats ? stats : &local;
@@ -606,6 +611,7 @@ ORC_API int orc_poisson_solve(int method, size_t nx, size_t ny, size_t nz, doubl
             return stationary_solve(&g, POISSON_METHOD_REDBLACK_SOR, prm, x, x_temp, rhs, st);
         case POISSON_METHOD_CG: return cg_solve(&g, prm, x, rhs, st);
         case POISSON_METHOD_BICGSTAB: return bicgstab_solve(&g, prm, x, rhs, st);
+        case POISSON_METHOD_MULTIGRID: return mg_solve(&g, prm, x, rhs, st);
         default: return CFD_ERROR_UNSUPPORTED;
     }
 }

@@ -257,3 +257,61 @@ def test_exact_division_sequence(orc):
     for q, b in enumerate(np.concatenate([1.0 + 0.1 * rng.random(300), 10.0 ** rng.uniform(-9, 9, 300),
                                           [1.0, 1000.0, 998.2, 1.225, 0.9999999999999999, 1.9999999999999998]])):
         assert fn(float(b), 99 + q, 20_000) == 0, b
+
+
+# ---------------------------------------------------------------------------------------
+# Geometric multigrid (oracle_mg.inc): no reference implementation exists (poisson_solver.h:60 is a
+# placeholder), so the CPU statement is checked against the PROBLEM it must solve -- the discrete
+# system of the pinned Jacobi / Red-Black SOR restatements -- and for its convergence rate.
+# ---------------------------------------------------------------------------------------
+def test_multigrid_hierarchy(orc):
+    o = orc
+    # odd unknown counts keep every second point, even ones merge pairs; every active axis must halve
+    assert o.mg_levels(129, 129, 1) == [(129, 129, 1), (65, 65, 1), (33, 33, 1), (17, 17, 1), (9, 9, 1), (5, 5, 1)]
+    assert o.mg_levels(256, 256, 256)[:3] == [(256,) * 3, (129,) * 3, (65,) * 3]
+    assert o.mg_levels(130, 130, 6) == [(130, 130, 6), (66, 66, 4)]
+    assert o.mg_levels(3, 3, 1) == [(3, 3, 1)]
+    assert o.mg_levels(1024, 1024, 1024)[-1] == (5, 5, 5)
+
+
+@pytest.mark.parametrize("shape", [(129, 129, 1), (130, 130, 1), (66, 50, 1), (33, 33, 33), (34, 34, 34), (21, 36, 27)])
+def test_multigrid_solves_the_reference_system(orc, shape):
+    nx, ny, nz = shape
+    g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=3)
+    dx, dy, dz = g.spacing
+    pp = abi.poisson_params_default()
+    pp.max_iterations, pp.tolerance, pp.absolute_tolerance = 100, 1e-10, 1e-14
+    rc, st = orc.poisson(abi.POISSON_METHOD_MULTIGRID, nx, ny, nz, dx, dy, dz, pp, x, rhs)
+    assert rc == abi.CFD_SUCCESS and st.status == abi.POISSON_CONVERGED
+    assert st.iterations <= 25  # ~0.15-0.3 per V(2,2) cycle
+    assert st.final_residual < 1e-10 * st.initial_residual
+    # Red-Black SOR (pinned against the compiled reference) on the same system
+    xr = np.zeros_like(x)
+    pr = abi.poisson_params_default()
+    pr.max_iterations, pr.tolerance, pr.absolute_tolerance = 200000, 1e-10, 1e-14
+    rc_r, _ = orc.poisson(abi.POISSON_METHOD_REDBLACK_SOR, nx, ny, nz, dx, dy, dz, pr, xr, rhs)
+    assert rc_r == abi.CFD_SUCCESS
+    inner = (slice(1, -1) if nz > 1 else slice(None), slice(1, -1), slice(1, -1))
+    d = (x[inner] - x[inner].mean()) - (xr[inner] - xr[inner].mean())
+    assert np.abs(d).max() <= 1e-6 * np.abs(xr[inner] - xr[inner].mean()).max()
+    xb = x.copy()
+    orc.neumann(xb)
+    assert np.array_equal(xb, x)  # boundary cells = nearest interior cell, as the other methods leave them
+
+
+def test_multigrid_residual_is_the_reference_residual(orc, ref):
+    """The stopping quantity is the L-infinity norm of lap(x) - rhs: compare with the reference's own
+    poisson_solver_compute_residual-based stats on the same field (rounding apart)."""
+    g, x, rhs = cases.poisson_problem(65, 65, 1, seed=8)
+    dx, dy, dz = g.spacing
+    pp = abi.poisson_params_default()
+    pp.max_iterations, pp.tolerance = 3, 1e-30
+    rc, st = orc.poisson(abi.POISSON_METHOD_MULTIGRID, 65, 65, 1, dx, dy, dz, pp, x, rhs)
+    assert rc == abi.CFD_ERROR_MAX_ITER and st.iterations == 3
+    # one Jacobi iteration of the REFERENCE reports the residual of its input as initial_residual
+    pj = abi.poisson_params_default()
+    pj.max_iterations = 1
+    xj = x.copy()
+    _, stj = ref.poisson(abi.POISSON_METHOD_JACOBI, abi.POISSON_BACKEND_SCALAR, 65, 65, 1, dx, dy, dz, pj, xj, rhs,
+                         np.zeros_like(x))
+    assert abs(stj.initial_residual - st.final_residual) <= 1e-9 * st.final_residual
