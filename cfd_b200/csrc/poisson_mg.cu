@@ -23,6 +23,7 @@
 #include "session.h"
 
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace cfdb {
@@ -53,6 +54,12 @@ struct MgState {
     MgLv lv[MG_MAX_LEVELS];
     double h[MG_MAX_LEVELS][3], aL[MG_MAX_LEVELS][3], aR[MG_MAX_LEVELS][3];
     std::vector<double*> owned;
+    // one V-cycle + the residual check, captured once as a CUDA graph (the cycle of a small grid is ~60 launches of
+    // a few microseconds each: launch-bound); valid for the x / rhs pointers it was captured with
+    cudaGraphExec_t exec = nullptr;
+    const double *gx = nullptr, *gb = nullptr;
+    bool graph_failed = false;
+    unsigned long long graph_launches = 0, graph_kind[KK_COUNT] = {};
 };
 
 namespace {
@@ -185,13 +192,19 @@ __global__ void __launch_bounds__(256) k_mg_restrict(MgLv F, MgLv C) {
     const int K = C.lo[2] + blockIdx.z;
     if (I > C.hi[0] || J > C.hi[1]) return;
     const Taps3 tx = mg_restrict_taps(F, C, 0, I), ty = mg_restrict_taps(F, C, 1, J), tz = mg_restrict_taps(F, C, 2, K);
-    double az = 0.0;
-    for (int c = 0; c < tz.n; c++) {
+    double az = 0.0;  // (unrolled with guards: the tap arrays stay in registers)
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        if (c >= tz.n) continue;
         double ay = 0.0;
-        for (int b = 0; b < ty.n; b++) {
+#pragma unroll
+        for (int b = 0; b < 3; b++) {
+            if (b >= ty.n) continue;
             double ax = 0.0;
             const double* row = F.r + (long long)tz.f[c] * F.sz + (long long)ty.f[b] * F.sy;
-            for (int a = 0; a < tx.n; a++) ax += tx.w[a] * row[tx.f[a]];
+#pragma unroll
+            for (int a = 0; a < 3; a++)
+                if (a < tx.n) ax += tx.w[a] * row[tx.f[a]];
             ay += ty.w[b] * ax;
         }
         az += tz.w[c] * ay;
@@ -363,6 +376,7 @@ bool plan_next(MgState* st, int l, int nn[3], double nh[3], double naL[3], doubl
 
 void mg_release(cfd_b200_session* s) {
     if (!s->mg) return;
+    if (s->mg->exec) cudaGraphExecDestroy(s->mg->exec);
     for (double* p : s->mg->owned) cudaFree(p);
     delete s->mg;
     s->mg = nullptr;
@@ -435,6 +449,54 @@ cfd_status_t mg_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg,
         cudaStreamSynchronize(s->st);
         return *h_res;
     };
+    // capture (or re-use) the graph of one cycle; per-launch profiling needs the individual launches
+    const bool want_graph = !(t_prof && t_prof->on) && !st->graph_failed && !getenv("CFD_B200_NO_MG_GRAPH");
+    if (want_graph && (!st->exec || st->gx != x || st->gb != rhs)) {
+        if (st->exec) cudaGraphExecDestroy(st->exec);
+        st->exec = nullptr;
+        const unsigned long long l0 = g_launches;
+        unsigned long long k0[KK_COUNT];
+        if (t_prof) memcpy(k0, t_prof->launches, sizeof(k0));
+        cudaGraph_t graph = nullptr;
+        bool ok = cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+        if (ok) {
+            vcycle(Lc, st, 0);
+            cudaMemsetAsync(slot, 0, sizeof(double), s->st);
+            residual(Lc, st->lv[0], nullptr, slot);
+            cudaMemcpyAsync(h_res, slot, sizeof(double), cudaMemcpyDeviceToHost, s->st);
+            ok = cudaStreamEndCapture(s->st, &graph) == cudaSuccess && graph;
+        }
+        if (ok) ok = cudaGraphInstantiate(&st->exec, graph, 0) == cudaSuccess;
+        if (graph) cudaGraphDestroy(graph);
+        // nothing ran during the capture: take its launches back and remember them per replay
+        st->graph_launches = g_launches - l0;
+        g_launches = l0;
+        if (t_prof)
+            for (int k = 0; k < KK_COUNT; k++) {
+                st->graph_kind[k] = t_prof->launches[k] - k0[k];
+                t_prof->launches[k] = k0[k];
+            }
+        if (!ok) {
+            cudaGetLastError();
+            st->exec = nullptr;
+            st->graph_failed = true;  // direct launches from now on
+        }
+        st->gx = x;
+        st->gb = rhs;
+    }
+    const bool graph = want_graph && st->exec;
+    auto cycle_and_residual = [&]() -> double {
+        if (!graph) {
+            vcycle(Lc, st, 0);
+            return linf();
+        }
+        cudaGraphLaunch(st->exec, s->st);
+        g_launches += st->graph_launches;
+        if (t_prof)
+            for (int k = 0; k < KK_COUNT; k++) t_prof->launches[k] += st->graph_kind[k];
+        cudaStreamSynchronize(s->st);
+        return *h_res;
+    };
     poisson_solver_stats_t ps;
     memset(&ps, 0, sizeof(ps));
     const double r0 = linf();
@@ -449,8 +511,7 @@ cfd_status_t mg_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg,
         bool converged = false;
         int iter;
         for (iter = 0; iter < pp.max_iterations; iter++) {
-            vcycle(Lc, st, 0);
-            res = linf();
+            res = cycle_and_residual();
             if (res < tol || res < pp.absolute_tolerance) {
                 converged = true;
                 break;

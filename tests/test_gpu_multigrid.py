@@ -40,8 +40,12 @@ SHAPES = [(129, 129, 1), (130, 130, 1), (100, 64, 1), (67, 41, 1), (33, 33, 33),
           (3, 3, 1), (5, 4, 1), (4, 4, 4), (9, 9, 9), (130, 130, 6), (258, 258, 1), (66, 66, 66)]
 
 
+@pytest.mark.parametrize("graph", [True, False])
 @pytest.mark.parametrize("shape", SHAPES)
-def test_multigrid_matches_cpu_statement_bitwise(orc, shape):
+def test_multigrid_matches_cpu_statement_bitwise(orc, shape, graph, monkeypatch):
+    """graph: one V-cycle + residual check replayed as a CUDA graph (default) or launched kernel by kernel."""
+    if not graph:
+        monkeypatch.setenv("CFD_B200_NO_MG_GRAPH", "1")
     nx, ny, nz = shape
     g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=11)
     pp = mg_params()

@@ -44,17 +44,19 @@ def main():
             pc = abi.poisson_config(m, tolerance=a.tol, max_iterations=(200 if m == "multigrid" else a.cap))
             s.poisson(pc, x0, rhs)  # warm-up: allocations, hierarchy, module load
             s.sync()
-            s.reset_kernel_stats()
-            s.profile(True)
-            best = None
-            for _ in range(2):
+
+            def solve():
                 api.check(s.L.cfd_b200_session_upload_poisson(s.h, abi._ptr(x0), abi._ptr(rhs)), "upload_poisson")
                 s.sync()
                 t0 = time.perf_counter()
                 rc, _ = s.poisson(pc)
                 s.sync()
-                dt = time.perf_counter() - t0
-                best = dt if best is None else min(best, dt)
+                return rc, time.perf_counter() - t0
+            best = min(solve()[1] for _ in range(3))  # as a user runs it (multigrid: one CUDA graph per cycle)
+            s.reset_kernel_stats()
+            s.profile(True)                           # per-launch events: individual launches
+            for _ in range(2):
+                rc, _ = solve()
             s.profile(False)
             st = s.last_poisson_stats()
             ks = [k for k in s.kernel_stats() if k["total_ms"] > 0]
