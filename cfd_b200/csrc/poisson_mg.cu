@@ -39,6 +39,7 @@ struct MgLv {
     double ih2[3], vL[3], vR[3], wL[3], wR[3];  // w = 1 / v (IEEE, computed once on the host)
     long long sy, sz, total;
     double *x, *b, *r;
+    double* x2;  // ping-pong partner of x for the one-pass sweep (may be null: two-pass smoother)
 };
 
 __host__ __device__ inline double mg_vol(const MgLv& L, int d, int i) {
@@ -103,6 +104,62 @@ __global__ void __launch_bounds__(256) k_mg_smooth(MgLv L, double* x, const doub
     const int i = i0 + 2 * (blockIdx.x * blockDim.x + threadIdx.x);
     if (i > L.hi[0]) return;
     mg_relax_cell(L, x, b, i, j, k);
+}
+
+// One whole Red-Black Gauss-Seidel sweep in ONE pass, out of place (xin -> xout).  The two-pass smoother above
+// moves every sector of x and rhs once per colour; here a block loads its TX x TY x TZ tile plus a 2-cell frame
+// into shared memory (indices clamped at the walls = the mirrored neighbours), relaxes the red cells of the tile
+// plus a 1-cell frame in place, then the black cells of the tile, and writes the tile.  The frame's red cells are
+// recomputed by the neighbouring blocks from the same inputs with the same operations, so the result is
+// bit-identical to k_mg_smooth(colour 0) followed by k_mg_smooth(colour 1).
+template <int TX, int TY, int TZ, bool D3>
+__global__ void __launch_bounds__(256) k_mg_sweep2(MgLv L, const double* __restrict__ xin, double* __restrict__ xout,
+                                                   const double* __restrict__ b) {
+    constexpr int HZ = D3 ? 2 : 0;
+    constexpr int SX = TX + 4, SY = TY + 4, SZ = TZ + 2 * HZ;
+    __shared__ double sm[SZ][SY][SX];
+    const int tid = threadIdx.x;
+    const int i0 = L.lo[0] + blockIdx.x * TX, j0 = L.lo[1] + blockIdx.y * TY, k0 = D3 ? L.lo[2] + blockIdx.z * TZ : 0;
+    for (int t = tid; t < SX * SY * SZ; t += 256) {
+        const int a = t % SX, bb = (t / SX) % SY, c = t / (SX * SY);
+        const int gi = min(max(i0 - 2 + a, L.lo[0]), L.hi[0]), gj = min(max(j0 - 2 + bb, L.lo[1]), L.hi[1]);
+        const int gk = D3 ? min(max(k0 - 2 + c, L.lo[2]), L.hi[2]) : 0;
+        sm[c][bb][a] = xin[(long long)gk * L.sz + (long long)gj * L.sy + gi];
+    }
+    __syncthreads();
+    // phase 0: red cells of the tile + 1-cell frame; phase 1: black cells of the tile
+#pragma unroll
+    for (int ph = 0; ph < 2; ph++) {
+        const int F = 1 - ph;  // frame width of this phase
+        const int EX = TX + 2 * F, EY = TY + 2 * F, EZ = D3 ? TZ + 2 * F : 1;
+        const int HXR = (EX + 1) / 2;
+        for (int t = tid; t < HXR * EY * EZ; t += 256) {
+            const int u = t % HXR, bb = 2 - F + (t / HXR) % EY, c = D3 ? 2 - F + t / (HXR * EY) : 0;
+            const int gj = j0 - 2 + bb, gk = D3 ? k0 - 2 + c : 0;
+            const int a0 = 2 - F;                                     // first column of the region
+            const int par = ((i0 - 2 + a0 + gj + gk) & 1) != ph;      // skip one column if the first has the other colour
+            const int a = a0 + 2 * u + par;
+            const int gi = i0 - 2 + a;
+            if (a >= a0 + EX || gi < L.lo[0] || gi > L.hi[0] || gj < L.lo[1] || gj > L.hi[1] ||
+                (D3 && (gk < L.lo[2] || gk > L.hi[2])))
+                continue;
+            double cf[3];
+            mg_coef(L, gi, gj, gk, cf);
+            const double xc = sm[c][bb][a];
+            const double xu = D3 ? sm[c + 1][bb][a] : xc, xd = D3 ? sm[c - 1][bb][a] : xc;
+            const double sv = (cf[0] * (sm[c][bb][a + 1] + sm[c][bb][a - 1]) + cf[1] * (sm[c][bb + 1][a] + sm[c][bb - 1][a])) +
+                              cf[2] * (xu + xd);
+            const double diag = 2.0 * ((cf[0] + cf[1]) + cf[2]);
+            sm[c][bb][a] = (sv - b[(long long)gk * L.sz + (long long)gj * L.sy + gi]) / diag;
+        }
+        __syncthreads();
+    }
+    for (int t = tid; t < TX * TY * TZ; t += 256) {
+        const int a = t % TX, bb = (t / TX) % TY, c = t / (TX * TY);
+        const int gi = i0 + a, gj = j0 + bb, gk = D3 ? k0 + c : 0;
+        if (gi <= L.hi[0] && gj <= L.hi[1] && (!D3 || gk <= L.hi[2]))
+            xout[(long long)gk * L.sz + (long long)gj * L.sy + gi] = sm[c + HZ][bb + 2][a + 2];
+    }
 }
 
 // All sweeps of the coarsest level in one block (colours separated by block barriers).
@@ -283,6 +340,27 @@ inline dim3 cell_grid(const MgLv& L, int cols, dim3 blk) {
 }
 
 void smooth(const LaunchCtx& Lc, const MgLv& L, int sweeps) {
+    // (environment read per call: a fresh session re-captures its graph)
+    // Measured on B200 (profiles/r1s_mg_compare.jsonl): the one-pass sweep wins on 2-D levels (1025^2: 3.1 ms of
+    // smoothing per solve against 4.5 ms) and loses on 3-D ones (512^3: 68 ms against 52 ms -- the 36 x 12 x 12 tile
+    // re-reads 2.5 cells per cell through L2 and its phases are latency-bound), so 3-D levels keep one kernel per
+    // colour unless CFD_B200_MG_FUSED3D=1.
+    const bool fused = !getenv("CFD_B200_NO_MG_FUSED") && (L.n[2] == 1 || getenv("CFD_B200_MG_FUSED3D"));
+    if (L.x2 && sweeps % 2 == 0 && fused) {  // whole sweeps out of place, x -> x2 -> x
+        const int m0 = L.hi[0] - L.lo[0] + 1, m1 = L.hi[1] - L.lo[1] + 1, m2 = L.hi[2] - L.lo[2] + 1;
+        for (int q = 0; q < sweeps; q++) {
+            const double* in = (q & 1) ? L.x2 : L.x;
+            double* out = (q & 1) ? L.x : L.x2;
+            if (L.n[2] > 1) {
+                const dim3 grd((m0 + 31) / 32, (m1 + 7) / 8, (m2 + 7) / 8);
+                CFDB_LAUNCH(KK_MG_SWEEP2, Lc.st, (k_mg_sweep2<32, 8, 8, true><<<grd, 256, 0, Lc.st>>>(L, in, out, L.b)));
+            } else {
+                const dim3 grd((m0 + 63) / 64, (m1 + 15) / 16, 1);
+                CFDB_LAUNCH(KK_MG_SWEEP2, Lc.st, (k_mg_sweep2<64, 16, 1, false><<<grd, 256, 0, Lc.st>>>(L, in, out, L.b)));
+            }
+        }
+        return;
+    }
     const dim3 blk(32, 8);
     const int m0 = L.hi[0] - L.lo[0] + 1;
     const dim3 grd = cell_grid(L, (m0 + 1) / 2, blk);
@@ -338,7 +416,7 @@ void level_init(MgState* st, int l, const int n[3], const double h[3], const dou
     L.sy = n[0];
     L.sz = (long long)n[0] * n[1];
     L.total = L.sz * n[2];
-    L.x = L.b = L.r = nullptr;
+    L.x = L.b = L.r = L.x2 = nullptr;
 }
 
 // how level l coarsens (same rule as oracle_mg.inc: every active axis must be able to halve)
@@ -392,8 +470,8 @@ static cfd_status_t mg_prepare(cfd_b200_session* s) {
     for (;;) {
         level_init(st, st->nl, n, h, aL, aR);
         MgLv& L = st->lv[st->nl];
-        const int nbuf = st->nl == 0 ? 1 : 3;  // level 0 solves in the caller's x / rhs
-        double* buf[3] = {nullptr, nullptr, nullptr};
+        const int nbuf = st->nl == 0 ? 2 : 4;  // level 0 solves in the caller's x / rhs
+        double* buf[4] = {nullptr, nullptr, nullptr, nullptr};
         for (int q = 0; q < nbuf; q++) {
             if (cudaMalloc(&buf[q], (size_t)L.total * sizeof(double)) != cudaSuccess) {
                 cudaGetLastError();
@@ -407,8 +485,9 @@ static cfd_status_t mg_prepare(cfd_b200_session* s) {
             cudaMemsetAsync(buf[q], 0, (size_t)L.total * sizeof(double), s->st);
         }
         L.r = buf[0];
-        L.x = buf[1];
-        L.b = buf[2];
+        L.x2 = buf[1];
+        L.x = buf[2];
+        L.b = buf[3];
         st->nl++;
         int nn[3];
         double nh[3], naL[3], naR[3];

@@ -62,9 +62,14 @@ def test_poisson_config_roundtrip_without_gpu():
     assert L.cfd_b200_set_poisson_config(C.byref(cfg)) == 0
     got = L.cfd_b200_get_poisson_config()
     assert got.method == abi.POISSON_METHOD_BICGSTAB and got.params.max_iterations == 50
+    mg = abi.poisson_config("multigrid")  # the reference's placeholder method: implemented here
+    assert mg.method == abi.POISSON_METHOD_MULTIGRID and mg.params.max_iterations == 100
+    assert L.cfd_b200_set_poisson_config(C.byref(mg)) == 0
+    assert L.cfd_b200_get_poisson_config().method == abi.POISSON_METHOD_MULTIGRID
     bad = abi.poisson_config("cg")
-    bad.method = abi.POISSON_METHOD_MULTIGRID
-    assert L.cfd_b200_set_poisson_config(C.byref(bad)) == abi.CFD_ERROR_UNSUPPORTED
+    for method in (abi.POISSON_METHOD_GAUSS_SEIDEL, abi.POISSON_METHOD_SOR):  # no GPU backend in the reference either
+        bad.method = method
+        assert L.cfd_b200_set_poisson_config(C.byref(bad)) == abi.CFD_ERROR_UNSUPPORTED
     L.cfd_b200_set_poisson_config(C.byref(d))
 
 
