@@ -207,6 +207,8 @@ __global__ void __launch_bounds__(256) k_mg_residual(MgLv L, const double* __res
     }
 }
 
+constexpr int MG_ZC = 8;  // planes marched per thread by the 3-D prolongation
+
 struct Taps3 {
     int n, f[3];
     double w[3], den;
@@ -332,6 +334,44 @@ __global__ void __launch_bounds__(256) k_mg_prolong_add(MgLv F, MgLv C) {
     F.x[(long long)k * F.sz + (long long)j * F.sy + i] += tz.w[0] * vz[0] + tz.w[1] * vz[1];
 }
 
+// 3-D levels: the same prolongation with a thread marching MG_ZC fine planes; the in-plane taps are set up once
+// and the in-plane interpolation of a coarse plane is re-used by the (up to) two or three fine planes that need it.
+__global__ void __launch_bounds__(256) k_mg_prolong_add_march(MgLv F, MgLv C) {
+    const int i = F.lo[0] + blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = F.lo[1] + blockIdx.y * blockDim.y + threadIdx.y;
+    const int kb = F.lo[2] + blockIdx.z * MG_ZC, ke = min(kb + MG_ZC - 1, F.hi[2]);
+    if (i > F.hi[0] || j > F.hi[1]) return;
+    const Taps2 tx = mg_prolong_taps(F, C, 0, i), ty = mg_prolong_taps(F, C, 1, j);
+    const double* r0 = C.x + (long long)ty.I[0] * C.sy;
+    const double* r1 = C.x + (long long)ty.I[1] * C.sy;
+    auto plane = [&](int K) -> double {  // in-plane interpolation of coarse plane K at (i, j)
+        const double* p0 = r0 + (long long)K * C.sz;
+        const double* p1 = r1 + (long long)K * C.sz;
+        const double v0 = tx.w[0] * p0[tx.I[0]] + tx.w[1] * p0[tx.I[1]];
+        const double v1 = tx.w[0] * p1[tx.I[0]] + tx.w[1] * p1[tx.I[1]];
+        return ty.w[0] * v0 + ty.w[1] * v1;
+    };
+    int KA = -1, KB = -1;  // cached coarse planes
+    double vA = 0.0, vB = 0.0;
+    long long n = (long long)kb * F.sz + (long long)j * F.sy + i;
+    for (int k = kb; k <= ke; k++, n += F.sz) {
+        const Taps2 tz = mg_prolong_taps(F, C, 2, k);
+        double v[2];
+#pragma unroll
+        for (int q = 0; q < 2; q++) {
+            const int K = tz.I[q];
+            if (K == KA) v[q] = vA;
+            else if (K == KB) v[q] = vB;
+            else {
+                v[q] = plane(K);
+                // replace the older entry (planes are visited in non-decreasing order)
+                if (KA <= KB) { KA = K; vA = v[q]; } else { KB = K; vB = v[q]; }
+            }
+        }
+        F.x[n] += tz.w[0] * v[0] + tz.w[1] * v[1];
+    }
+}
+
 #endif  // __CUDACC__
 
 inline dim3 cell_grid(const MgLv& L, int cols, dim3 blk) {
@@ -370,6 +410,8 @@ void smooth(const LaunchCtx& Lc, const MgLv& L, int sweeps) {
 
 void residual(const LaunchCtx& Lc, const MgLv& L, double* r, unsigned long long* slot) {
     const dim3 blk(32, 8);
+    // (a z-marching variant of this kernel -- 6 loads per cell, reduction once per 8 cells -- was measured 25 % SLOWER
+    // at 512^3, profiles/r1u_mg_compare.jsonl: the march serialises the loads a one-cell thread has in flight at once)
     CFDB_LAUNCH(KK_MG_RESIDUAL, Lc.st,
                 k_mg_residual<<<cell_grid(L, L.hi[0] - L.lo[0] + 1, blk), blk, 0, Lc.st>>>(L, L.x, L.b, r, slot));
 }
@@ -391,8 +433,14 @@ void vcycle(const LaunchCtx& Lc, MgState* st, int l) {
     CFDB_LAUNCH(KK_MG_RESTRICT, Lc.st,
                 k_mg_restrict<<<cell_grid(C, C.hi[0] - C.lo[0] + 1, blk), blk, 0, Lc.st>>>(L, C));
     vcycle(Lc, st, l + 1);
-    CFDB_LAUNCH(KK_MG_PROLONG, Lc.st,
-                k_mg_prolong_add<<<cell_grid(L, L.hi[0] - L.lo[0] + 1, blk), blk, 0, Lc.st>>>(L, C));
+    if (L.n[2] > 1 && !getenv("CFD_B200_NO_MG_MARCH")) {
+        dim3 grd = cell_grid(L, L.hi[0] - L.lo[0] + 1, blk);
+        grd.z = (grd.z + MG_ZC - 1) / MG_ZC;
+        CFDB_LAUNCH(KK_MG_PROLONG, Lc.st, k_mg_prolong_add_march<<<grd, blk, 0, Lc.st>>>(L, C));
+    } else {
+        CFDB_LAUNCH(KK_MG_PROLONG, Lc.st,
+                    k_mg_prolong_add<<<cell_grid(L, L.hi[0] - L.lo[0] + 1, blk), blk, 0, Lc.st>>>(L, C));
+    }
     smooth(Lc, L, MG_NU2);
 }
 

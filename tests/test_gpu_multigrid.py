@@ -40,20 +40,23 @@ SHAPES = [(129, 129, 1), (130, 130, 1), (100, 64, 1), (67, 41, 1), (33, 33, 33),
           (3, 3, 1), (5, 4, 1), (4, 4, 4), (9, 9, 9), (130, 130, 6), (258, 258, 1), (66, 66, 66), (75, 21, 13)]
 
 
-@pytest.mark.parametrize("path", ["default", "no_graph", "two_pass_smoother", "one_pass_3d"])
+@pytest.mark.parametrize("path", ["default", "no_graph", "two_pass_smoother", "one_pass_3d", "no_march"])
 @pytest.mark.parametrize("shape", SHAPES)
 def test_multigrid_matches_cpu_statement_bitwise(orc, shape, path, monkeypatch):
     """default: one-pass two-colour sweeps on 2-D levels, one kernel per colour on 3-D ones, one V-cycle +
     residual check replayed as a CUDA graph; no_graph: the same kernels launched one by one;
-    two_pass_smoother: one kernel per colour everywhere; one_pass_3d: the one-pass sweep on 3-D levels too."""
+    two_pass_smoother: one kernel per colour everywhere; one_pass_3d: the one-pass sweep on 3-D levels too;
+    no_march: prolongation with one cell per thread on 3-D levels (default: z-marching threads)."""
     if path == "no_graph":
         monkeypatch.setenv("CFD_B200_NO_MG_GRAPH", "1")
     if path == "two_pass_smoother":
         monkeypatch.setenv("CFD_B200_NO_MG_FUSED", "1")
+    if path in ("one_pass_3d", "no_march") and shape[2] == 1:
+        pytest.skip("2-D grid: same kernels as the default path")
     if path == "one_pass_3d":
-        if shape[2] == 1:
-            pytest.skip("2-D grid: the default path already is the one-pass sweep")
         monkeypatch.setenv("CFD_B200_MG_FUSED3D", "1")
+    if path == "no_march":
+        monkeypatch.setenv("CFD_B200_NO_MG_MARCH", "1")
     nx, ny, nz = shape
     g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=11)
     pp = mg_params()
