@@ -122,6 +122,15 @@ def main():
     # even nx: the TMA kernels (odd-nx grids above take the direct kernels... 20/22 are even: both covered)
     run_case("projection+jacobi 3d nx odd", "random", (21, 14, nzg), "projection", "jacobi", max_iterations=25)
     run_case("projection+cg 3d nx odd", "random", (21, 14, nzg), "projection", "cg", tol=1e-8)
+    if world > 1:  # the multigrid hierarchy is single-GPU: a decomposed session must refuse it, not mis-solve
+        s = api.Session(20, 14, 8, 0.1, 0.1, 0.1, rank=rank, nranks=world, device=local)
+        rc, _ = s.poisson(abi.poisson_config("multigrid"))
+        s.close()
+        if rank == 0:
+            ok = rc == abi.CFD_ERROR_UNSUPPORTED
+            print("%-34s world=%d rc=%d %s" % ("multigrid on a slab is refused", world, rc, "ok" if ok else "FAIL"), flush=True)
+            if not ok:
+                fails.append("multigrid refusal")
     td.barrier()
     td.destroy_process_group()
     if rank == 0:
