@@ -109,3 +109,21 @@ def test_dropin_library_registers_the_gpu_names(ref):
     if not lib.load().gpu_is_available():
         assert not L.cfd_solver_create(reg, b"projection_gpu")
     L.cfd_registry_destroy(reg)
+
+
+def test_every_kernel_kind_has_a_name_and_a_byte_figure():
+    """kernels.h's KernelKind, session.cu's name and bytes-per-cell tables must stay the same length: a missing
+    initialiser would be a NULL name handed to the caller of cfd_b200_session_kernel_stats."""
+    import os
+    import re
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "cfd_b200", "csrc")
+    hdr = open(os.path.join(root, "kernels.h")).read()
+    body = re.search(r"enum KernelKind \{(.*?)\};", hdr, re.S).group(1)
+    kinds = [k.strip().split("=")[0].strip() for k in body.replace("\n", " ").split(",") if k.strip()]
+    assert kinds[-1] == "KK_COUNT"
+    src = open(os.path.join(root, "session.cu")).read()
+    names = re.search(r"kKernelNames\[KK_COUNT\] = \{(.*?)\};", src, re.S).group(1)
+    n_names = len(re.findall(r'"[^"]+"', names))
+    table = re.search(r"kKernelBytesPerCell\[KK_COUNT\] = \{(.*?)\};", src, re.S).group(1)
+    n_bytes = len(re.findall(r"\d+(?:\.\d+)?", re.sub(r"//.*", "", table)))
+    assert n_names == n_bytes == len(kinds) - 1, (n_names, n_bytes, len(kinds) - 1)

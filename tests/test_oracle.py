@@ -315,3 +315,51 @@ def test_multigrid_residual_is_the_reference_residual(orc, ref):
     _, stj = ref.poisson(abi.POISSON_METHOD_JACOBI, abi.POISSON_BACKEND_SCALAR, 65, 65, 1, dx, dy, dz, pj, xj, rhs,
                          np.zeros_like(x))
     assert abs(stj.initial_residual - st.final_residual) <= 1e-9 * st.final_residual
+
+
+def test_multigrid_cycle_is_linear_under_power_of_two_scaling(orc):
+    """One V-cycle is a linear map of (x, rhs); scaling both by a power of two scales every intermediate
+    exactly, so the iterate must scale bit for bit (a property the CUDA path inherits through parity)."""
+    g, x, rhs = cases.poisson_problem(37, 26, 1, seed=12)
+    dx, dy, dz = g.spacing
+    pp = abi.poisson_params_default()
+    pp.max_iterations, pp.tolerance, pp.absolute_tolerance = 3, 1e-30, 0.0
+    x1, x2 = x.copy(), 8.0 * x
+    orc.poisson(abi.POISSON_METHOD_MULTIGRID, 37, 26, 1, dx, dy, dz, pp, x1, rhs)
+    orc.poisson(abi.POISSON_METHOD_MULTIGRID, 37, 26, 1, dx, dy, dz, pp, x2, 8.0 * rhs)
+    assert np.array_equal(8.0 * x1, x2)
+
+
+def test_multigrid_leaves_constants_alone(orc):
+    """Constants are the null space of the all-Neumann operator: a constant start with a zero right-hand side
+    has a zero residual and comes back untouched; added to a start vector it only shifts the answer."""
+    nx, ny, nz = 20, 18, 12
+    g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=13)
+    dx, dy, dz = g.spacing
+    pp = abi.poisson_params_default()
+    pp.max_iterations = 50
+    c = np.full_like(x, 3.25)
+    rc, st = orc.poisson(abi.POISSON_METHOD_MULTIGRID, nx, ny, nz, dx, dy, dz, pp, c, np.zeros_like(x))
+    assert rc == abi.CFD_SUCCESS and st.iterations == 0 and np.all(c == 3.25)
+    xa, xb = x.copy(), x + 1.0
+    rca, sta = orc.poisson(abi.POISSON_METHOD_MULTIGRID, nx, ny, nz, dx, dy, dz, pp, xa, rhs)
+    rcb, stb = orc.poisson(abi.POISSON_METHOD_MULTIGRID, nx, ny, nz, dx, dy, dz, pp, xb, rhs)
+    assert rca == rcb == abi.CFD_SUCCESS and sta.iterations == stb.iterations
+    inner = (slice(1, -1),) * 3
+    assert np.max(np.abs((xb - xa)[inner] - 1.0)) <= 1e-9
+
+
+def test_multigrid_on_an_anisotropic_box_still_contracts(orc):
+    """hx : hz = 1 : 4 -- outside the point smoother's comfort zone: slower, but every cycle must
+    still reduce the residual."""
+    nx, ny, nz = 65, 33, 17
+    g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=14)
+    dx, dy, dz = g.spacing
+    res = []
+    for cycles in (1, 2, 3, 4):
+        pp = abi.poisson_params_default()
+        pp.max_iterations, pp.tolerance, pp.absolute_tolerance = cycles, 1e-30, 0.0
+        xc = x.copy()
+        _, st = orc.poisson(abi.POISSON_METHOD_MULTIGRID, nx, ny, nz, dx, dy, dz, pp, xc, rhs)
+        res.append(st.final_residual)
+    assert all(b < a for a, b in zip(res, res[1:]))
