@@ -176,6 +176,29 @@ __global__ void __launch_bounds__(256) k_mg_coarse(MgLv L, double* x, const doub
     }
 }
 
+// The same with the level held in shared memory (whole array, ghost layout included, so the indices are unchanged):
+// a phase of the global-memory version pays an L2 round trip on top of the division's dependent chain (60 phases =
+// 37 us per cycle); from shared memory the 60 phases take 29 us (profiles/r1x_mg_compare.jsonl) -- what is left is
+// the barrier, the rhs load and the FP64 division latency of each phase.  Same operations, same order of the colours.
+constexpr int MG_SMEM_DOUBLES = 4096;
+__global__ void __launch_bounds__(256) k_mg_coarse_smem(MgLv L, double* x, const double* __restrict__ b, int sweeps) {
+    __shared__ double xs[MG_SMEM_DOUBLES];
+    const int total = (int)L.total;
+    for (int t = threadIdx.x; t < total; t += blockDim.x) xs[t] = x[t];
+    __syncthreads();
+    const int m0 = L.hi[0] - L.lo[0] + 1, m1 = L.hi[1] - L.lo[1] + 1, m2 = L.hi[2] - L.lo[2] + 1;
+    const int cells = m0 * m1 * m2;
+    for (int q = 0; q < 2 * sweeps; q++) {
+        const int colour = q & 1;
+        for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+            const int i = L.lo[0] + c % m0, j = L.lo[1] + (c / m0) % m1, k = L.lo[2] + c / (m0 * m1);
+            if (((i + j + k) & 1) == colour) mg_relax_cell(L, xs, b, i, j, k);
+        }
+        __syncthreads();
+    }
+    for (int t = threadIdx.x; t < total; t += blockDim.x) x[t] = xs[t];
+}
+
 // r = b - A x (r may be null); the maximum of |r| goes to *slot (bits of a non-negative double order like integers).
 __global__ void __launch_bounds__(256) k_mg_residual(MgLv L, const double* __restrict__ x, const double* __restrict__ b,
                                                      double* __restrict__ r, unsigned long long* slot) {
@@ -420,7 +443,9 @@ void vcycle(const LaunchCtx& Lc, MgState* st, int l) {
     const MgLv& L = st->lv[l];
     if (l == st->nl - 1) {
         const long long cells = (long long)(L.hi[0] - L.lo[0] + 1) * (L.hi[1] - L.lo[1] + 1) * (L.hi[2] - L.lo[2] + 1);
-        if (cells <= MG_ONE_BLOCK_CELLS)
+        if (cells <= MG_ONE_BLOCK_CELLS && L.total <= MG_SMEM_DOUBLES && !getenv("CFD_B200_NO_MG_COARSE_SMEM"))
+            CFDB_LAUNCH(KK_MG_COARSE, Lc.st, k_mg_coarse_smem<<<1, 256, 0, Lc.st>>>(L, L.x, L.b, MG_NCOARSE));
+        else if (cells <= MG_ONE_BLOCK_CELLS)
             CFDB_LAUNCH(KK_MG_COARSE, Lc.st, k_mg_coarse<<<1, 256, 0, Lc.st>>>(L, L.x, L.b, MG_NCOARSE));
         else
             smooth(Lc, L, MG_NCOARSE);

@@ -40,7 +40,8 @@ SHAPES = [(129, 129, 1), (130, 130, 1), (100, 64, 1), (67, 41, 1), (33, 33, 33),
           (3, 3, 1), (5, 4, 1), (4, 4, 4), (9, 9, 9), (130, 130, 6), (258, 258, 1), (66, 66, 66), (75, 21, 13)]
 
 
-@pytest.mark.parametrize("path", ["default", "no_graph", "two_pass_smoother", "one_pass_3d", "no_march"])
+@pytest.mark.parametrize("path", ["default", "no_graph", "two_pass_smoother", "one_pass_3d", "no_march",
+                                  "coarsest_in_global_memory"])
 @pytest.mark.parametrize("shape", SHAPES)
 def test_multigrid_matches_cpu_statement_bitwise(orc, shape, path, monkeypatch):
     """default: one-pass two-colour sweeps on 2-D levels, one kernel per colour on 3-D ones, one V-cycle +
@@ -57,6 +58,8 @@ def test_multigrid_matches_cpu_statement_bitwise(orc, shape, path, monkeypatch):
         monkeypatch.setenv("CFD_B200_MG_FUSED3D", "1")
     if path == "no_march":
         monkeypatch.setenv("CFD_B200_NO_MG_MARCH", "1")
+    if path == "coarsest_in_global_memory":  # default: the coarsest level is relaxed in shared memory when it fits
+        monkeypatch.setenv("CFD_B200_NO_MG_COARSE_SMEM", "1")
     nx, ny, nz = shape
     g, x, rhs = cases.poisson_problem(nx, ny, nz, seed=11)
     pp = mg_params()
