@@ -363,3 +363,82 @@ def test_multigrid_on_an_anisotropic_box_still_contracts(orc):
         _, st = orc.poisson(abi.POISSON_METHOD_MULTIGRID, nx, ny, nz, dx, dy, dz, pp, xc, rhs)
         res.append(st.final_residual)
     assert all(b < a for a, b in zip(res, res[1:]))
+
+
+# ---------------------------------------------------------------------------------------
+# Randomised pinning: shapes, spacings, solver parameters and fields drawn by hypothesis (derandomised, so the
+# run is reproducible), the restatement against the compiled reference, bit for bit.
+# ---------------------------------------------------------------------------------------
+from hypothesis import HealthCheck, given, settings, strategies as hst  # noqa: E402
+
+_FUZZ = dict(max_examples=200, deadline=None, derandomize=True,
+             suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
+
+
+@settings(**_FUZZ)
+@given(nx=hst.integers(3, 14), ny=hst.integers(3, 14), nz=hst.sampled_from([1, 3, 4, 7, 9]),
+       name=hst.sampled_from(["jacobi", "rbsor", "cg", "pcg", "bicgstab"]), seed=hst.integers(0, 2 ** 16),
+       cap=hst.integers(1, 60), check=hst.integers(1, 7), omega=hst.sampled_from([0.0, 1.0, 1.3, 1.85]),
+       tol=hst.sampled_from([1e-6, 1e-3, 1e-10]), stretch=hst.sampled_from([(1.0, 1.0, 1.0), (1.0, 1.7, 0.6), (2.5, 1.0, 1.0)]))
+def test_fuzz_oracle_poisson_against_reference(orc, ref, nx, ny, nz, name, seed, cap, check, omega, tol, stretch):
+    rng = np.random.default_rng(seed)
+    g = abi.HostGrid(nx, ny, nz, 0.0, stretch[0], 0.0, stretch[1], 0.0, stretch[2] if nz > 1 else 0.0)
+    rhs = abi.aligned_zeros(nx * ny * nz).reshape(nz, ny, nx)
+    sl = (slice(1, -1) if nz > 1 else slice(None), slice(1, -1), slice(1, -1))
+    rhs[sl] = rng.standard_normal(rhs[sl].shape)
+    x = abi.aligned_zeros(nx * ny * nz).reshape(nz, ny, nx)
+    x[...] = 0.1 * rng.standard_normal(x.shape)
+    pp = abi.poisson_params_default()
+    pp.max_iterations, pp.check_interval, pp.omega, pp.tolerance = cap, check, omega, tol
+    if name == "pcg":
+        pp.preconditioner = abi.POISSON_PRECOND_JACOBI
+    x2 = x.copy()
+    dx, dy, dz = g.spacing
+    rc_r, st_r = ref.poisson(METH[name], abi.POISSON_BACKEND_SCALAR, nx, ny, nz, dx, dy, dz, pp, x, rhs,
+                             np.zeros_like(x))
+    rc_o, st_o = orc.poisson(METH[name], nx, ny, nz, dx, dy, dz, pp, x2, rhs, np.zeros_like(x))
+    assert (rc_r, st_r.iterations, st_r.status) == (rc_o, st_o.iterations, st_o.status)
+    assert st_r.initial_residual == st_o.initial_residual
+    assert st_r.final_residual == st_o.final_residual or (np.isnan(st_r.final_residual) and np.isnan(st_o.final_residual))
+    np.testing.assert_array_equal(x, x2)
+
+
+@settings(**dict(_FUZZ, max_examples=120))
+@given(nx=hst.integers(3, 12), ny=hst.integers(3, 12), nz=hst.sampled_from([1, 3, 5, 8]),
+       stepper=hst.sampled_from(["projection", "rk2", "rk4", "explicit_euler"]), seed=hst.integers(0, 2 ** 16),
+       scale=hst.sampled_from([0.05, 1.0, 40.0]), dt=hst.sampled_from([1e-4, 1e-3, 2e-2]),
+       amp=hst.sampled_from([(0.0, 0.0), (0.1, 0.05)]), thermal=hst.booleans())
+def test_fuzz_oracle_steppers_against_reference(orc, ref, nx, ny, nz, stepper, seed, scale, dt, amp, thermal):
+    """Large scales and time steps drive the clamps and limiters; `thermal` switches the energy equation,
+    buoyancy and the thermal boundary conditions on."""
+    g, f = cases.random_field(nx, ny, nz, seed=seed, scale=scale)
+    p = cases.params(dt=dt, amp=amp)
+    if thermal:
+        p.alpha, p.beta, p.T_ref = 1e-2, 3e-3, 300.0
+        p.gravity[1] = -9.81
+        p.thermal_bc.left, p.thermal_bc.right = abi.BC_TYPE_DIRICHLET, abi.BC_TYPE_DIRICHLET
+        p.thermal_bc.dirichlet_values.left, p.thermal_bc.dirichlet_values.right = 310.0, 290.0
+    f2 = f.copy()
+    rc_r, _ = ref.run_solver(stepper, f, g, p, 2)
+    if stepper == "projection":
+        rc_o = 0
+        for _ in range(2):
+            rc_o, _ = orc.projection(f2, g, p, abi.poisson_config("cg"), 1)
+            if rc_o != 0:
+                break
+    elif stepper == "explicit_euler":
+        rc_o = 0
+        for _ in range(2):
+            rc_o = orc.explicit_euler(f2, g, p, 1)
+            if rc_o != 0:
+                break
+    else:
+        rc_o = 0
+        for _ in range(2):
+            rc_o = orc.rk(f2, g, p, int(stepper[2]), 1)
+            if rc_o != 0:
+                break
+    assert rc_r == rc_o
+    if rc_r == 0:
+        for k in f.NAMES:
+            np.testing.assert_array_equal(getattr(f, k), getattr(f2, k), err_msg=k)
