@@ -16,6 +16,16 @@ from . import abi
 from .lib import CfdB200Error, check, last_error, load
 
 FM_U, FM_V, FM_W, FM_P, FM_RHO, FM_T, FM_ALL = 1, 2, 4, 8, 16, 32, 63
+SYNC_FULL, SYNC_UPLOAD_BOUNDARY, SYNC_DOWNLOAD_LAZY = 0, 1, 2
+
+
+def set_device_count(n):
+    """GPUs behind every drop-in call of this process (cfd_b200_set_device_count; 0 = CFD_B200_NGPU or 1)."""
+    check(load().cfd_b200_set_device_count(int(n)), "cfd_b200_set_device_count")
+
+
+def get_device_count():
+    return int(load().cfd_b200_get_device_count())
 
 
 def gpu_is_available():
@@ -66,6 +76,13 @@ class GpuSolver:
         st = abi.NSSolverStats()
         rc = self._solve(self._slv, C.byref(field.c), C.byref(grid.c), C.byref(params), C.byref(st))
         return rc, st
+
+    def set_host_sync(self, flags):
+        """SYNC_FULL | SYNC_UPLOAD_BOUNDARY | SYNC_DOWNLOAD_LAZY (cfd_b200_solver_set_host_sync)."""
+        check(load().cfd_b200_solver_set_host_sync(self._slv, int(flags)), "cfd_b200_solver_set_host_sync")
+
+    def sync_host(self, field):
+        check(load().cfd_b200_solver_sync_host(self._slv, C.byref(field.c)), "cfd_b200_solver_sync_host")
 
     def close(self):
         if self._slv:
@@ -166,6 +183,9 @@ class Session:
 
     def download(self, field, mask=FM_ALL):
         check(self.L.cfd_b200_session_download_mask(self.h, C.byref(field.c), mask), "session_download")
+
+    def set_slab(self, global_layers, global_lo):
+        check(self.L.cfd_b200_session_set_slab(self.h, global_layers, global_lo), "session_set_slab")
 
     def set_coords(self, x=None, y=None):
         """Exact cell coordinates of this slab (slices of the global grid arrays)."""

@@ -1,6 +1,6 @@
 // capi.cu -- the C-ABI: drop-in symbols with the reference's names and signatures
 // (include/cfd_b200.h Part 2) and the cfd_b200_* extension surface (Part 3).
-#include "session.h"
+#include "runner.h"
 
 #include <math.h>
 #include <mutex>
@@ -46,39 +46,6 @@ void init_pcfg_locked() {
     g_pcfg_init = true;
 }
 
-// Session cache of the stateless drop-in entry points: device buffers persist across calls
-// (the reference re-allocates 22 buffers per call, solver_projection_gpu.cu:417-436).
-cfd_b200_session* g_cached = nullptr;
-
-cfd_b200_session* cached_session(const flow_field* f, const grid* g) {
-    const double dx = g->dx[0], dy = g->dy[0];
-    const double dz = (f->nz > 1 && g->dz) ? g->dz[0] : 0.0;
-    cfd_b200_session* s = g_cached;
-    if (s && (s->desc.nx != f->nx || s->desc.ny != f->ny || s->desc.nz != f->nz || s->desc.dx != dx ||
-              s->desc.dy != dy || s->desc.dz != dz)) {
-        cfd_b200_session_destroy(s);
-        s = g_cached = nullptr;
-    }
-    if (!s) {
-        cfd_b200_session_desc_t d;
-        memset(&d, 0, sizeof(d));
-        d.nx = f->nx; d.ny = f->ny; d.nz = f->nz;
-        d.dx = dx; d.dy = dy; d.dz = dz;
-        d.xmin = g->xmin; d.ymin = g->ymin; d.zmin = g->zmin;
-        d.rank = 0; d.nranks = 1; d.device = -1;
-        s = g_cached = cfd_b200_session_create(&d);
-        static bool hooked = false;
-        if (s && !hooked) {
-            hooked = true;
-            atexit([] {
-                if (g_cached) { cfd_b200_session_destroy(g_cached); g_cached = nullptr; }
-            });
-        }
-    }
-    if (s) session_set_coords(s, g->x, g->y);
-    return s;
-}
-
 }  // namespace
 
 namespace cfdb {
@@ -113,48 +80,6 @@ cfd_status_t validate_common(const flow_field* f, const grid* g, const ns_solver
 
 namespace {
 
-// Periodic wrap of the HOST density ghost cells: the only change apply_boundary_conditions
-// makes to rho (solver_explicit_euler.c:231-314); rho is never written on the device.
-void wrap_host_rho(flow_field* f) {
-    const size_t nx = f->nx, ny = f->ny, nz = f->nz, plane = nx * ny;
-    double* r = f->rho;
-    for (size_t k = 0; k < nz; k++) {
-        double* q = r + k * plane;
-        for (size_t j = 0; j < ny; j++) { q[j * nx] = q[j * nx + nx - 2]; q[j * nx + nx - 1] = q[j * nx + 1]; }
-        for (size_t i = 0; i < nx; i++) { q[i] = q[(ny - 2) * nx + i]; q[(ny - 1) * nx + i] = q[nx + i]; }
-    }
-    if (nz > 1)
-        for (size_t n = 0; n < plane; n++) { r[n] = r[(nz - 2) * plane + n]; r[(nz - 1) * plane + n] = r[plane + n]; }
-}
-
-enum StepKind { SK_PROJECTION, SK_RK2, SK_RK4, SK_EULER };
-
-cfd_status_t run_on_session(cfd_b200_session* s, StepKind kind, flow_field* f, const ns_solver_params_t* prm,
-                            int nsteps, ns_solver_stats_t* stats) {
-    const bool thermo = (prm->alpha > 0.0 || prm->beta != 0.0);
-    cfd_status_t rc;
-    if (kind == SK_PROJECTION) {
-        rc = session_upload(s, f, FM_U | FM_V | FM_W | FM_P | (thermo ? FM_T : 0));
-        if (rc != CFD_SUCCESS) return rc;
-        cfd_b200_poisson_config_t pc = cfd_b200_get_poisson_config();
-        rc = run_projection(s, prm, &pc, nsteps, stats);
-        if (rc == CFD_SUCCESS || rc == CFD_ERROR_MAX_ITER || rc == CFD_ERROR_DIVERGED) {
-            cfd_status_t r2 = session_download(s, f, FM_U | FM_V | FM_W | FM_P | (prm->alpha > 0.0 ? FM_T : 0));
-            if (r2 != CFD_SUCCESS) return r2;
-        }
-        return rc;
-    }
-    rc = session_upload(s, f, FM_ALL);
-    if (rc != CFD_SUCCESS) return rc;
-    rc = run_rk(s, kind == SK_EULER ? 1 : (kind == SK_RK2 ? 2 : 4), prm, nsteps, stats);
-    if (rc == CFD_SUCCESS || rc == CFD_ERROR_DIVERGED) {
-        cfd_status_t r2 = session_download(s, f, FM_U | FM_V | FM_W | FM_P | FM_T);
-        if (r2 != CFD_SUCCESS) return r2;
-        if (nsteps > 0) wrap_host_rho(f);
-    }
-    return rc;
-}
-
 cfd_status_t dropin(StepKind kind, flow_field* f, const grid* g, const ns_solver_params_t* prm,
                     const gpu_config_t* config) {
     if (!f || !g || !prm) return CFD_ERROR_INVALID;
@@ -162,10 +87,17 @@ cfd_status_t dropin(StepKind kind, flow_field* f, const grid* g, const ns_solver
     if (!gpu_should_use(&cfg, f->nx, f->ny, f->nz, prm->max_iter)) return CFD_ERROR;
     cfd_status_t rc = validate_common(f, g, prm);
     if (rc != CFD_SUCCESS) return rc;
-    std::lock_guard<std::mutex> lk(g_mu);
-    cfd_b200_session* s = cached_session(f, g);
-    if (!s) return CFD_ERROR_NOMEM;
-    return run_on_session(s, kind, f, prm, prm->max_iter, nullptr);
+    // one runner per (shape, spacing, device, GPU count), used by one call at a time; different shapes run
+    // concurrently on their own runners (runner_cache_acquire)
+    Runner* r = runner_cache_acquire(f, g);
+    if (!r) return CFD_ERROR_NOMEM;
+    {
+        std::lock_guard<std::mutex> lk(r->mu);
+        rc = runner_run(r, kind, f, g, prm, prm->max_iter, nullptr, SYNC_FULL);
+        if (kind != SK_PROJECTION && (rc == CFD_SUCCESS || rc == CFD_ERROR_DIVERGED) && prm->max_iter > 0) wrap_host_rho(f);
+    }
+    runner_cache_release(r);
+    return rc;
 }
 
 }  // namespace
@@ -251,6 +183,7 @@ cfd_status_t cfd_b200_set_poisson_config(const cfd_b200_poisson_config_t* cfg) {
     return CFD_SUCCESS;
 }
 cfd_b200_poisson_config_t cfd_b200_get_poisson_config(void) {
+    std::lock_guard<std::mutex> lk(g_mu);
     init_pcfg_locked();
     return g_pcfg;
 }

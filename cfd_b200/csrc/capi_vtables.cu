@@ -4,7 +4,7 @@
 // and the legacy persistent-context API gpu_solver_* (gpu_device.h:145-194).
 // Objects are calloc'ed because the reference frees them with cfd_free == free
 // (solver_registry.c:414-423, linear_solver.c:288-298, core/memory.c).
-#include "session.h"
+#include "runner.h"
 
 #include <stdlib.h>
 #include <string.h>
@@ -91,29 +91,25 @@ poisson_solver_t* make_ps(const char* name, const char* desc, poisson_solver_met
 
 // ---------------- ns_solver_t vtable (persistent context) ----------------
 struct NsCtx {
-    cfd_b200_session* s;
-    int kind;  // 0 projection, 1 explicit Euler, 2 rk2, 4 rk4
+    Runner* r;     // one session, or a gang of slabs when cfd_b200_set_device_count / CFD_B200_NGPU > 1
+    int kind;      // StepKind: 0 projection, 1 explicit Euler, 2 rk2, 4 rk4
+    int sync;      // cfd_b200_host_sync_t bits (cfd_b200_solver_set_host_sync)
+    unsigned magic;
 };
+constexpr unsigned NS_MAGIC = 0xCFDB2001u;
 
 cfd_status_t ns_ensure(ns_solver_t* slv, const flow_field* f, const grid* g) {
     NsCtx* c = (NsCtx*)slv->context;
-    const double dx = g->dx[0], dy = g->dy[0], dz = (f->nz > 1 && g->dz) ? g->dz[0] : 0.0;
-    if (c->s && (c->s->desc.nx != f->nx || c->s->desc.ny != f->ny || c->s->desc.nz != f->nz ||
-                 c->s->desc.dx != dx || c->s->desc.dy != dy || c->s->desc.dz != dz)) {
-        cfd_b200_session_destroy(c->s);
-        c->s = nullptr;
+    int want = configured_device_count();
+    if (c->kind == SK_PROJECTION && cfd_b200_get_poisson_config().method == POISSON_METHOD_MULTIGRID) want = 1;
+    if (c->r && !runner_matches(c->r, f, g, want)) {
+        runner_destroy(c->r);
+        c->r = nullptr;
     }
-    if (!c->s) {
-        cfd_b200_session_desc_t d;
-        memset(&d, 0, sizeof(d));
-        d.nx = f->nx; d.ny = f->ny; d.nz = f->nz;
-        d.dx = dx; d.dy = dy; d.dz = dz;
-        d.xmin = g->xmin; d.ymin = g->ymin; d.zmin = g->zmin;
-        d.nranks = 1; d.device = -1;
-        c->s = cfd_b200_session_create(&d);
-        if (!c->s) return CFD_ERROR_NOMEM;
+    if (!c->r) {
+        c->r = runner_create(f, g, want);
+        if (!c->r) return CFD_ERROR_NOMEM;
     }
-    session_set_coords(c->s, g->x, g->y);
     return CFD_SUCCESS;
 }
 
@@ -124,31 +120,17 @@ cfd_status_t ns_run(ns_solver_t* slv, flow_field* f, const grid* g, const ns_sol
     if (rc != CFD_SUCCESS) return rc;
     if ((rc = ns_ensure(slv, f, g)) != CFD_SUCCESS) return rc;
     NsCtx* c = (NsCtx*)slv->context;
-    cfd_b200_session* s = c->s;
     const bool thermo = (prm->alpha > 0.0 || prm->beta != 0.0);
-    if (c->kind == 0) {
-        rc = session_upload(s, f, FM_U | FM_V | FM_W | FM_P | (thermo ? FM_T : 0));
-        if (rc != CFD_SUCCESS) return rc;
-        cfd_b200_poisson_config_t pc = cfd_b200_get_poisson_config();
-        rc = run_projection(s, prm, &pc, nsteps, stats);
-        if (rc == CFD_SUCCESS || rc == CFD_ERROR_MAX_ITER || rc == CFD_ERROR_DIVERGED) {
-            cfd_status_t r2 = session_download(s, f, FM_U | FM_V | FM_W | FM_P | (prm->alpha > 0.0 ? FM_T : 0));
-            if (r2 != CFD_SUCCESS) return r2;
-        }
+    rc = runner_run(c->r, (StepKind)c->kind, f, g, prm, nsteps, stats, c->sync);
+    if (c->kind == SK_PROJECTION) {
         if (stats && rc == CFD_SUCCESS && !thermo) {  // T never went to the device: max over the host copy
             double mt = f->T[0];
             const size_t N = f->nx * f->ny * f->nz;
             for (size_t n = 1; n < N; n++) if (f->T[n] > mt) mt = f->T[n];
             stats->max_temperature = mt;
         }
-    } else {
-        rc = session_upload(s, f, FM_ALL);
-        if (rc != CFD_SUCCESS) return rc;
-        rc = run_rk(s, c->kind, prm, nsteps, stats);
-        if (rc == CFD_SUCCESS || rc == CFD_ERROR_DIVERGED) {
-            cfd_status_t r2 = session_download(s, f, FM_U | FM_V | FM_W | FM_P | FM_T | FM_RHO);
-            if (r2 != CFD_SUCCESS) return r2;
-        }
+    } else if ((rc == CFD_SUCCESS || rc == CFD_ERROR_DIVERGED) && nsteps > 0 && !c->r->host_stale) {
+        wrap_host_rho(f);
     }
     if (stats) stats->status = rc;
     return rc;
@@ -166,7 +148,8 @@ cfd_status_t ns_init(ns_solver_t* slv, const grid* g, const ns_solver_params_t* 
 void ns_destroy(ns_solver_t* slv) {
     if (!slv || !slv->context) return;
     NsCtx* c = (NsCtx*)slv->context;
-    if (c->s) cfd_b200_session_destroy(c->s);
+    if (c->r) runner_destroy(c->r);
+    c->magic = 0;
     free(c);
     slv->context = nullptr;
 }
@@ -194,6 +177,8 @@ ns_solver_t* make_ns(const char* name, const char* desc, int kind) {
     NsCtx* c = (NsCtx*)calloc(1, sizeof(NsCtx));
     if (!s || !c) { free(s); free(c); return nullptr; }
     c->kind = kind;
+    c->magic = NS_MAGIC;
+    c->sync = SYNC_FULL;
     s->name = name;
     s->description = desc;
     s->version = "cfd_b200-0.1.0";
@@ -240,6 +225,38 @@ ns_solver_t* cfd_b200_create_rk2_gpu_solver(void) {
 }
 ns_solver_t* cfd_b200_create_rk4_gpu_solver(void) {
     return make_ns("rk4_gpu", "B200-native classical RK4 explicit stepper", 4);
+}
+
+// ---- host-sync policy of the ns_solver_t objects made above ----
+static NsCtx* ns_ctx_of(ns_solver_t* slv) {
+    if (!slv || !slv->context || slv->step != ns_step) return nullptr;
+    NsCtx* c = (NsCtx*)slv->context;
+    return c->magic == NS_MAGIC ? c : nullptr;
+}
+cfd_status_t cfd_b200_solver_set_host_sync(ns_solver_t* slv, int flags) {
+    NsCtx* c = ns_ctx_of(slv);
+    if (!c || (flags & ~(SYNC_UPLOAD_BOUNDARY | SYNC_DOWNLOAD_LAZY))) {
+        set_error(CFD_ERROR_INVALID, "cfd_b200_solver_set_host_sync: not a cfd_b200 solver object, or unknown flag bits");
+        return CFD_ERROR_INVALID;
+    }
+    if (c->r && c->r->host_stale && !(flags & SYNC_DOWNLOAD_LAZY)) {
+        set_error(CFD_ERROR_INVALID, "the device is ahead of the host copy: call cfd_b200_solver_sync_host() before "
+                                     "leaving CFD_B200_SYNC_DOWNLOAD_LAZY");
+        return CFD_ERROR_INVALID;
+    }
+    c->sync = flags;
+    return CFD_SUCCESS;
+}
+cfd_status_t cfd_b200_solver_sync_host(ns_solver_t* slv, flow_field* f) {
+    NsCtx* c = ns_ctx_of(slv);
+    if (!c || !f) return CFD_ERROR_INVALID;
+    if (!c->r || !c->r->host_stale) return CFD_SUCCESS;  // nothing newer on the device
+    if (f->nx != c->r->nx || f->ny != c->r->ny || f->nz != c->r->nz) return CFD_ERROR_INVALID;
+    int mask = (c->r->resident_mask & (FM_U | FM_V | FM_W | FM_P | FM_T));
+    if (c->kind != SK_PROJECTION) mask = FM_U | FM_V | FM_W | FM_P | FM_T;
+    cfd_status_t rc = runner_download(c->r, f, mask);
+    if (rc == CFD_SUCCESS && c->kind != SK_PROJECTION) wrap_host_rho(f);
+    return rc;
 }
 
 // ---- legacy persistent context (gpu_device.h:145-194) ----
@@ -305,12 +322,12 @@ cfd_status_t gpu_solver_step(gpu_solver_context_t* c, const grid* g, const ns_so
         set_spacing(s->g, dx, dy, dz);
     }
     session_set_coords(s, g->x, g->y);
-    const unsigned long long l0 = g_launches;
+    const unsigned long long l0 = g_launches.load();
     const double t0 = now_ms();
     cfd_b200_poisson_config_t pc = cfd_b200_get_poisson_config();
     cfd_status_t rc = run_projection(s, prm, &pc, 1, nullptr);
     c->stats.kernel_time_ms += now_ms() - t0;
-    c->stats.kernels_launched += (int)(g_launches - l0);
+    c->stats.kernels_launched += (int)(g_launches.load() - l0);
     c->stats.poisson_iterations = s->last_ps.iterations;
     c->stats.poisson_residual = s->last_ps.final_residual;
     c->stats.memory_allocated = s->bytes_allocated;

@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <math.h>
+#include <atomic>
 
 #include "../../include/cfd_b200.h"
 
@@ -80,7 +81,7 @@ struct KArgs {
     } while (0)
 
 void set_error(cfd_status_t st, const char* fmt, ...);
-extern unsigned long long g_launches;  // kernels launched by this library
+extern std::atomic<unsigned long long> g_launches;  // kernels launched by this library (any thread)
 
 // ---------------------------------------------------------------------------------------
 // Device helpers

@@ -63,6 +63,10 @@ double optimal_omega(const cfd_b200_session_desc_t& d, size_t gnx, size_t gny, s
 cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double** px,
                            double** pxt, const double* rhs, poisson_solver_stats_t* out) {
     if (cfg->method == POISSON_METHOD_MULTIGRID) return mg_solve(s, cfg, *px, rhs, out);
+    {
+        const cfd_status_t cr = comm_ready(s);
+        if (cr != CFD_SUCCESS) return cr;
+    }
     const poisson_solver_params_t& pp = cfg->params;
     const LaunchCtx L = s->L();
     const int R = s->desc.nranks;
@@ -78,11 +82,8 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
     {
         // global extents along the decomposed axis (every rank owns n-2 interior layers)
         size_t gnx = s->desc.nx, gny = s->desc.ny, gnz = s->desc.nz;
-        // NOTE: uniform slabs assumed for the omega formula; set via session extension if not
-        if (R > 1) {
-            if (s->g.dim3) gnz = (s->desc.nz - 2) * (size_t)R + 2;
-            else gny = (s->desc.ny - 2) * (size_t)R + 2;
-        }
+        if (s->g.dim3) gnz = global_dec_extent(s);  // uneven slabs: cfd_b200_session_set_slab
+        else gny = global_dec_extent(s);
         a.omega = pp.omega > 0.0 ? pp.omega : optimal_omega(s->desc, gnx, gny, gnz);
     }
     launch_zero_ctl(L);
@@ -287,6 +288,7 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         double* f[1] = {*px};
         halo_exchange(s, f, 1, false);
     }
+    if (comm_check(s) != CFD_SUCCESS) return CFD_ERROR;  // an exchange or reduction was lost: no per-slab "success"
     return st.status == POISSON_CONVERGED ? CFD_SUCCESS
                                           : (st.status == POISSON_ERROR ? CFD_ERROR : CFD_ERROR_MAX_ITER);
 }

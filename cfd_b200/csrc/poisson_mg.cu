@@ -606,7 +606,7 @@ cfd_status_t mg_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg,
     if (want_graph && (!st->exec || st->gx != x || st->gb != rhs)) {
         if (st->exec) cudaGraphExecDestroy(st->exec);
         st->exec = nullptr;
-        const unsigned long long l0 = g_launches;
+        const unsigned long long l0 = g_launches.load();
         unsigned long long k0[KK_COUNT];
         if (t_prof) memcpy(k0, t_prof->launches, sizeof(k0));
         cudaGraph_t graph = nullptr;
@@ -621,8 +621,8 @@ cfd_status_t mg_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg,
         if (ok) ok = cudaGraphInstantiate(&st->exec, graph, 0) == cudaSuccess;
         if (graph) cudaGraphDestroy(graph);
         // nothing ran during the capture: take its launches back and remember them per replay
-        st->graph_launches = g_launches - l0;
-        g_launches = l0;
+        st->graph_launches = g_launches.load() - l0;
+        g_launches -= st->graph_launches;
         if (t_prof)
             for (int k = 0; k < KK_COUNT; k++) {
                 st->graph_kind[k] = t_prof->launches[k] - k0[k];

@@ -11,7 +11,7 @@
 
 namespace cfdb {
 
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 thread_local Profiler* t_prof = nullptr;
 static thread_local char t_err[512] = "";
 
@@ -139,7 +139,7 @@ extern "C" {
 
 const char* cfd_b200_last_error(void) { return cfdb::last_error(); }
 const char* cfd_b200_version(void) { return "cfd_b200 0.1.0 (sm_100a, FP64)"; }
-unsigned long long cfd_b200_kernel_launch_count(void) { return g_launches; }
+unsigned long long cfd_b200_kernel_launch_count(void) { return g_launches.load(); }
 
 void* cfd_b200_host_alloc(size_t bytes) {
     void* p = nullptr;

@@ -22,6 +22,7 @@ struct Nccl {
     int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
+    int (*CommInitAll)(void**, int, const int*) = nullptr;
 };
 
 struct MgState;  // multigrid hierarchy of a session (poisson_mg.cu)
@@ -62,6 +63,12 @@ struct cfd_b200_session {
     cfdb::Nccl nccl;
     poisson_solver_stats_t last_ps = {};
     size_t bytes_allocated = 0;
+    // slab bookkeeping: global extent of the decomposed axis (boundary layers included; 0 = uniform slabs,
+    // derived from nranks) -- cfd_b200_session_set_slab
+    size_t gdec = 0;
+    // first failure of a halo exchange / all-reduce since the last check (comm_check): a decomposed solve
+    // that lost an exchange must not report success on a per-slab answer
+    cfd_status_t comm_err = CFD_SUCCESS;
     int kernels_at_create = 0;
 
     cfdb::LaunchCtx L() const {
@@ -90,6 +97,12 @@ cfd_status_t xfer_fields(cfd_b200_session* s, double* const* dev, double* const*
 cfd_status_t session_set_coords(cfd_b200_session* s, const double* x, const double* y);
 cfd_status_t halo_exchange(cfd_b200_session* s, double* const* fields, int nf, bool periodic_ring);
 cfd_status_t allreduce(cfd_b200_session* s, double* dev, int n, bool is_max);
+cfd_status_t allreduce_int_max(cfd_b200_session* s, int* dev, int n);
+// nranks > 1 needs a communicator; returns (and clears) the first exchange failure since the last call
+cfd_status_t comm_ready(cfd_b200_session* s);
+cfd_status_t comm_check(cfd_b200_session* s);
+size_t global_dec_extent(const cfd_b200_session* s);  // global layers along the decomposed axis
+cfd_status_t load_nccl(Nccl& n, const char* path);
 cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double** x,
                            double** xtmp, const double* rhs, poisson_solver_stats_t* st);
 // geometric multigrid (poisson_mg.cu): x in place, boundary cells filled at the end; one GPU only

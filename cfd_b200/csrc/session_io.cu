@@ -5,6 +5,7 @@
 
 #include <dlfcn.h>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace cfdb {
@@ -61,9 +62,12 @@ cfd_status_t session_set_coords(cfd_b200_session* s, const double* x, const doub
 }
 
 // ---- NCCL plumbing -------------------------------------------------------------------
-static cfd_status_t load_nccl(Nccl& n, const char* path) {
+cfd_status_t load_nccl(Nccl& n, const char* path) {
     if (n.lib) return CFD_SUCCESS;
-    n.lib = dlopen(path && path[0] ? path : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    // one NCCL per process: when the host program (e.g. torch) has already loaded libnccl.so.2, take that
+    // copy whatever `path` says; only otherwise load the named / default library
+    if (!getenv("CFD_B200_NCCL_FORCE_PATH")) n.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+    if (!n.lib) n.lib = dlopen(path && path[0] ? path : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
     if (!n.lib) {
         set_error(CFD_ERROR_UNSUPPORTED, "dlopen(%s) failed: %s", path ? path : "libnccl.so.2", dlerror());
         return CFD_ERROR_UNSUPPORTED;
@@ -82,6 +86,7 @@ static cfd_status_t load_nccl(Nccl& n, const char* path) {
     SYM(Recv, "ncclRecv")
     SYM(GroupStart, "ncclGroupStart")
     SYM(GroupEnd, "ncclGroupEnd")
+    SYM(CommInitAll, "ncclCommInitAll")
 #undef SYM
     return CFD_SUCCESS;
 }
@@ -94,6 +99,7 @@ cfd_status_t halo_exchange(cfd_b200_session* s, double* const* fields, int nf, b
     if (R <= 1) return CFD_SUCCESS;
     if (!s->nccl.comm) {
         set_error(CFD_ERROR, "multi-rank session without a communicator (call cfd_b200_session_init_comm)");
+        if (s->comm_err == CFD_SUCCESS) s->comm_err = CFD_ERROR;
         return CFD_ERROR;
     }
     const Geom& g = s->g;
@@ -119,19 +125,49 @@ cfd_status_t halo_exchange(cfd_b200_session* s, double* const* fields, int nf, b
     }
     if (n.GroupEnd() != 0) {
         set_error(CFD_ERROR, "NCCL halo exchange failed");
+        if (s->comm_err == CFD_SUCCESS) s->comm_err = CFD_ERROR;
         return CFD_ERROR;
     }
     return CFD_SUCCESS;
 }
 
-cfd_status_t allreduce(cfd_b200_session* s, double* dev, int cnt, bool is_max) {
+static cfd_status_t allreduce_any(cfd_b200_session* s, void* dev, int cnt, int dtype, int op) {
     if (s->desc.nranks <= 1) return CFD_SUCCESS;
-    if (!s->nccl.comm) return CFD_ERROR;
-    if (s->nccl.AllReduce(dev, dev, (size_t)cnt, 8, is_max ? 2 : 0, s->nccl.comm, s->st) != 0) {
+    if (!s->nccl.comm) {
+        set_error(CFD_ERROR, "multi-rank session without a communicator (call cfd_b200_session_init_comm)");
+        if (s->comm_err == CFD_SUCCESS) s->comm_err = CFD_ERROR;
+        return CFD_ERROR;
+    }
+    if (s->nccl.AllReduce(dev, dev, (size_t)cnt, dtype, op, s->nccl.comm, s->st) != 0) {
         set_error(CFD_ERROR, "NCCL all-reduce failed");
+        if (s->comm_err == CFD_SUCCESS) s->comm_err = CFD_ERROR;
         return CFD_ERROR;
     }
     return CFD_SUCCESS;
+}
+// ncclDouble = 8, ncclInt32 = 2; ncclSum = 0, ncclMax = 2 (nccl.h 2.27 / 2.28)
+cfd_status_t allreduce(cfd_b200_session* s, double* dev, int cnt, bool is_max) {
+    return allreduce_any(s, dev, cnt, 8, is_max ? 2 : 0);
+}
+cfd_status_t allreduce_int_max(cfd_b200_session* s, int* dev, int cnt) { return allreduce_any(s, dev, cnt, 2, 2); }
+
+cfd_status_t comm_ready(cfd_b200_session* s) {
+    if (s->desc.nranks > 1 && !s->nccl.comm) {
+        set_error(CFD_ERROR, "session is rank %d of %d but has no communicator (call cfd_b200_session_init_comm)",
+                  s->desc.rank, s->desc.nranks);
+        return CFD_ERROR;
+    }
+    return CFD_SUCCESS;
+}
+cfd_status_t comm_check(cfd_b200_session* s) {
+    const cfd_status_t rc = s->comm_err;
+    s->comm_err = CFD_SUCCESS;
+    return rc;
+}
+size_t global_dec_extent(const cfd_b200_session* s) {
+    if (s->gdec) return s->gdec;
+    const size_t loc = s->g.dim3 ? s->desc.nz : s->desc.ny;
+    return s->desc.nranks > 1 ? (loc - 2) * (size_t)s->desc.nranks + 2 : loc;
 }
 
 }  // namespace cfdb
@@ -161,6 +197,23 @@ cfd_status_t cfd_b200_session_init_comm(cfd_b200_session_t* s, const char* nccl_
         set_error(CFD_ERROR, "ncclCommInitRank(rank %d of %d) failed", s->desc.rank, s->desc.nranks);
         return CFD_ERROR;
     }
+    return CFD_SUCCESS;
+}
+
+cfd_status_t cfd_b200_session_set_slab(cfd_b200_session_t* s, size_t global_layers, size_t global_lo) {
+    if (!s || global_layers < 3) return CFD_ERROR_INVALID;
+    const size_t loc = s->g.dim3 ? s->desc.nz : s->desc.ny;
+    if (global_lo + loc > global_layers) {
+        set_error(CFD_ERROR_INVALID, "slab [%zu, %zu) does not fit in %zu global layers", global_lo, global_lo + loc,
+                  global_layers);
+        return CFD_ERROR_INVALID;
+    }
+    s->gdec = global_layers;
+    if (s->g.dim3) s->g.gk0 = (long long)global_lo;
+    else s->g.gj0 = (long long)global_lo;
+    // physical faces follow from the position, not from the rank number
+    s->g.glo[s->dec_axis] = (global_lo == 0);
+    s->g.ghi[s->dec_axis] = (global_lo + loc == global_layers);
     return CFD_SUCCESS;
 }
 

@@ -59,7 +59,12 @@ static cfd_status_t check_thermal(const ns_solver_params_t* prm, bool dim3) {
     return CFD_SUCCESS;
 }
 
+// One host synchronisation per time step.  Decomposed runs first all-reduce (max) the flag: a NaN in ONE slab
+// must take every rank out of the step loop at the same step, or the others block in the next exchange.
 static cfd_status_t read_flags(cfd_b200_session* s, int* nonfinite) {
+    if (s->desc.nranks > 1) {
+        if (allreduce_int_max(s, &s->ctl->nonfinite, 1) != CFD_SUCCESS) return CFD_ERROR;
+    }
     CFDB_CUDA_OK(cudaMemcpyAsync(&s->h_ctl[0], s->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s->st));
     CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
     *nonfinite = s->h_ctl[0].nonfinite;
@@ -89,6 +94,7 @@ cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
     if (rc != CFD_SUCCESS) return rc;
     CFDB_CUDA_OK(cudaSetDevice(s->dev));
     t_prof = &s->prof;
+    if ((rc = comm_ready(s)) != CFD_SUCCESS) return rc;
     double** need[] = {&s->us, &s->vs, &s->ws, &s->pn, &s->rhs};
     for (auto q : need)
         if ((rc = dalloc(s, q)) != CFD_SUCCESS) return rc;
@@ -147,6 +153,7 @@ cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
             return CFD_ERROR_DIVERGED;
         }
     }
+    if (comm_check(s) != CFD_SUCCESS) return CFD_ERROR;
     cudaError_t ce = cudaGetLastError();
     if (ce != cudaSuccess) {
         set_error(CFD_ERROR, "CUDA failure in projection step: %s", cudaGetErrorString(ce));
@@ -171,6 +178,7 @@ static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm
     if (rc != CFD_SUCCESS) return rc;
     CFDB_CUDA_OK(cudaSetDevice(s->dev));
     t_prof = &s->prof;
+    if ((rc = comm_ready(s)) != CFD_SUCCESS) return rc;
     for (int q = 0; q < 4; q++)
         if ((rc = dalloc(s, &s->rk[q])) != CFD_SUCCESS) return rc;
     if (!s->rho) {  // session extension: no density uploaded => rho = 1 everywhere
@@ -228,6 +236,7 @@ static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm
             return CFD_ERROR_DIVERGED;
         }
     }
+    if (comm_check(s) != CFD_SUCCESS) return CFD_ERROR;
     cudaError_t ce = cudaGetLastError();
     if (ce != cudaSuccess) {
         set_error(CFD_ERROR, "CUDA failure in explicit Euler step: %s", cudaGetErrorString(ce));
@@ -253,6 +262,7 @@ cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* pr
     if (rc != CFD_SUCCESS) return rc;
     CFDB_CUDA_OK(cudaSetDevice(s->dev));
     t_prof = &s->prof;
+    if ((rc = comm_ready(s)) != CFD_SUCCESS) return rc;
     const int nbuf = (order == 4) ? 12 : 8;  // B[4], (C[4]), ACC[4]
     for (int q = 0; q < nbuf; q++)
         if ((rc = dalloc(s, &s->rk[q])) != CFD_SUCCESS) return rc;
@@ -333,6 +343,7 @@ cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* pr
             return CFD_ERROR_DIVERGED;
         }
     }
+    if (comm_check(s) != CFD_SUCCESS) return CFD_ERROR;
     cudaError_t ce = cudaGetLastError();
     if (ce != cudaSuccess) {
         set_error(CFD_ERROR, "CUDA failure in RK step: %s", cudaGetErrorString(ce));

@@ -97,6 +97,12 @@ def load():
     proto("cfd_b200_session_stream", vp, [vp])
     proto("cfd_b200_session_sync", i32, [vp])
     proto("cfd_b200_abi_table", i32, [C.POINTER(C.c_size_t), i32])
+    proto("cfd_b200_set_device_count", i32, [i32])
+    proto("cfd_b200_get_device_count", i32, [])
+    proto("cfd_b200_session_set_slab", i32, [vp, C.c_size_t, C.c_size_t])
+    proto("cfd_b200_release_cached_sessions", None, [])
+    proto("cfd_b200_solver_set_host_sync", i32, [C.POINTER(abi.NSSolver), i32])
+    proto("cfd_b200_solver_sync_host", i32, [C.POINTER(abi.NSSolver), FF])
     _lib = L
     return L
 
@@ -123,6 +129,8 @@ DECLARED_SYMBOLS = [
     "cfd_b200_session_poisson", "cfd_b200_session_upload_poisson", "cfd_b200_session_download_poisson",
     "cfd_b200_session_last_poisson_stats", "cfd_b200_session_profile", "cfd_b200_session_kernel_stats",
     "cfd_b200_session_reset_kernel_stats", "cfd_b200_session_stream", "cfd_b200_session_sync",
+    "cfd_b200_set_device_count", "cfd_b200_get_device_count", "cfd_b200_session_set_slab",
+    "cfd_b200_release_cached_sessions", "cfd_b200_solver_set_host_sync", "cfd_b200_solver_sync_host",
 ]
 
 

@@ -547,6 +547,40 @@ CFD_B200_API cfd_status_t cfd_b200_session_download_poisson(cfd_b200_session_t* 
 /* Poisson statistics of the most recent projection step / Poisson solve. */
 CFD_B200_API poisson_solver_stats_t cfd_b200_session_last_poisson_stats(const cfd_b200_session_t* s);
 
+/* ---- Multi-GPU behind the drop-in boundary (SURVEY 8e "process model") ----
+ * The reference's entry points receive one host flow_field (gpu_device.h:209-249, called from
+ * solver_registry.c:1121-1245 behind run_simulation_step).  With a device count G > 1 -- this setter, or the
+ * environment variable CFD_B200_NGPU when the setter was never called (0 = back to the environment) -- every
+ * solve_*_method_gpu call and every ns_solver_t made by the cfd_b200_create_*_gpu_solver factories cuts the grid
+ * into G slabs along z (along y when nz == 1; uneven when the interior layers do not divide), one GPU and one
+ * host thread per slab inside this process, NCCL communicators from ncclCommInitAll.  Clamped to the visible
+ * devices and to >= 4 owned layers per slab; the multigrid method stays on one GPU. */
+CFD_B200_API cfd_status_t cfd_b200_set_device_count(int ngpu);
+CFD_B200_API int cfd_b200_get_device_count(void);
+/* Position of a session's slab in the global grid: global layer count of the decomposed axis (boundary
+ * layers included) and the global index of local layer 0.  Needed for uneven slabs (red/black colouring,
+ * optimal omega); uniform slabs derive both from rank / nranks. */
+CFD_B200_API cfd_status_t cfd_b200_session_set_slab(cfd_b200_session_t* s, size_t global_layers, size_t global_lo);
+/* Device buffers of the stateless solve_*_method_gpu symbols are cached between calls (LRU of
+ * CFD_B200_SESSION_CACHE = 2 shapes); this frees the idle ones. */
+CFD_B200_API void cfd_b200_release_cached_sessions(void);
+
+/* ---- Host-sync policy of an ns_solver_t made by the cfd_b200_create_*_gpu_solver factories ----
+ * FULL (default): every step()/solve() uploads the caller's fields and downloads the result -- a drop-in with
+ * no assumptions.  UPLOAD_BOUNDARY: the caller promises that, since the previous call on this solver returned,
+ * it has edited only boundary cells (the outermost layer) of the SAME field -- what the reference's drivers do
+ * (tests/validation/lid_driven_cavity_common.h:306-338); the first call uploads everything, later calls only
+ * the six faces.  DOWNLOAD_LAZY: the result stays on the device (boundary velocities set by the caller are
+ * preserved by the steppers, boundary_copy_utils.h:93-148) and nothing is uploaded while the host copy is the
+ * stale one; cfd_b200_solver_sync_host() brings the caller's arrays up to date. */
+typedef enum {
+    CFD_B200_SYNC_FULL = 0,
+    CFD_B200_SYNC_UPLOAD_BOUNDARY = 1,
+    CFD_B200_SYNC_DOWNLOAD_LAZY = 2
+} cfd_b200_host_sync_t;
+CFD_B200_API cfd_status_t cfd_b200_solver_set_host_sync(ns_solver_t* solver, int flags);
+CFD_B200_API cfd_status_t cfd_b200_solver_sync_host(ns_solver_t* solver, flow_field* field);
+
 /* ---- Measurement hooks (bench.py): per-kernel CUDA-event timing on the session stream ---- */
 #define CFD_B200_MAX_KERNEL_KINDS 48
 typedef struct {
