@@ -225,6 +225,18 @@ class Session:
     def last_poisson_stats(self):
         return self.L.cfd_b200_session_last_poisson_stats(self.h)
 
+    def peer_export(self):
+        out = C.create_string_buffer(64)
+        check(self.L.cfd_b200_session_peer_export(self.h, out), "session_peer_export")
+        return out.raw
+
+    def peer_attach(self, handles):
+        """handles: the 64-byte exports of ALL ranks, concatenated in rank order."""
+        return self.L.cfd_b200_session_peer_attach(self.h, handles)
+
+    def transport(self):
+        return {0: "none", 1: "nccl", 2: "peer"}[self.L.cfd_b200_session_transport(self.h)]
+
     def init_comm(self, nccl_lib, unique_id):
         check(self.L.cfd_b200_session_init_comm(self.h, nccl_lib.encode() if nccl_lib else None,
                                                 unique_id), "session_init_comm")

@@ -54,7 +54,8 @@ struct Ctl {
     int result_buf;       // which ping-pong buffer holds x (Jacobi)
     int skip_final_bc;    // reference returned before its final Neumann BC (stagnation paths)
     int nonfinite;        // NaN/Inf flag of the time step (solver_projection.c:281-289)
-    int pad[2];
+    int comm_timeout;     // a peer-transport wait gave up (peer.cu): the step's answer is not to be trusted
+    int pad[1];
     double stat[4];       // max |vel|, max |p|, max T, spare (solver_registry.c:31-62)
 };
 

@@ -60,6 +60,13 @@ void wrap_host_rho(flow_field* f) {
         for (size_t n = 0; n < plane; n++) { r[n] = r[(nz - 2) * plane + n]; r[(nz - 1) * plane + n] = r[plane + n]; }
 }
 
+// CFD_B200_VIRTUAL_RANKS=1: all slabs on the CURRENT device, one stream each (peer transport only).  The
+// decomposition, halo and reduction logic is then exercised on a one-GPU box.
+static bool virtual_ranks() {
+    const char* e = getenv("CFD_B200_VIRTUAL_RANKS");
+    return e && e[0] && e[0] != '0';
+}
+
 int configured_device_count() {
     int want = g_ngpu.load();
     if (want <= 0) {
@@ -67,10 +74,43 @@ int configured_device_count() {
         want = e ? atoi(e) : 1;
     }
     if (want < 1) want = 1;
+    if (want > PEER_MAX_RANKS) want = PEER_MAX_RANKS;
+    if (virtual_ranks()) return want;
     int have = 0;
     if (cudaGetDeviceCount(&have) != cudaSuccess) { cudaGetLastError(); have = 0; }
     if (want > have) want = have > 0 ? have : 1;
     return want;
+}
+
+// Slabs of one process talk through peer memory: a box per rank, every device mapped into every other.
+static bool connect_peers(Runner* r, const std::vector<int>& devs) {
+    const int G = r->G;
+    for (int q = 0; q < G; q++)
+        if (peer_alloc_box(r->s[q]) != CFD_SUCCESS) return false;
+    for (int a = 0; a < G; a++) {
+        cudaSetDevice(devs[a]);
+        for (int b = 0; b < G; b++) {
+            if (devs[a] == devs[b]) continue;
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, devs[a], devs[b]) != cudaSuccess || !can) {
+                cudaGetLastError();
+                set_error(CFD_ERROR_UNSUPPORTED, "device %d cannot map device %d's memory", devs[a], devs[b]);
+                return false;
+            }
+            const cudaError_t e = cudaDeviceEnablePeerAccess(devs[b], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                set_error(CFD_ERROR_UNSUPPORTED, "cudaDeviceEnablePeerAccess(%d -> %d): %s", devs[a], devs[b], cudaGetErrorString(e));
+                cudaGetLastError();
+                return false;
+            }
+            cudaGetLastError();
+        }
+    }
+    for (int a = 0; a < G; a++) {
+        for (int b = 0; b < G; b++) r->s[a]->peer.peer_box[b] = r->s[b]->peer.box;
+        r->s[a]->peer.on = true;
+    }
+    return true;
 }
 
 static int effective_gpus(const flow_field* f, int want) {
@@ -142,13 +182,20 @@ Runner* runner_create(const flow_field* f, const grid* g, int want) {
         d.zmin = d3 ? g->zmin + (double)r->lo[q] * r->dz : g->zmin;
         d.rank = q;
         d.nranks = G;
-        d.device = G > 1 ? (r->dev0 + q) % ndev : -1;
-        devs[q] = G > 1 ? d.device : r->dev0;
+        d.device = (G > 1 && !virtual_ranks()) ? (r->dev0 + q) % ndev : -1;
+        devs[q] = d.device >= 0 ? d.device : r->dev0;
         r->s[q] = cfd_b200_session_create(&d);
         ok = r->s[q] != nullptr;
         if (ok && G > 1) ok = cfd_b200_session_set_slab(r->s[q], glayers, r->lo[q]) == CFD_SUCCESS;
     }
-    if (ok && G > 1) {
+    const char* tr = getenv("CFD_B200_GANG_TRANSPORT");
+    bool want_nccl = tr && !strcmp(tr, "nccl") && !virtual_ranks();
+    if (ok && G > 1 && !want_nccl && !connect_peers(r, devs)) {
+        if (virtual_ranks()) ok = false;
+        else want_nccl = true;  // no peer mapping between these devices: the library transport
+    }
+    if (ok && G > 1 && want_nccl) {
+        for (int q = 0; q < G; q++) r->s[q]->peer.on = false;
         Nccl n;
         ok = load_nccl(n, getenv("CFD_B200_NCCL_LIB")) == CFD_SUCCESS;
         std::vector<void*> comms(G, nullptr);

@@ -38,7 +38,7 @@ enum KernelKind {
     KK_CG_UPDATE, KK_BICG_DIR, KK_BICG_S, KK_BICG_UPDATE, KK_PREDICTOR, KK_DIVERGENCE,
     KK_CORRECTOR, KK_THERMAL_BC, KK_PERIODIC_BC, KK_RK_STAGE, KK_FIELD_STATS, KK_SYNTH_INIT,
     KK_COPY, KK_EULER, KK_BOUNDARY, KK_FILL, KK_CTL_RESET, KK_RBSOR_FUSED, KK_JACOBI_CLUSTER, KK_CG_CLUSTER,
-    KK_MG_SMOOTH, KK_MG_RESIDUAL, KK_MG_RESTRICT, KK_MG_PROLONG, KK_MG_COARSE, KK_MG_SWEEP2, KK_COUNT
+    KK_MG_SMOOTH, KK_MG_RESIDUAL, KK_MG_RESTRICT, KK_MG_PROLONG, KK_MG_COARSE, KK_MG_SWEEP2, KK_HALO, KK_ALLREDUCE, KK_COUNT
 };
 extern const char* const kKernelNames[KK_COUNT];
 extern const double kKernelBytesPerCell[KK_COUNT];

@@ -21,11 +21,13 @@ const char* const kKernelNames[KK_COUNT] = {
     "predictor", "divergence_rhs", "corrector", "thermal_bc", "periodic_bc", "rk_stage",
     "field_stats", "synth_init", "copy", "euler", "boundary_cells", "fill", "ctl_reset", "rbsor_fused_iteration",
     "jacobi_cluster_solve", "cg_cluster_solve",
-    "mg_smooth_colour", "mg_residual", "mg_restrict", "mg_prolong_add", "mg_coarsest_solve", "mg_sweep_two_colours"};
+    "mg_smooth_colour", "mg_residual", "mg_restrict", "mg_prolong_add", "mg_coarsest_solve", "mg_sweep_two_colours",
+    "halo_push_pull_peer", "allreduce_peer"};
 // Algorithmic bytes per interior cell per launch.
 const double kKernelBytesPerCell[KK_COUNT] = {0, 24, 16, 16, 0, 32, 32, 48, 48, 32, 56,
                                               48, 32, 56, 0, 0, 136, 40, 0, 16, 72, 0, 8, 0, 24, 0, 0,
-                                              0, 0, 0, 0, 0, 0};  // multigrid kernels run on every level: no per-cell figure
+                                              0, 0, 0, 0, 0, 0,  // multigrid kernels run on every level: no per-cell figure
+                                              0, 0};
 
 // The reference keeps a thread-local error string (cfd/core/cfd_status.h:31-43).  When its core
 // library is loaded in the process we forward to it; otherwise we keep our own.
@@ -270,6 +272,7 @@ void cfd_b200_session_destroy(cfd_b200_session_t* s) {
     for (auto& e : s->ev) if (e) cudaEventDestroy(e);
     s->prof.release();
     if (s->nccl.comm && s->nccl.CommDestroy) s->nccl.CommDestroy(s->nccl.comm);
+    peer_release(s);
     if (s->st) cudaStreamDestroy(s->st);
     if (t_prof == &s->prof) t_prof = nullptr;
     delete s;

@@ -25,6 +25,29 @@ struct Nccl {
     int (*CommInitAll)(void**, int, const int*) = nullptr;
 };
 
+// Peer-memory transport (peer.cu): every rank owns one "box" in its device memory that its neighbours write
+// into over NVLink (cudaDeviceEnablePeerAccess inside one process, cudaIpc handles across processes): halo
+// mailboxes, reduction slots and sequence flags.  No library call on the data path.
+constexpr int PEER_MAX_RANKS = 16;
+constexpr int PEER_MAX_FIELDS = 6;
+constexpr int PEER_RED_WORDS = 8;
+struct PeerBoxHeader {                       // lives at offset 0 of a box; flags are monotone sequence numbers
+    unsigned long long hflag[2][2];          // [side lo/hi][buffer]: halo planes of exchange #seq have landed
+    unsigned long long rflag[PEER_MAX_RANKS][2];  // [source rank][buffer]: its reduction payload #seq has landed
+    double rval[2][PEER_MAX_RANKS][PEER_RED_WORDS];
+    unsigned ticket;                         // last-block detection of the push kernel (self-resetting)
+    unsigned pad[15];
+};
+struct Peer {
+    bool on = false;
+    char* box = nullptr;                     // my box (device memory, cudaMalloc)
+    char* peer_box[PEER_MAX_RANKS] = {};     // every rank's box as mapped here (peer_box[rank] == box)
+    bool ipc_mapped[PEER_MAX_RANKS] = {};    // opened with cudaIpcOpenMemHandle (to be closed)
+    size_t cnt = 0;                          // doubles per halo layer
+    size_t box_bytes = 0;
+    unsigned long long hseq = 0, rseq = 0;   // exchanges / reductions issued so far (identical on every rank)
+};
+
 struct MgState;  // multigrid hierarchy of a session (poisson_mg.cu)
 
 enum FieldMask { FM_U = 1, FM_V = 2, FM_W = 4, FM_P = 8, FM_RHO = 16, FM_T = 32, FM_ALL = 63 };
@@ -61,6 +84,7 @@ struct cfd_b200_session {
     cfdb::TmaCache tma;
     int zchunk_tma = 1;
     cfdb::Nccl nccl;
+    cfdb::Peer peer;
     poisson_solver_stats_t last_ps = {};
     size_t bytes_allocated = 0;
     // slab bookkeeping: global extent of the decomposed axis (boundary layers included; 0 = uniform slabs,
@@ -103,6 +127,11 @@ cfd_status_t comm_ready(cfd_b200_session* s);
 cfd_status_t comm_check(cfd_b200_session* s);
 size_t global_dec_extent(const cfd_b200_session* s);  // global layers along the decomposed axis
 cfd_status_t load_nccl(Nccl& n, const char* path);
+// peer transport (peer.cu)
+cfd_status_t peer_alloc_box(cfd_b200_session* s);
+void peer_release(cfd_b200_session* s);
+cfd_status_t peer_halo_exchange(cfd_b200_session* s, double* const* fields, int nf, bool periodic_ring);
+cfd_status_t peer_allreduce(cfd_b200_session* s, void* dev, int n, int op);  // op 0 sum f64, 1 max f64, 2 max i32
 cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double** x,
                            double** xtmp, const double* rhs, poisson_solver_stats_t* st);
 // geometric multigrid (poisson_mg.cu): x in place, boundary cells filled at the end; one GPU only

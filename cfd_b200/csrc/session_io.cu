@@ -97,6 +97,7 @@ cfd_status_t load_nccl(Nccl& n, const char* path) {
 cfd_status_t halo_exchange(cfd_b200_session* s, double* const* fields, int nf, bool periodic_ring) {
     const int R = s->desc.nranks, r = s->desc.rank;
     if (R <= 1) return CFD_SUCCESS;
+    if (s->peer.on) return peer_halo_exchange(s, fields, nf, periodic_ring);
     if (!s->nccl.comm) {
         set_error(CFD_ERROR, "multi-rank session without a communicator (call cfd_b200_session_init_comm)");
         if (s->comm_err == CFD_SUCCESS) s->comm_err = CFD_ERROR;
@@ -133,6 +134,7 @@ cfd_status_t halo_exchange(cfd_b200_session* s, double* const* fields, int nf, b
 
 static cfd_status_t allreduce_any(cfd_b200_session* s, void* dev, int cnt, int dtype, int op) {
     if (s->desc.nranks <= 1) return CFD_SUCCESS;
+    if (s->peer.on) return peer_allreduce(s, dev, cnt, dtype == 2 ? 2 : (op == 2 ? 1 : 0));
     if (!s->nccl.comm) {
         set_error(CFD_ERROR, "multi-rank session without a communicator (call cfd_b200_session_init_comm)");
         if (s->comm_err == CFD_SUCCESS) s->comm_err = CFD_ERROR;
@@ -152,16 +154,23 @@ cfd_status_t allreduce(cfd_b200_session* s, double* dev, int cnt, bool is_max) {
 cfd_status_t allreduce_int_max(cfd_b200_session* s, int* dev, int cnt) { return allreduce_any(s, dev, cnt, 2, 2); }
 
 cfd_status_t comm_ready(cfd_b200_session* s) {
-    if (s->desc.nranks > 1 && !s->nccl.comm) {
+    if (s->desc.nranks > 1 && !s->nccl.comm && !s->peer.on) {
         set_error(CFD_ERROR, "session is rank %d of %d but has no communicator (call cfd_b200_session_init_comm)",
                   s->desc.rank, s->desc.nranks);
         return CFD_ERROR;
     }
     return CFD_SUCCESS;
 }
+// (call after a host synchronisation that refreshed h_ctl[0])
 cfd_status_t comm_check(cfd_b200_session* s) {
-    const cfd_status_t rc = s->comm_err;
+    cfd_status_t rc = s->comm_err;
     s->comm_err = CFD_SUCCESS;
+    if (rc == CFD_SUCCESS && s->peer.on && s->h_ctl[0].comm_timeout) {
+        set_error(CFD_ERROR, "peer transport: rank %d waited too long for a neighbour (lost rank or mismatched call sequence)",
+                  s->desc.rank);
+        cudaMemsetAsync(&s->ctl->comm_timeout, 0, sizeof(int), s->st);
+        rc = CFD_ERROR;
+    }
     return rc;
 }
 size_t global_dec_extent(const cfd_b200_session* s) {

@@ -68,6 +68,7 @@ static cfd_status_t read_flags(cfd_b200_session* s, int* nonfinite) {
     CFDB_CUDA_OK(cudaMemcpyAsync(&s->h_ctl[0], s->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s->st));
     CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
     *nonfinite = s->h_ctl[0].nonfinite;
+    if (s->desc.nranks > 1 && comm_check(s) != CFD_SUCCESS) return CFD_ERROR;
     return CFD_SUCCESS;
 }
 

@@ -110,10 +110,33 @@ def broadcast_unique_id(make_id, rank, src=0):
     return bytes(buf.cpu().tolist())
 
 
-def attach_comm(session, rank, nranks):
-    """Create the library-side NCCL communicator of `session` (all ranks must call)."""
+def attach_peers(session, rank, nranks):
+    """Peer-memory transport across processes: every rank exports its box as a cudaIpcMemHandle, the handles
+    are all-gathered, every rank maps the others' boxes.  Returns True when EVERY rank succeeded."""
+    import torch.distributed as td
+    try:
+        mine = session.peer_export()
+    except Exception:
+        mine = None
+    got = [None] * nranks
+    td.all_gather_object(got, mine)
+    ok = all(h is not None for h in got)
+    if ok:
+        ok = session.peer_attach(b"".join(got)) == 0
+    flags = [None] * nranks
+    td.all_gather_object(flags, bool(ok))
+    return all(flags)
+
+
+def attach_comm(session, rank, nranks, transport=None):
+    """Connect the slab of `session` to its neighbours (all ranks must call): the peer-memory transport
+    (csrc/peer.cu) when every rank can map the others' memory, else an NCCL communicator owned by the library.
+    transport / env CFD_B200_TRANSPORT: "peer" (default, falls back to NCCL), "nccl"."""
     from .lib import check, load
     if nranks <= 1:
+        return
+    transport = transport or os.environ.get("CFD_B200_TRANSPORT", "peer")
+    if transport == "peer" and attach_peers(session, rank, nranks):
         return
     L = load()
     path = find_nccl()

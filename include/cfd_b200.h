@@ -565,6 +565,17 @@ CFD_B200_API cfd_status_t cfd_b200_session_set_slab(cfd_b200_session_t* s, size_
  * CFD_B200_SESSION_CACHE = 2 shapes); this frees the idle ones. */
 CFD_B200_API void cfd_b200_release_cached_sessions(void);
 
+/* ---- Peer-memory transport between slabs (csrc/peer.cu) ----
+ * Halo layers and the <= 8-word all-reduces of the Krylov / residual scalars travel by direct stores into the
+ * neighbours' device memory over NVLink, with sequence flags instead of a communication library.  Slabs of one
+ * process (cfd_b200_set_device_count) are connected automatically; one process per GPU: every rank exports a
+ * 64-byte handle, the caller gathers them in rank order (nranks x 64 bytes) and every rank attaches.  After a
+ * successful attach the session uses this transport; otherwise the NCCL communicator of
+ * cfd_b200_session_init_comm.  cfd_b200_session_transport: 0 none, 1 NCCL, 2 peer memory. */
+CFD_B200_API cfd_status_t cfd_b200_session_peer_export(cfd_b200_session_t* s, char out[64]);
+CFD_B200_API cfd_status_t cfd_b200_session_peer_attach(cfd_b200_session_t* s, const char* handles);
+CFD_B200_API int cfd_b200_session_transport(const cfd_b200_session_t* s);
+
 /* ---- Host-sync policy of an ns_solver_t made by the cfd_b200_create_*_gpu_solver factories ----
  * FULL (default): every step()/solve() uploads the caller's fields and downloads the result -- a drop-in with
  * no assumptions.  UPLOAD_BOUNDARY: the caller promises that, since the previous call on this solver returned,

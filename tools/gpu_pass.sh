@@ -1,0 +1,91 @@
+#!/bin/bash
+# One parametrised GPU job script (run on the box through gpurun):
+#
+#   gpurun --timeout 1500 -- 'bash tools/gpu_pass.sh TAG stage [stage ...]'
+#
+# Every stage writes into gpurun_out/ with the TAG prefix; what is worth keeping is copied to profiles/ by hand.
+#   tests        pytest -m gpu (whole suite)                      tests:<expr>  pytest -m gpu -k <expr>
+#   smoke        __graft_entry__.smoke()
+#   bench        python bench.py (default run)                    bench:<args>  extra bench.py arguments
+#   parity:N     tests/multigpu_parity.py under torchrun, N ranks (needs gpurun --gpus N)
+#   scale:N      torchrun bench.py --gpus N
+#   tables       tools/kernel_table.py over the BASELINE.json shapes
+#   launches     ncu launch list (gpu__time_duration.sum) of the default bench command + share summary
+#   ncu          ncu --set full of the headline kernels -> profiles-ready CSV (tools/ncu_summary.py)
+#   ncu512       ncu --set full of the 512^3 kernels that are not part of the headline
+#   sass         SASS opcode histogram of the shipped cubins (runs anywhere)
+TAG=$1; shift
+mkdir -p gpurun_out
+O=gpurun_out/$TAG
+torchrun_() { n=$1; shift; python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500 + n)) "$@"; }
+for stage in "$@"; do
+  arg=${stage#*:}; [ "$arg" = "$stage" ] && arg=""
+  case ${stage%%:*} in
+    tests)
+      if [ -n "$arg" ]; then timeout 1500 python -m pytest tests -m gpu -q -x -k "$arg" > ${O}_pytest.log 2>&1
+      else timeout 1500 python -m pytest tests -m gpu -q > ${O}_pytest.log 2>&1; fi
+      echo "pytest exit $?" >> ${O}_pytest.log; tail -15 ${O}_pytest.log | cut -c1-400 ;;
+    smoke)
+      timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > ${O}_smoke.log 2>&1; echo "smoke exit $?" >> ${O}_smoke.log
+      tail -3 ${O}_smoke.log | cut -c1-300 ;;
+    bench)
+      timeout 900 python bench.py $arg > ${O}_bench.json 2> ${O}_bench.err; echo "bench exit $?"
+      cut -c1-600 ${O}_bench.json; tail -3 ${O}_bench.err ;;
+    parity)
+      timeout 900 bash -c "$(declare -f torchrun_); torchrun_ $arg tests/multigpu_parity.py" > ${O}_parity_${arg}gpu.log 2>&1
+      echo "parity exit $?" >> ${O}_parity_${arg}gpu.log; grep -E "ok|FAIL|PARITY|exit|Error" ${O}_parity_${arg}gpu.log | tail -50 | cut -c1-200 ;;
+    scale)
+      n=${arg%% *}; extra=${arg#$n}
+      timeout 1200 bash -c "$(declare -f torchrun_); torchrun_ $n bench.py --gpus $n $extra" > ${O}_bench_${n}gpu.json 2> ${O}_bench_${n}gpu.err
+      echo "scale exit $?"; cut -c1-500 ${O}_bench_${n}gpu.json; tail -3 ${O}_bench_${n}gpu.err | cut -c1-300 ;;
+    tables)
+      out=${O}_kernel_tables.jsonl; : > $out
+      run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
+      for m in jacobi rbsor cg pcg bicgstab; do run --shape 512,512,512 --stepper projection --method $m --iters 50; done
+      run --shape 512,512,512 --stepper rk2; run --shape 512,512,512 --stepper rk4; run --shape 512,512,512 --stepper euler
+      run --shape 512,512,512 --stepper projection --method cg --iters 50 --energy
+      run --shape 128,128,128 --stepper rk4 --steps 20; run --shape 256,256,256 --stepper projection --method rbsor --iters 100
+      run --shape 4096,4096,1 --stepper projection --method pcg --iters 50 --energy
+      run --shape 4096,4096,1 --stepper projection --method rbsor --iters 50
+      run --shape 129,129,1 --stepper projection --method jacobi --iters 50
+      run --shape 1024,1024,1024 --stepper projection --method rbsor --iters 20 --steps 1
+      wc -l $out ;;
+    launches)
+      timeout 600 python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu > ${O}_launch_bench.json 2>/dev/null &&
+      timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file ${O}_launches.csv \
+          python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu > ${O}_ncu_launches.log 2>&1
+      python tools/launch_list_summary.py ${O}_launches.csv ${O}_launch_bench.json > ${O}_launch_list_summary.md; tail -20 ${O}_launch_list_summary.md ;;
+    ncu)
+      timeout 600 python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu > /dev/null 2>&1 &&
+      timeout 1200 ncu --set full --clock-control none --import-source on \
+          -k regex:'bicg_dir_tma|bicg_s_tma|bicg_update|predictor_tma|divergence_tma|corrector_tma|krylov_init' \
+          --launch-skip 12 -c 14 -o ${O}_ncu_headline -f python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu > ${O}_ncu_full.log 2>&1
+      box=$(python -c "import json;print(json.load(open('${O}_launch_bench.json'))['config']['grid_global'][0])" 2>/dev/null || echo 1024)
+      python tools/ncu_summary.py "ncu --set full --clock-control none, python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu; box=$box; $(date -u +%F) $TAG" \
+          ${O}_ncu_headline.csv ${O}_ncu_headline.ncu-rep
+      if [ $(stat -c %s ${O}_ncu_headline.ncu-rep) -gt 40000000 ]; then rm ${O}_ncu_headline.ncu-rep; fi ;;
+    ncu512)
+      cat > /tmp/prof512.py <<'PY'
+import subprocess, sys
+for args in (["--stepper", "projection", "--method", "jacobi", "--iters", "3"],
+             ["--stepper", "projection", "--method", "rbsor", "--iters", "3"],
+             ["--stepper", "projection", "--method", "cg", "--iters", "3"],
+             ["--stepper", "rk4"], ["--stepper", "euler"]):
+    r = subprocess.run([sys.executable, "tools/kernel_table.py", "--shape", "512,512,512", "--steps", "1"] + args,
+                       capture_output=True, text=True)
+    if r.returncode != 0:
+        print(r.stdout[-2000:], r.stderr[-2000:]); sys.exit(1)
+PY
+      timeout 300 python /tmp/prof512.py &&
+      timeout 900 ncu --set full --clock-control none --import-source on --target-processes all \
+          -k regex:'jacobi_tma|rbsor_fused|cg_dir_tma|cg_update|rk_stage_tma|predictor_tma|corrector_tma|euler_tma' \
+          -c 40 -o ${O}_ncu_512 -f python /tmp/prof512.py > ${O}_ncu_512.log 2>&1
+      python tools/ncu_summary.py "ncu --set full --clock-control none, tools/kernel_table.py --shape 512,512,512 (jacobi, rbsor, cg, rk4, euler); $(date -u +%F) $TAG" \
+          ${O}_ncu_512.csv ${O}_ncu_512.ncu-rep
+      if [ $(stat -c %s ${O}_ncu_512.ncu-rep) -gt 40000000 ]; then rm ${O}_ncu_512.ncu-rep; fi ;;
+    sass)
+      python tools/sass_histogram.py > ${O}_sass_histogram.md; head -30 ${O}_sass_histogram.md ;;
+    *) echo "unknown stage $stage" ;;
+  esac
+done
+ls -la gpurun_out | tail -20
