@@ -24,6 +24,11 @@ def set_device_count(n):
     check(load().cfd_b200_set_device_count(int(n)), "cfd_b200_set_device_count")
 
 
+def set_arithmetic(fast):
+    """Arithmetic policy of sessions / solvers created afterwards: 0 exact (default), 1 fast, -1 environment."""
+    check(load().cfd_b200_set_arithmetic(int(fast)), "cfd_b200_set_arithmetic")
+
+
 def get_device_count():
     return int(load().cfd_b200_get_device_count())
 

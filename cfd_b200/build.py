@@ -28,14 +28,21 @@ def _newest_dep():
     return t
 
 
-def _compile(src):
-    obj = os.path.join(OBJ, src.replace(".cu", ".o"))
-    r = subprocess.run([NVCC, *FLAGS, "-c", os.path.join(CSRC, src), "-o", obj],
+# kernel translation units that are also built with the "fast" arithmetic policy (csrc/common.cuh): FMA contraction on,
+# quotients as reciprocal multiplies; their kernels / launchers land in cfdb::arith_fast
+FAST_TWINS = ["poisson_kernels.cu", "ns_kernels.cu", "ns_kernels2.cu"]
+FAST_FLAGS = [f for f in FLAGS if f != "-fmad=false"] + ["-fmad=true", "-DCFDB_FAST"]
+
+
+def _compile(job):
+    src, fast = job
+    obj = os.path.join(OBJ, src.replace(".cu", "_fast.o" if fast else ".o"))
+    r = subprocess.run([NVCC, *(FAST_FLAGS if fast else FLAGS), "-c", os.path.join(CSRC, src), "-o", obj],
                        capture_output=True, text=True)
     with open(obj + ".log", "w") as fh:
         fh.write(r.stdout + r.stderr)
     if r.returncode != 0:
-        raise RuntimeError("nvcc failed on %s:\n%s" % (src, (r.stdout + r.stderr)[-4000:]))
+        raise RuntimeError("nvcc failed on %s%s:\n%s" % (src, " (fast)" if fast else "", (r.stdout + r.stderr)[-4000:]))
     return obj
 
 
@@ -44,7 +51,7 @@ def build(force=False, verbose=False):
         return LIB
     os.makedirs(OBJ, exist_ok=True)
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 2)) as ex:
-        objs = list(ex.map(_compile, SOURCES))
+        objs = list(ex.map(_compile, [(f, False) for f in SOURCES] + [(f, True) for f in FAST_TWINS]))
     r = subprocess.run([NVCC, "-shared", "-o", LIB, *objs, "-ldl", "-lpthread"],
                        capture_output=True, text=True)
     if r.returncode != 0:

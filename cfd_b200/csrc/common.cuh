@@ -8,6 +8,20 @@
 
 #include "../../include/cfd_b200.h"
 
+// Two builds of the stencil / Poisson kernel translation units (cfd_b200/build.py):
+//   exact (default)  -fmad=false, the reference's divisions reproduced bit for bit (ediv);
+//   fast (CFDB_FAST) -fmad=true (FMA contraction), quotients as reciprocal multiplies -- same formulas, last-bit
+//                    different; selected per session (CFD_B200_ARITH=fast / cfd_b200_set_arithmetic).
+// The fast twins live in the inline namespace cfdb::arith_fast so both sets of kernels and launchers link into
+// one library under distinct symbols.
+#ifdef CFDB_FAST
+#define CFDB_ARITH_BEGIN inline namespace arith_fast {
+#define CFDB_ARITH_END }
+#else
+#define CFDB_ARITH_BEGIN
+#define CFDB_ARITH_END
+#endif
+
 namespace cfdb {
 
 // ---------------------------------------------------------------------------------------
@@ -135,6 +149,10 @@ __device__ __forceinline__ void max_into(double& m, double r) {
 // instructions instead of the ~14 of the generic FP64 division sequence.  Differs only for
 // non-finite a (NaN instead of Inf; both are caught by the same scans) and denormal quotients.
 __device__ __forceinline__ double ediv(double a, double b, double y) {
+#ifdef CFDB_FAST
+    (void)b;
+    return a * y;
+#endif
     const double q = a * y;
     const double r = fma(-b, q, a);
     return fma(r, y, q);
@@ -149,7 +167,11 @@ struct RhoDiv {
     double rh, y;
     bool plain;
     __device__ __forceinline__ explicit RhoDiv(double rho) : rh(rho), y(1.0 / rho), plain(!(rho <= 1e100)) {}
+#ifdef CFDB_FAST
+    __device__ __forceinline__ double operator()(double a) const { return a * y; }
+#else
     __device__ __forceinline__ double operator()(double a) const { return plain ? a / rh : ediv(a, rh, y); }
+#endif
 };
 
 __device__ __forceinline__ double warp_sum(double v) {

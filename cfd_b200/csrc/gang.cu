@@ -125,7 +125,8 @@ bool runner_matches(const Runner* r, const flow_field* f, const grid* g, int wan
     int dev = 0;
     cudaGetDevice(&dev);
     return r->nx == f->nx && r->ny == f->ny && r->nz == f->nz && r->dx == g->dx[0] && r->dy == g->dy[0] &&
-           r->dz == dz && r->G == effective_gpus(f, want) && r->dev0 == dev;
+           r->dz == dz && r->G == effective_gpus(f, want) && r->dev0 == dev && !r->s.empty() &&
+           r->s[0]->fast == default_fast_arithmetic();
 }
 
 void runner_destroy(Runner* r) {

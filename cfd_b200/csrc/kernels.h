@@ -60,35 +60,6 @@ struct Profiler {
 };
 extern thread_local Profiler* t_prof;
 
-// ---- Poisson ----
-void launch_neumann_fill(const LaunchCtx& L, double* x, int seq, int honour_skip, bool use_ctl);
-void launch_jacobi(const LaunchCtx& L, const KArgs& a, const double* xin, double* xout, const double* rhs);
-void launch_redblack(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs, int colour, int decide);
-bool rbsor_fused_available(const LaunchCtx& L);
-// whole Red-Black SOR iteration x_q -> x_{q+1} out of place (+ res(x_q)); false => not launched, use the half-sweeps
-bool launch_rbsor_fused(const LaunchCtx& L, const KArgs& a, const double* xin, double* xout, const double* rhs);
-// whole Jacobi solve of a small 2-D grid in one thread-block-cluster launch (poisson_mini.cu); x in place
-bool jacobi_cluster_available(const LaunchCtx& L);
-bool launch_jacobi_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs);
-// whole (P)CG solve of a small 2-D grid in one cluster launch; the caller runs the Neumann passes around it
-bool cg_cluster_available(const LaunchCtx& L);
-bool launch_cg_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs, int precond);
-void launch_linf_residual(const LaunchCtx& L, const KArgs& a, const double* x, const double* rhs, int slot);
-void launch_stationary_final(const LaunchCtx& L, const KArgs& a);
-void launch_krylov_init(const LaunchCtx& L, const KArgs& a, const double* x, const double* rhs, double* r,
-                        double* p0, double* rhat, int precond);
-void launch_cg_dir(const LaunchCtx& L, const KArgs& a, const double* r, const double* pold, double* pnew,
-                   double* Ap, int precond, int decide_only);
-void launch_cg_update(const LaunchCtx& L, const KArgs& a, double* x, double* r, const double* p,
-                      const double* Ap, int precond);
-void launch_bicg_dir(const LaunchCtx& L, const KArgs& a, const double* r, const double* pold,
-                     const double* vold, const double* rhat, double* pnew, double* vnew, int first,
-                     int decide_only);
-void launch_bicg_s(const LaunchCtx& L, const KArgs& a, const double* r, const double* v, double* s, double* t);
-void launch_bicg_update(const LaunchCtx& L, const KArgs& a, double* x, double* r, const double* p,
-                        const double* s, const double* t, const double* rhat);
-
-// ---- Navier-Stokes step ----
 struct NsConst {            // per-step constants of the projection / RK kernels
     double dt, nu, rho, dt_over_rho, rho_over_dt;
     double beta, T_ref, gx, gy, gz;   // Boussinesq (energy_solver.c:185-196)
@@ -97,38 +68,25 @@ struct NsConst {            // per-step constants of the projection / RK kernels
     double mu;                         // RK: nu_eff = min(mu/rho, 1)
     double src_decay;                  // exp(-lambda*iter*dt) (solver_explicit_euler.c:326-331)
 };
-// su_tab[j] = A_u sin(pi y_j) exp(-lambda*iter*dt), sv_tab[i] = A_v sin(2 pi x_i) exp(...): evaluated
-// on the host with libm so device libm differences cannot enter.
-void launch_predictor(const LaunchCtx& L, const NsConst& c, const double* u, const double* v, const double* w,
-                      const double* T, const double* su_tab, const double* sv_tab, double* us, double* vs,
-                      double* ws);
-void launch_divergence(const LaunchCtx& L, const NsConst& c, const double* us, const double* vs,
-                       const double* ws, double* rhs);
-void launch_corrector(const LaunchCtx& L, const NsConst& c, const double* us, const double* vs,
-                      const double* ws, const double* p, double* u, double* v, double* w, const double* T,
-                      double* Tn);
-void launch_energy(const LaunchCtx& L, const NsConst& c, const double* u, const double* v, const double* w,
-                   const double* T, double* Tn);
-void launch_thermal_bc(const LaunchCtx& L, const ns_thermal_bc_config_t& bc, double* T);
-void launch_periodic_bc(const LaunchCtx& L, double* f, int wrap_y, int wrap_z);
-void launch_periodic_faces(const LaunchCtx& L, double* const* f, int nf, int wrap_y, int wrap_z);
-void launch_field_stats(const LaunchCtx& L, const double* u, const double* v, const double* w,
-                        const double* p, const double* T);
-void launch_rk_stage(const LaunchCtx& L, const NsConst& c, const RkArgs& ra, const P4& qin, const P4& q0,
-                      const W4& acc, const W4& qout, const double* rho, const double* T,
-                      const double* su_tab, const double* sv_tab);
-// explicit Euler step (interior cells, out of place) and the O(N^(2/3)) boundary helpers
-void launch_euler(const LaunchCtx& L, const NsConst& c, const EulerArgs& ea, const P4& qin, const W4& qout,
-                  const double* rho, const double* T, const double* su_tab, const double* sv_tab);
-void launch_boundary_carry3(const LaunchCtx& L, const double* u, const double* v, const double* w, double* us,
-                            double* vs, double* ws);
-void launch_boundary_scan(const LaunchCtx& L, const double* u, const double* v, const double* w, const double* p);
-void launch_synth_init(const LaunchCtx& L, uint64_t seed, long long gk0, long long gnz, double* u, double* v,
-                       double* w, double* p, double* T, double* rho);
-void launch_copy(const LaunchCtx& L, double* dst, const double* src, size_t n);
-void launch_fill(const LaunchCtx& L, double* dst, double v, size_t n);
-void launch_zero_ctl(const LaunchCtx& L);
 
+// launchers of the two arithmetic builds (common.cuh): exact ones in cfdb::, fast twins in cfdb::arith_fast::
+#ifdef CFDB_FAST
+inline namespace arith_fast {
+#include "launchers.inc"
+}
+#else
+#include "launchers.inc"
+namespace arith_fast {
+#include "launchers.inc"
+}
+#endif
+// exact build only (poisson_mini.cu): whole solves of small 2-D grids in one thread-block-cluster launch
+// whole Jacobi solve of a small 2-D grid in one thread-block-cluster launch (poisson_mini.cu); x in place
+bool jacobi_cluster_available(const LaunchCtx& L);
+bool launch_jacobi_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs);
+// whole (P)CG solve of a small 2-D grid in one cluster launch; the caller runs the Neumann passes around it
+bool cg_cluster_available(const LaunchCtx& L);
+bool launch_cg_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs, int precond);
 
 #define CFDB_LAUNCH(kind, st, ...)                         \
     do {                                                   \

@@ -18,6 +18,7 @@
 #include <limits.h>
 
 namespace cfdb {
+CFDB_ARITH_BEGIN
 
 constexpr int TX = 32, TY = 8;
 
@@ -366,4 +367,5 @@ void launch_energy(const LaunchCtx& L, const NsConst& c, const double* u, const 
     else CFDB_LAUNCH(KK_CORRECTOR, L.st, k_energy<false><<<L.grid(), blk2(), 0, L.st>>>(L.g, c, L.zchunk, u, v, w, T, Tn, L.ctl));
 }
 
+CFDB_ARITH_END
 }  // namespace cfdb

@@ -8,6 +8,7 @@
 #include <limits.h>
 
 namespace cfdb {
+CFDB_ARITH_BEGIN
 
 constexpr int TX = 32, TY = 8;
 
@@ -544,4 +545,5 @@ __global__ void k_zero_ctl(Ctl* ctl) {
 
 #include "ns_launch2.inc"
 
+CFDB_ARITH_END
 }  // namespace cfdb

@@ -86,7 +86,7 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         else gny = global_dec_extent(s);
         a.omega = pp.omega > 0.0 ? pp.omega : optimal_omega(s->desc, gnx, gny, gnz);
     }
-    launch_zero_ctl(L);
+    CFDB_KL(s, launch_zero_ctl)(L);
     Poll poll{s};
     const int B = batch_size(s);
     double* x = *px;
@@ -96,7 +96,7 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
 
     // the one-pass Red-Black SOR iteration is out of place: it needs the ping-pong partner as well
     // (no memory for it => the in-place half-sweeps below)
-    if (method == POISSON_METHOD_REDBLACK_SOR && R == 1 && pxt && !*pxt && rbsor_fused_available(L) &&
+    if (method == POISSON_METHOD_REDBLACK_SOR && R == 1 && pxt && !*pxt && CFDB_KL(s, rbsor_fused_available)(L) &&
         dalloc(s, pxt) != CFD_SUCCESS)
         *pxt = nullptr;
 
@@ -113,7 +113,7 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
             for (int b = 0; b < B && q <= a.max_iter; b++, q++) {
                 a.seq = seq++;
                 a.it = q;
-                launch_jacobi(L, a, buf[q & 1], buf[(q + 1) & 1], rhs);
+                CFDB_KL(s, launch_jacobi)(L, a, buf[q & 1], buf[(q + 1) & 1], rhs);
                 if (R > 1) {
                     double* f[1] = {buf[(q + 1) & 1]};
                     halo_exchange(s, f, 1, false);
@@ -124,13 +124,13 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         }
         a.seq = seq++;
         a.it = a.max_iter;
-        launch_stationary_final(L, a);
+        CFDB_KL(s, launch_stationary_final)(L, a);
         const Ctl& c = poll.final_state();
         if (c.result_buf == 1) {  // x lives in the ping-pong partner: swap the caller's pointers
             *px = buf[1];
             *pxt = buf[0];
         }
-    } else if (method == POISSON_METHOD_REDBLACK_SOR && R == 1 && pxt && *pxt && rbsor_fused_available(L) &&
+    } else if (method == POISSON_METHOD_REDBLACK_SOR && R == 1 && pxt && *pxt && CFDB_KL(s, rbsor_fused_available)(L) &&
                L.tc->get_wide(x) && L.tc->get_wide(*pxt) && L.tc->get(rhs)) {
         // one pass per iteration, same protocol as Jacobi: sweep q reads x_q, writes x_{q+1}, leaves res(x_q)
         double* buf[2] = {x, *pxt};
@@ -138,13 +138,13 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
             for (int b = 0; b < B && q <= a.max_iter; b++, q++) {
                 a.seq = seq++;
                 a.it = q;
-                if (!launch_rbsor_fused(L, a, buf[q & 1], buf[(q + 1) & 1], rhs)) return CFD_ERROR;
+                if (!CFDB_KL(s, launch_rbsor_fused)(L, a, buf[q & 1], buf[(q + 1) & 1], rhs)) return CFD_ERROR;
             }
             if (poll.step()) break;
         }
         a.seq = seq++;
         a.it = a.max_iter;
-        launch_stationary_final(L, a);
+        CFDB_KL(s, launch_stationary_final)(L, a);
         const Ctl& c = poll.final_state();
         if (c.result_buf == 1) {
             *px = buf[1];
@@ -152,21 +152,21 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         }
     } else if (method == POISSON_METHOD_REDBLACK_SOR) {
         a.seq = seq++;
-        launch_linf_residual(L, a, x, rhs, 0);
+        CFDB_KL(s, launch_linf_residual)(L, a, x, rhs, 0);
         if (R > 1) allreduce(s, &s->ctl->dot[0], 1, true);
         for (int it = 0; it < a.max_iter;) {
             for (int b = 0; b < B && it < a.max_iter; b++, it++) {
                 a.it = it;
                 double* f[1] = {x};
                 a.seq = seq++;
-                launch_redblack(L, a, x, rhs, 0, 1);
+                CFDB_KL(s, launch_redblack)(L, a, x, rhs, 0, 1);
                 if (R > 1) halo_exchange(s, f, 1, false);
                 a.seq = seq++;
-                launch_redblack(L, a, x, rhs, 1, 0);
+                CFDB_KL(s, launch_redblack)(L, a, x, rhs, 1, 0);
                 if (R > 1) halo_exchange(s, f, 1, false);
                 if (it % a.check == 0) {
                     a.seq = seq++;
-                    launch_linf_residual(L, a, x, rhs, (it + 1) & 1);
+                    CFDB_KL(s, launch_linf_residual)(L, a, x, rhs, (it + 1) & 1);
                     if (R > 1) allreduce(s, &s->ctl->dot[(it + 1) & 1], 1, true);
                 }
             }
@@ -174,24 +174,24 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         }
         a.seq = seq++;
         a.it = a.max_iter;
-        launch_stationary_final(L, a);
+        CFDB_KL(s, launch_stationary_final)(L, a);
         (void)poll.final_state();
     } else if (method == POISSON_METHOD_CG && R == 1 && cg_cluster_available(L) &&
-               (launch_neumann_fill(L, x, 0, 0, false), a.seq = seq,
+               (CFDB_KL(s, launch_neumann_fill)(L, x, 0, 0, false), a.seq = seq,
                 launch_cg_cluster(L, a, x, rhs, pp.preconditioner == POISSON_PRECOND_JACOBI))) {
         // small 2-D grid: the whole (P)CG solve ran in one cluster launch between the two Neumann passes
         // (a failed launch leaves only the -- idempotent -- initial pass behind and falls through)
         seq++;
-        launch_neumann_fill(L, x, 0, 1, true);
+        CFDB_KL(s, launch_neumann_fill)(L, x, 0, 1, true);
         (void)poll.final_state();
     } else if (method == POISSON_METHOD_CG) {
         const int pre = (pp.preconditioner == POISSON_PRECOND_JACOBI);
         for (int q = 0; q < 4; q++)
             if ((rc = dalloc(s, &s->kv[q])) != CFD_SUCCESS) return rc;
         double *r = s->kv[0], *Ap = s->kv[1], *pb[2] = {s->kv[2], s->kv[3]};
-        launch_neumann_fill(L, x, 0, 0, false);
+        CFDB_KL(s, launch_neumann_fill)(L, x, 0, 0, false);
         a.seq = seq++;
-        launch_krylov_init(L, a, x, rhs, r, pb[0], nullptr, pre);
+        CFDB_KL(s, launch_krylov_init)(L, a, x, rhs, r, pb[0], nullptr, pre);
         if (R > 1) {
             double* f[2] = {r, pb[0]};
             halo_exchange(s, f, 2, false);
@@ -204,10 +204,10 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
                 // iteration it: p_it lives in pb[it&1]; it == 0 only applies A to p_0
                 double* pold = (it == 0) ? pb[0] : pb[(it - 1) & 1];
                 double* pnew = pb[it & 1];
-                launch_cg_dir(L, a, r, pold, pnew, Ap, pre, 0);
+                CFDB_KL(s, launch_cg_dir)(L, a, r, pold, pnew, Ap, pre, 0);
                 if (R > 1) allreduce(s, &s->ctl->dot[4 + (it & 1)], 1, false);
                 a.seq = seq++;
-                launch_cg_update(L, a, x, r, pnew, Ap, pre);
+                CFDB_KL(s, launch_cg_update)(L, a, x, r, pnew, Ap, pre);
                 if (R > 1) {
                     double* f[1] = {r};
                     halo_exchange(s, f, 1, false);
@@ -218,17 +218,17 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         }
         a.seq = seq++;
         a.it = a.max_iter;
-        launch_cg_dir(L, a, r, pb[0], pb[1], Ap, pre, 1);
-        launch_neumann_fill(L, x, 0, 1, true);
+        CFDB_KL(s, launch_cg_dir)(L, a, r, pb[0], pb[1], Ap, pre, 1);
+        CFDB_KL(s, launch_neumann_fill)(L, x, 0, 1, true);
         (void)poll.final_state();
     } else if (method == POISSON_METHOD_BICGSTAB) {
         for (int q = 0; q < 8; q++)
             if ((rc = dalloc(s, &s->kv[q])) != CFD_SUCCESS) return rc;
         double *r = s->kv[0], *rh = s->kv[1], *sv = s->kv[2], *tv = s->kv[3];
         double *pb[2] = {s->kv[4], s->kv[5]}, *vb[2] = {s->kv[6], s->kv[7]};
-        launch_neumann_fill(L, x, 0, 0, false);
+        CFDB_KL(s, launch_neumann_fill)(L, x, 0, 0, false);
         a.seq = seq++;
-        launch_krylov_init(L, a, x, rhs, r, nullptr, rh, 0);
+        CFDB_KL(s, launch_krylov_init)(L, a, x, rhs, r, nullptr, rh, 0);
         if (R > 1) {
             double* f[1] = {r};
             halo_exchange(s, f, 1, false);
@@ -240,17 +240,17 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
                 a.seq = seq++;
                 double *pold = pb[(it + 1) & 1], *pnew = pb[it & 1];
                 double *vold = vb[(it + 1) & 1], *vnew = vb[it & 1];
-                launch_bicg_dir(L, a, r, pold, vold, rh, pnew, vnew, it == 0, 0);
+                CFDB_KL(s, launch_bicg_dir)(L, a, r, pold, vold, rh, pnew, vnew, it == 0, 0);
                 if (R > 1) {
                     double* f[1] = {vnew};
                     halo_exchange(s, f, 1, false);
                     allreduce(s, &s->ctl->dot[4 + (it & 1)], 1, false);
                 }
                 a.seq = seq++;
-                launch_bicg_s(L, a, r, vnew, sv, tv);
+                CFDB_KL(s, launch_bicg_s)(L, a, r, vnew, sv, tv);
                 if (R > 1) allreduce(s, &s->ctl->dot[8 + 4 * (it & 1)], 3, false);
                 a.seq = seq++;
-                launch_bicg_update(L, a, x, r, pnew, sv, tv, rh);
+                CFDB_KL(s, launch_bicg_update)(L, a, x, r, pnew, sv, tv, rh);
                 if (R > 1) {
                     double* f[1] = {r};
                     halo_exchange(s, f, 1, false);
@@ -261,8 +261,8 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         }
         a.seq = seq++;
         a.it = a.max_iter;
-        launch_bicg_dir(L, a, r, pb[0], vb[0], rh, pb[1], vb[1], 0, 1);
-        launch_neumann_fill(L, x, 0, 1, true);
+        CFDB_KL(s, launch_bicg_dir)(L, a, r, pb[0], vb[0], rh, pb[1], vb[1], 0, 1);
+        CFDB_KL(s, launch_neumann_fill)(L, x, 0, 1, true);
         (void)poll.final_state();
     } else {
         set_error(CFD_ERROR_UNSUPPORTED, "Poisson method %d has no GPU implementation", method);

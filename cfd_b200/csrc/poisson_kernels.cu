@@ -18,6 +18,7 @@
 #include <limits.h>
 
 namespace cfdb {
+CFDB_ARITH_BEGIN
 
 constexpr int TX = 32, TY = 8;  // thread tile (x fastest): 256 threads, 8 warps
 
@@ -655,10 +656,14 @@ k_bicg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const doub
 // =======================================================================================
 // Host launchers
 // =======================================================================================
+#ifndef CFDB_FAST  // (a member of cfdb::LaunchCtx: defined once, by the exact build)
+CFDB_ARITH_END
 dim3 LaunchCtx::grid() const {
     const int nzi = g.k1 - g.k0;
     return dim3((g.nx + TX - 1) / TX, (g.ny + TY - 1) / TY, (nzi + zchunk - 1) / zchunk);
 }
+CFDB_ARITH_BEGIN
+#endif
 static inline dim3 blk() { return dim3(TX, TY); }
 // grid of the pointwise sweeps: x tiles of PW_THREADS cells, row chunks sized for ~6 waves of
 // 148 x 8 blocks, never more blocks than the partial-sum buffer has rows
@@ -892,4 +897,5 @@ void launch_bicg_update(const LaunchCtx& L, const KArgs& a0, double* x, double* 
     }
 }
 
+CFDB_ARITH_END
 }  // namespace cfdb

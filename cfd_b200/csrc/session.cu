@@ -42,6 +42,14 @@ void set_error(cfd_status_t st, const char* fmt, ...) {
 }
 const char* last_error() { return t_err; }
 
+static std::atomic<int> g_arith{-1};  // -1: environment decides
+bool default_fast_arithmetic() {
+    const int v = g_arith.load();
+    if (v >= 0) return v != 0;
+    const char* e = getenv("CFD_B200_ARITH");
+    return e && !strcmp(e, "fast");
+}
+
 void Profiler::begin(cudaStream_t st) {
     if (used >= (1u << 16)) collect();  // bound the pool on very long profiled runs
     if (used == pool.size()) {
@@ -143,6 +151,13 @@ const char* cfd_b200_last_error(void) { return cfdb::last_error(); }
 const char* cfd_b200_version(void) { return "cfd_b200 0.1.0 (sm_100a, FP64)"; }
 unsigned long long cfd_b200_kernel_launch_count(void) { return g_launches.load(); }
 
+cfd_status_t cfd_b200_set_arithmetic(int fast) {
+    if (fast < -1 || fast > 1) return CFD_ERROR_INVALID;
+    cfdb::g_arith.store(fast);
+    return CFD_SUCCESS;
+}
+int cfd_b200_session_arithmetic(const cfd_b200_session_t* s) { return s && s->fast ? 1 : 0; }
+
 void* cfd_b200_host_alloc(size_t bytes) {
     void* p = nullptr;
     if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
@@ -181,6 +196,7 @@ cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
         }
     }
     cudaGetDevice(&s->dev);
+    s->fast = default_fast_arithmetic();
     fill_geom(s);
     s->N = (size_t)s->g.ncell;
     bool ok = cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) == cudaSuccess;

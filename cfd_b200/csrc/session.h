@@ -87,6 +87,7 @@ struct cfd_b200_session {
     cfdb::Peer peer;
     poisson_solver_stats_t last_ps = {};
     size_t bytes_allocated = 0;
+    bool fast = false;        // arithmetic policy of this session's stencil / Poisson kernels (common.cuh)
     // slab bookkeeping: global extent of the decomposed axis (boundary layers included; 0 = uniform slabs,
     // derived from nranks) -- cfd_b200_session_set_slab
     size_t gdec = 0;
@@ -109,7 +110,11 @@ struct cfd_b200_session {
     }
 };
 
+// launcher of the session's arithmetic build
+#define CFDB_KL(s, fn) ((s)->fast ? cfdb::arith_fast::fn : cfdb::fn)
+
 namespace cfdb {
+bool default_fast_arithmetic();   // cfd_b200_set_arithmetic / CFD_B200_ARITH
 void set_spacing(Geom& g, double dx, double dy, double dz);
 cfd_status_t dalloc(cfd_b200_session* s, double** p);           // zero-filled N doubles
 cfd_status_t session_upload(cfd_b200_session* s, const flow_field* f, int mask);

@@ -74,7 +74,7 @@ static cfd_status_t read_flags(cfd_b200_session* s, int* nonfinite) {
 
 static void fill_stats(cfd_b200_session* s, ns_solver_stats_t* stats, int iters) {
     if (!stats) return;
-    launch_field_stats(s->L(), s->u, s->v, s->w, s->p, s->T);
+    CFDB_KL(s, launch_field_stats)(s->L(), s->u, s->v, s->w, s->p, s->T);
     if (s->desc.nranks > 1) allreduce(s, &s->ctl->stat[0], 3, true);
     cudaMemcpyAsync(&s->h_ctl[0], s->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s->st);
     cudaStreamSynchronize(s->st);
@@ -125,13 +125,13 @@ cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
             double* f[4] = {s->u, s->v, s->w, s->T};
             halo_exchange(s, f, thermo ? 4 : 3, false);
         }
-        launch_predictor(L, c, s->u, s->v, s->w, s->T, s->su_tab, s->sv_tab, s->us, s->vs, s->ws);
+        CFDB_KL(s, launch_predictor)(L, c, s->u, s->v, s->w, s->T, s->su_tab, s->sv_tab, s->us, s->vs, s->ws);
         if (R > 1) {
             double* f[3] = {s->us, s->vs, s->ws};
             halo_exchange(s, f, 3, false);
         }
-        launch_divergence(L, c, s->us, s->vs, s->ws, s->rhs);
-        launch_copy(L, s->pn, s->p, s->N);  // p_new starts from the previous pressure (:108, :253)
+        CFDB_KL(s, launch_divergence)(L, c, s->us, s->vs, s->ws, s->rhs);
+        CFDB_KL(s, launch_copy)(L, s->pn, s->p, s->N);  // p_new starts from the previous pressure (:108, :253)
         poisson_solver_stats_t ps;
         rc = poisson_solve(s, pc, &s->pn, &s->xt, s->rhs, &ps);
         if (rc == CFD_ERROR || rc == CFD_ERROR_NOMEM || rc == CFD_ERROR_UNSUPPORTED || rc == CFD_ERROR_INVALID)
@@ -141,11 +141,11 @@ cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
                       (int)ps.status, ps.iterations);
             return CFD_ERROR_MAX_ITER;  // solver_projection.c:220-224
         }
-        launch_corrector(L, c, s->us, s->vs, s->ws, s->pn, s->u, s->v, s->w, s->T, s->Tn);
+        CFDB_KL(s, launch_corrector)(L, c, s->us, s->vs, s->ws, s->pn, s->u, s->v, s->w, s->T, s->Tn);
         std::swap(s->p, s->pn);  // memcpy(field->p, p_new) without the copy
         if (energy) {
             std::swap(s->T, s->Tn);
-            launch_thermal_bc(s->L(), prm->thermal_bc, s->T);
+            CFDB_KL(s, launch_thermal_bc)(s->L(), prm->thermal_bc, s->T);
         }
         int bad = 0;
         if ((rc = read_flags(s, &bad)) != CFD_SUCCESS) return rc;
@@ -184,7 +184,7 @@ static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm
         if ((rc = dalloc(s, &s->rk[q])) != CFD_SUCCESS) return rc;
     if (!s->rho) {  // session extension: no density uploaded => rho = 1 everywhere
         if ((rc = dalloc(s, &s->rho)) != CFD_SUCCESS) return rc;
-        launch_fill(s->L(), s->rho, 1.0, s->N);
+        CFDB_KL(s, launch_fill)(s->L(), s->rho, 1.0, s->N);
     }
     const bool energy = prm->alpha > 0.0;
     if ((energy || prm->beta != 0.0) && (rc = dalloc(s, &s->T)) != CFD_SUCCESS) return rc;
@@ -212,11 +212,11 @@ static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm
             double* f[6] = {s->u, s->v, s->w, s->p, s->rho, s->T};
             halo_exchange(s, f, s->T ? 6 : 5, false);
         }
-        launch_euler(L, c, ea, in, out, s->rho, s->T, s->su_tab, s->sv_tab);
-        launch_boundary_carry3(L, s->u, s->v, s->w, s->rk[0], s->rk[1], s->rk[2]);
+        CFDB_KL(s, launch_euler)(L, c, ea, in, out, s->rho, s->T, s->su_tab, s->sv_tab);
+        CFDB_KL(s, launch_boundary_carry3)(L, s->u, s->v, s->w, s->rk[0], s->rk[1], s->rk[2]);
         for (int q = 0; q < 4; q++) std::swap(*cur[q], s->rk[q]);  // memcpy(field <- new) without the copy (:528-531)
         if (energy) {
-            launch_energy(L, c, s->u, s->v, s->w, s->T, s->Tn);  // (the halo of T is current: exchanged above)
+            CFDB_KL(s, launch_energy)(L, c, s->u, s->v, s->w, s->T, s->Tn);  // (the halo of T is current: exchanged above)
             std::swap(s->T, s->Tn);
         }
         // apply_boundary_conditions (:231-314) on everything the velocity restore does not undo
@@ -226,10 +226,10 @@ static cfd_status_t run_euler(cfd_b200_session* s, const ns_solver_params_t* prm
         wrap[nw++] = s->rho;
         if (s->T) wrap[nw++] = s->T;  // a T that never reached the device stays on the host untouched
         if (!s->g.dim3) wrap[nw++] = s->w;
-        launch_periodic_faces(L, wrap, nw, wrap_y, wrap_z);
+        CFDB_KL(s, launch_periodic_faces)(L, wrap, nw, wrap_y, wrap_z);
         if (R > 1) halo_exchange(s, wrap, nw, true);
-        if (energy) launch_thermal_bc(L, prm->thermal_bc, s->T);
-        launch_boundary_scan(L, s->u, s->v, s->w, s->p);
+        if (energy) CFDB_KL(s, launch_thermal_bc)(L, prm->thermal_bc, s->T);
+        CFDB_KL(s, launch_boundary_scan)(L, s->u, s->v, s->w, s->p);
         int bad = 0;
         if ((rc = read_flags(s, &bad)) != CFD_SUCCESS) return rc;
         if (bad) {
@@ -269,7 +269,7 @@ cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* pr
         if ((rc = dalloc(s, &s->rk[q])) != CFD_SUCCESS) return rc;
     if (!s->rho) {  // session extension: no density uploaded => rho = 1 everywhere
         if ((rc = dalloc(s, &s->rho)) != CFD_SUCCESS) return rc;
-        launch_fill(s->L(), s->rho, 1.0, s->N);
+        CFDB_KL(s, launch_fill)(s->L(), s->rho, 1.0, s->N);
     }
     const bool energy = prm->alpha > 0.0;
     if ((energy || prm->beta != 0.0) && (rc = dalloc(s, &s->T)) != CFD_SUCCESS) return rc;
@@ -297,46 +297,46 @@ cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* pr
         ra.src_decay = exp(-prm->source_decay_rate * iter * dt);
         // stage inputs carry their periodic images on the boundary cells (the TMA stage kernel reads
         // plain halos; the reference reads wrapped indices -- same values)
-        launch_periodic_faces(L, Aq, 4, wrap_y, wrap_z);
+        CFDB_KL(s, launch_periodic_faces)(L, Aq, 4, wrap_y, wrap_z);
         if (R > 1) halo_exchange(s, Aq, 4, true);
         if (order == 4) {
             // stage 1: k1 = f(Q0); acc = k1; B = Q0 + dt/2 k1
             ra.first = 1; ra.last = 0; ra.fac_next = 0.5 * dt; ra.w_k = 1.0;
-            launch_rk_stage(L, c, ra, P(Aq), P(Aq), W(ACC), W(B), s->rho, s->T, s->su_tab, s->sv_tab);
-            launch_periodic_faces(L, B, 4, wrap_y, wrap_z);
+            CFDB_KL(s, launch_rk_stage)(L, c, ra, P(Aq), P(Aq), W(ACC), W(B), s->rho, s->T, s->su_tab, s->sv_tab);
+            CFDB_KL(s, launch_periodic_faces)(L, B, 4, wrap_y, wrap_z);
             if (R > 1) halo_exchange(s, B, 4, true);
             // stage 2: k2 = f(B); acc += 2 k2; C = Q0 + dt/2 k2
             ra.first = 0; ra.w_k = 2.0;
-            launch_rk_stage(L, c, ra, P(B), P(Aq), W(ACC), W(C), s->rho, s->T, s->su_tab, s->sv_tab);
-            launch_periodic_faces(L, C, 4, wrap_y, wrap_z);
+            CFDB_KL(s, launch_rk_stage)(L, c, ra, P(B), P(Aq), W(ACC), W(C), s->rho, s->T, s->su_tab, s->sv_tab);
+            CFDB_KL(s, launch_periodic_faces)(L, C, 4, wrap_y, wrap_z);
             if (R > 1) halo_exchange(s, C, 4, true);
             // stage 3: k3 = f(C); acc += 2 k3; B = Q0 + dt k3
             ra.fac_next = dt;
-            launch_rk_stage(L, c, ra, P(C), P(Aq), W(ACC), W(B), s->rho, s->T, s->su_tab, s->sv_tab);
-            launch_periodic_faces(L, B, 4, wrap_y, wrap_z);
+            CFDB_KL(s, launch_rk_stage)(L, c, ra, P(C), P(Aq), W(ACC), W(B), s->rho, s->T, s->su_tab, s->sv_tab);
+            CFDB_KL(s, launch_periodic_faces)(L, B, 4, wrap_y, wrap_z);
             if (R > 1) halo_exchange(s, B, 4, true);
             // stage 4: k4 = f(B); Q = Q0 + dt/6 (acc + k4)
             ra.last = 1; ra.w_final = dt / 6.0;
-            launch_rk_stage(L, c, ra, P(B), P(Aq), W(ACC), W(Aq), s->rho, s->T, s->su_tab, s->sv_tab);
+            CFDB_KL(s, launch_rk_stage)(L, c, ra, P(B), P(Aq), W(ACC), W(Aq), s->rho, s->T, s->su_tab, s->sv_tab);
         } else {
             ra.first = 1; ra.last = 0; ra.fac_next = dt; ra.w_k = 1.0;
-            launch_rk_stage(L, c, ra, P(Aq), P(Aq), W(ACC), W(B), s->rho, s->T, s->su_tab, s->sv_tab);
-            launch_periodic_faces(L, B, 4, wrap_y, wrap_z);
+            CFDB_KL(s, launch_rk_stage)(L, c, ra, P(Aq), P(Aq), W(ACC), W(B), s->rho, s->T, s->su_tab, s->sv_tab);
+            CFDB_KL(s, launch_periodic_faces)(L, B, 4, wrap_y, wrap_z);
             if (R > 1) halo_exchange(s, B, 4, true);
             ra.first = 0; ra.last = 1; ra.w_final = 0.5 * dt;
-            launch_rk_stage(L, c, ra, P(B), P(Aq), W(ACC), W(Aq), s->rho, s->T, s->su_tab, s->sv_tab);
+            CFDB_KL(s, launch_rk_stage)(L, c, ra, P(B), P(Aq), W(ACC), W(Aq), s->rho, s->T, s->su_tab, s->sv_tab);
         }
         if (energy) {
             if (R > 1) { double* f[1] = {s->T}; halo_exchange(s, f, 1, false); }
-            launch_energy(L, c, s->u, s->v, s->w, s->T, s->Tn);
+            CFDB_KL(s, launch_energy)(L, c, s->u, s->v, s->w, s->T, s->Tn);
             std::swap(s->T, s->Tn);
         }
         // apply_boundary_conditions: periodic wrap of u,v,w,p,rho,T (solver_explicit_euler.c:231-314)
         double* all[6] = {s->u, s->v, s->w, s->p, s->rho, s->T};
         const int nall = s->T ? 6 : 5;  // a T that never reached the device stays on the host untouched
-        launch_periodic_faces(L, all, nall, wrap_y, wrap_z);
+        CFDB_KL(s, launch_periodic_faces)(L, all, nall, wrap_y, wrap_z);
         if (R > 1) halo_exchange(s, all, nall, true);
-        if (energy) launch_thermal_bc(s->L(), prm->thermal_bc, s->T);
+        if (energy) CFDB_KL(s, launch_thermal_bc)(s->L(), prm->thermal_bc, s->T);
         int bad = 0;
         if ((rc = read_flags(s, &bad)) != CFD_SUCCESS) return rc;
         if (bad) {

@@ -565,6 +565,16 @@ CFD_B200_API cfd_status_t cfd_b200_session_set_slab(cfd_b200_session_t* s, size_
  * CFD_B200_SESSION_CACHE = 2 shapes); this frees the idle ones. */
 CFD_B200_API void cfd_b200_release_cached_sessions(void);
 
+/* ---- Arithmetic policy of the stencil and Poisson kernels (csrc/common.cuh) ----
+ * exact (0, default): no FMA contraction, the reference's divisions reproduced -- Jacobi / Red-Black SOR / RK /
+ * Euler / predictor / corrector results are bit-identical to the reference's CPU path.
+ * fast (1): FMA contraction and reciprocal multiplies instead of divisions -- same formulas, results within
+ * ~1e-13 per step of the exact build (tests/test_gpu_fast.py holds it to the north-star tolerances), fewer FP64
+ * instructions in the issue-bound kernels.  -1 = decide from the environment (CFD_B200_ARITH=fast|exact).
+ * Applies to sessions / solver objects created afterwards. */
+CFD_B200_API cfd_status_t cfd_b200_set_arithmetic(int fast);
+CFD_B200_API int cfd_b200_session_arithmetic(const cfd_b200_session_t* s);
+
 /* ---- Peer-memory transport between slabs (csrc/peer.cu) ----
  * Halo layers and the <= 8-word all-reduces of the Krylov / residual scalars travel by direct stores into the
  * neighbours' device memory over NVLink, with sequence flags instead of a communication library.  Slabs of one
