@@ -48,6 +48,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--budget", type=float, default=150.0, help="seconds of CPU work allowed to --impl reference")
+    ap.add_argument("--config", default="c5", choices=["c5", "c4"],
+                    help="c5 (default, the metric's configuration): 1024^3 box per GPU + BiCGSTAB, weak scaling; "
+                         "c4: BASELINE.json configs[3], 4096^2 natural convection + PCG x iters on y-slabs, STRONG scaling")
     return ap.parse_args()
 
 
@@ -136,6 +139,207 @@ def synthetic_host_field(n, alloc=None):
     f.rho[...] = 1.0
     f.T[...] = 300.0
     return g, f
+
+
+# ------------------------------------------------------------------------------------------
+# C4 (BASELINE.json configs[3]): natural convection 2-D 4096 x 4096 (Boussinesq energy + buoyancy + thermal BCs),
+# projection + PCG, 1/2/4 GPUs on y-slabs.  The grid is FIXED, so this is strong scaling; SURVEY 8e asks for it to
+# be reported honestly: a PCG iteration on a quarter of 16.7 M cells is ~25 us of kernels against two all-reduces
+# and a halo row per iteration.
+# ------------------------------------------------------------------------------------------
+def c4_params():
+    """de Vahl Davis Ra = 1e3 set-up of tests/validation/test_natural_convection.c:49-58,139-200; dt = 2.5e-7
+    (< dx^2 / (4 alpha) at 4096^2)."""
+    import math
+    from cfd_b200 import abi
+    p = abi.ns_params_default()
+    Pr, Ra, beta, gmag, dT = 0.71, 1e3, 0.003333, 9.81, 20.0
+    nu = math.sqrt(gmag * beta * dT * Pr / Ra)
+    p.dt, p.mu, p.alpha, p.beta, p.T_ref = 2.5e-7, nu, nu / Pr, beta, 300.0
+    p.gravity[0], p.gravity[1], p.gravity[2] = 0.0, -gmag, 0.0
+    p.source_amplitude_u = p.source_amplitude_v = 0.0
+    tb = p.thermal_bc
+    tb.left = tb.right = abi.BC_TYPE_DIRICHLET
+    tb.bottom = tb.top = tb.front = tb.back = abi.BC_TYPE_NEUMANN
+    tb.dirichlet_values.left, tb.dirichlet_values.right = 310.0, 290.0
+    p.max_iter = 1
+    return p
+
+
+def c4_host_field(n, rows=None, lo=0, alloc=None):
+    """Rows [lo, lo + rows) of the global n x n state: quiescent, T = 310 - 20 x, p = 0, rho = 1."""
+    import numpy as np
+    from cfd_b200 import abi
+    rows = rows or n
+    f = abi.HostField(n, rows, 1, alloc=alloc) if alloc else abi.HostField(n, rows, 1)
+    x = np.linspace(0.0, 1.0, n)
+    for nm in ("u", "v", "w", "p"):
+        getattr(f, nm)[...] = 0.0
+    f.T[...] = 310.0 - 20.0 * x[None, None, :]
+    f.rho[...] = 1.0
+    return f
+
+
+def slab_partition(layers, world):
+    """(lo, nloc) per rank: global first layer and local layer count incl. halos -- the gang's rule (csrc/gang.cu)."""
+    interior, out, off = layers - 2, [], 0
+    for q in range(world):
+        own = interior // world + (1 if q < interior % world else 0)
+        out.append((off, own + 2))
+        off += own
+    return out
+
+
+def c4_main(a, real_out):
+    import numpy as np
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    td = None
+    if world > 1:
+        import torch.distributed as td
+        td.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from cfd_b200 import abi, api, dist, lib
+    L = lib.load()
+    n = a.n or 4096
+    method = "pcg" if a.method == "bicgstab" else a.method
+    parity = None
+    if td is not None:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import multigpu_parity
+        cx = multigpu_parity.Ctx(td, rank, world, local)
+        parity = multigpu_parity.run_case(cx, "C4 natconv pcg 258x(64w+2) y-slabs", "natconv_y", (258, 64 * world + 2, 1),
+                                          "projection", "pcg", tol=1e-8, nsteps=3, max_iterations=60)
+    h = 1.0 / (n - 1)
+    lo, nloc = slab_partition(n, world)[rank]
+    s = api.Session(n, nloc, 1, h, h, 0.0, 0.0, lo * h, 0.0, rank=rank, nranks=world, device=local)
+    if world > 1:
+        s.set_slab(n, lo)
+    dist.attach_comm(s, rank, world)
+    transport = s.transport()
+    coords = np.linspace(0.0, 1.0, n)
+    s.set_coords(coords, coords[lo:lo + nloc])
+    f = c4_host_field(n, nloc, lo)
+    s.upload(f)
+    prm, pc = c4_params(), poisson_cfg(method, a.iters)
+    stream = torch.cuda.ExternalStream(s.stream())
+
+    def barrier():
+        torch.cuda.synchronize()
+        if td is not None:
+            td.barrier()
+        torch.cuda.synchronize()
+
+    def run_steps(k):
+        rc, st = s.projection(prm, pc, k)
+        if rc != 0:
+            raise RuntimeError("projection failed rc=%d: %s" % (rc, lib.last_error()))
+
+    run_steps(a.warmup)
+    s.reset_kernel_stats()
+    s.profile(True)
+    l0 = L.cfd_b200_kernel_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    with Clocks(local) as clk:
+        e0.record(stream)
+        run_steps(a.steps)
+        e1.record(stream)
+        barrier()
+    ms = e0.elapsed_time(e1)
+    launches = int(L.cfd_b200_kernel_launch_count() - l0)
+    s.profile(False)
+    if td is not None:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        ms = float(t.item())
+    value = n * n * a.steps / (ms * 1e-3) / 1e6
+    interior = (n - 2) * (nloc - 2)
+    peak, peak_src = peaks()
+    ks = [k for k in s.kernel_stats() if k["total_ms"] > 0]
+    ks.sort(key=lambda k: -k["total_ms"])
+    ksum = sum(k["total_ms"] for k in ks) or 1.0
+    table = []
+    for k in ks:
+        avg = k["total_ms"] / k["launches"]
+        gbs = k["bytes_per_cell"] * interior / (avg * 1e-3) / 1e9
+        table.append({"kernel": k["name"], "launches": k["launches"], "avg_us": round(avg * 1e3, 2),
+                      "share": round(k["total_ms"] / ksum, 4), "bytes_per_cell": k["bytes_per_cell"],
+                      "GBps": round(gbs, 1), "frac": round(gbs / peak, 4)})
+    top = next((t for t in table if t["bytes_per_cell"] > 0), None)
+    roofline = None
+    if top:
+        roofline = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["GBps"], "peak": peak, "unit": "GB/s",
+                    "frac": top["frac"], "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": top["bytes_per_cell"] * interior, "kernels": table,
+                    "kernel_ms_per_step": round(ksum / a.steps, 3),
+                    "note": "slab of %d rows per rank: sum of kernel times vs ms_per_step shows what launch gaps and "
+                            "collectives cost at this size" % (nloc - 2)}
+    s.close()
+    # ---- e2e: the drop-in symbol with a pinned host flow_field (u, v, w, p, T both ways), rank 0 drives all GPUs
+    e2e = None
+    if not a.no_e2e:
+        store = None
+        if td is not None:
+            td.barrier()
+            store = td.distributed_c10d._get_default_store()
+        if rank == 0:
+            try:
+                keep = []
+
+                def alloc(m):
+                    import ctypes as C
+                    ptr = L.cfd_b200_host_alloc(m * 8)
+                    keep.append(ptr)
+                    return np.frombuffer((C.c_double * m).from_address(ptr), dtype=np.float64)
+
+                g = abi.HostGrid(n, n, 1, 0.0, 1.0, 0.0, 1.0)
+                fh = c4_host_field(n, alloc=alloc)
+                api.set_poisson(pc)
+                api.set_device_count(world)
+                steps = max(2, min(a.steps, 5))
+                rc = api.solve_method_gpu("projection", fh, g, prm)
+                assert rc == 0, lib.last_error()
+                t0 = time.perf_counter()
+                for _ in range(steps):
+                    rc = api.solve_method_gpu("projection", fh, g, prm)
+                    assert rc == 0, lib.last_error()
+                dt = time.perf_counter() - t0
+                e2e = {"value": n * n * steps / dt / 1e6, "unit": UNIT, "h2d_bytes_per_step": 5 * 8 * n * n,
+                       "d2h_bytes_per_step": 5 * 8 * n * n, "steps": steps, "ms_per_step": dt / steps * 1e3,
+                       "api": "solve_projection_method_gpu (C-ABI drop-in), pinned host flow_field, "
+                              "cfd_b200_set_device_count(%d)" % world}
+                api.set_device_count(0)
+                L.cfd_b200_release_cached_sessions()
+                for ptr in keep:
+                    L.cfd_b200_host_free(ptr)
+            finally:
+                if store is not None:
+                    store.set("cfd_b200_e2e_done", "1")
+        elif store is not None:
+            import datetime
+            store.wait(["cfd_b200_e2e_done"], datetime.timedelta(seconds=900))
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "C4 natural convection 2-D %d x %d (energy + buoyancy + thermal BCs), projection step + "
+                                       "%s x%d iterations (fixed), y-slab decomposition over %d GPU(s), FIXED global grid"
+                                       % (n, n, method, a.iters, world),
+                           "grid_global": [n, n, 1], "poisson": method, "poisson_iterations": a.iters, "dt": prm.dt,
+                           "parallelism": "yslab%d" % world, "transport": transport,
+                           "l2": "fields of %.0f MB per rank against 126 MB of L2: %s" %
+                                 (8 * n * nloc / 1e6, "larger than L2" if 8 * n * nloc * 9 > 126e6 else "cache resident")},
+                "roofline": roofline, "cpu_baseline": None, "e2e": e2e, "gpu_launches": launches, "clocks": clk.summary()}
+        if parity is not None:
+            line["parity"] = parity
+        real_out.write(json.dumps(line) + "\n")
+    if td is not None:
+        td.barrier()
+        td.destroy_process_group()
+    return 0
 
 
 # ------------------------------------------------------------------------------------------
@@ -518,6 +722,8 @@ def _main(a, real_out):
         os.environ.setdefault("OMP_PROC_BIND", "close")
         os.environ.setdefault("OMP_PLACES", "cores")
         return reference_main(a, real_out)
+    if a.config == "c4":
+        return c4_main(a, real_out)
     r = ours_main(a)
     e2e = None
     if not a.no_e2e:

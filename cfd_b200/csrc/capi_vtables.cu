@@ -9,6 +9,8 @@
 #include <stdlib.h>
 #include <string.h>
 #include <sys/time.h>
+#include <thread>
+#include <vector>
 
 using namespace cfdb;
 
@@ -98,6 +100,28 @@ struct NsCtx {
 };
 constexpr unsigned NS_MAGIC = 0xCFDB2001u;
 
+// compute_max_temperature (solver_registry.c:52-62) over the caller's array; a few threads for big fields
+// (1024^3 doubles take ~1 s on one core -- as long as the projection step itself)
+double host_max(const double* a, size_t n) {
+    unsigned hc = std::thread::hardware_concurrency();
+    size_t nt = n < (1u << 22) ? 1 : (hc >= 32 ? 16 : (hc >= 4 ? hc / 2 : 1));
+    std::vector<double> part(nt, a[0]);
+    auto work = [&](size_t t) {
+        double m = a[0];
+        for (size_t q = n * t / nt, e = n * (t + 1) / nt; q < e; q++)
+            if (a[q] > m) m = a[q];
+        part[t] = m;
+    };
+    std::vector<std::thread> th;
+    for (size_t t = 1; t < nt; t++) th.emplace_back(work, t);
+    work(0);
+    for (std::thread& x : th) x.join();
+    double m = part[0];
+    for (size_t t = 1; t < nt; t++)
+        if (part[t] > m) m = part[t];
+    return m;
+}
+
 cfd_status_t ns_ensure(ns_solver_t* slv, const flow_field* f, const grid* g) {
     NsCtx* c = (NsCtx*)slv->context;
     int want = configured_device_count();
@@ -123,12 +147,8 @@ cfd_status_t ns_run(ns_solver_t* slv, flow_field* f, const grid* g, const ns_sol
     const bool thermo = (prm->alpha > 0.0 || prm->beta != 0.0);
     rc = runner_run(c->r, (StepKind)c->kind, f, g, prm, nsteps, stats, c->sync);
     if (c->kind == SK_PROJECTION) {
-        if (stats && rc == CFD_SUCCESS && !thermo) {  // T never went to the device: max over the host copy
-            double mt = f->T[0];
-            const size_t N = f->nx * f->ny * f->nz;
-            for (size_t n = 1; n < N; n++) if (f->T[n] > mt) mt = f->T[n];
-            stats->max_temperature = mt;
-        }
+        if (stats && rc == CFD_SUCCESS && !thermo)  // T never went to the device: max over the host copy
+            stats->max_temperature = host_max(f->T, f->nx * f->ny * f->nz);
     } else if ((rc == CFD_SUCCESS || rc == CFD_ERROR_DIVERGED) && nsteps > 0 && !c->r->host_stale) {
         wrap_host_rho(f);
     }

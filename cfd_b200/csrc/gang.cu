@@ -277,6 +277,7 @@ cfd_status_t runner_run(Runner* r, StepKind kind, flow_field* f, const grid* g, 
         return CFD_SUCCESS;
     };
     const int umask = upload_mask(kind, prm);
+    const cfd_b200_poisson_config_t pc = cfd_b200_get_poisson_config();
     // ---- host -> device: whole slabs, or (caller's promise: only boundary cells edited since the last call's
     //      result) the boundary faces; nothing at all while the host copy is the stale one (DOWNLOAD_LAZY)
     const bool state_kept = r->resident && (r->resident_mask & umask) == umask;
@@ -285,9 +286,14 @@ cfd_status_t runner_run(Runner* r, StepKind kind, flow_field* f, const grid* g, 
     parallel(G, [&](int q) {
         cfd_b200_session* s = r->s[q];
         session_set_coords(s, g->x, d3 ? g->y : g->y + r->lo[q]);
-        if (skip_upload) return;
+        if (skip_upload) {
+            if (G > 1 && (rc[q] = prepare_buffers(s, (int)kind, prm, &pc)) != CFD_SUCCESS) err[q] = last_error();
+            return;
+        }
         const flow_field v = slab_view(r, q, f);
         rc[q] = faces_only ? upload_faces(r, q, &v, umask) : session_upload(s, &v, umask);
+        // all allocations of the run now, before any slab can be waiting for another inside a kernel
+        if (rc[q] == CFD_SUCCESS && G > 1) rc[q] = prepare_buffers(s, (int)kind, prm, &pc);
         if (rc[q] != CFD_SUCCESS) err[q] = last_error();
     });
     cudaSetDevice(cur);
@@ -295,16 +301,24 @@ cfd_status_t runner_run(Runner* r, StepKind kind, flow_field* f, const grid* g, 
     cfd_status_t st = first_failure();
     if (st != CFD_SUCCESS) return st;
     // ---- step: one host thread per GPU runs the per-slab driver
-    const cfd_b200_poisson_config_t pc = cfd_b200_get_poisson_config();
     std::vector<ns_solver_stats_t> rs(G);
     parallel(G, [&](int q) {
         cfd_b200_session* s = r->s[q];
+        if (getenv("CFD_B200_PROFILE_GANG")) s->prof.on = true;
         ns_solver_stats_t* ps = stats ? &rs[q] : nullptr;
         if (ps) *ps = *stats;
         rc[q] = (kind == SK_PROJECTION) ? run_projection(s, prm, &pc, nsteps, ps) : run_rk(s, (int)kind, prm, nsteps, ps);
         if (rc[q] != CFD_SUCCESS) err[q] = last_error();
     });
     cudaSetDevice(cur);
+    if (getenv("CFD_B200_PROFILE_GANG")) {  // debugging aid: per-kernel event times of every slab
+        for (int q = 0; q < G; q++) {
+            cfd_b200_kernel_stat_t ks[CFD_B200_MAX_KERNEL_KINDS];
+            const int nk = cfd_b200_session_kernel_stats(r->s[q], ks, CFD_B200_MAX_KERNEL_KINDS);
+            for (int k = 0; k < nk; k++)
+                fprintf(stderr, "[gang] rank %d %-24s x%-4llu %10.3f ms\n", q, ks[k].name, ks[k].launches, ks[k].total_ms);
+        }
+    }
     if (stats) *stats = rs[0];  // maxima are all-reduced: identical on every rank
     st = first_failure();
     const bool usable = st == CFD_SUCCESS || st == CFD_ERROR_DIVERGED || (kind == SK_PROJECTION && st == CFD_ERROR_MAX_ITER);

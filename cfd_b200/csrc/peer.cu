@@ -36,12 +36,14 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ bool wait_flag(const unsigned long long* p, unsigned long long want, int* timeout_flag) {
+// (timeout_flag[0] = which wait gave up first: 1 halo lo, 2 halo hi, 16 + r reduction from rank r; [1] = its sequence number)
+__device__ __forceinline__ bool wait_flag(const unsigned long long* p, unsigned long long want, int* timeout_flag,
+                                          int code) {
     if (*(volatile int*)timeout_flag) return false;  // an earlier wait of this step already gave up
     const long long t0 = clock64();
     while (ld_acquire_sys(p) < want) {
         if (clock64() - t0 > SPIN_LIMIT_CYCLES) {
-            *timeout_flag = 1;
+            if (atomicCAS(timeout_flag, 0, code) == 0) timeout_flag[1] = (int)want;
             return false;
         }
         __nanosleep(64);
@@ -110,8 +112,8 @@ __global__ void __launch_bounds__(256) k_halo_pull(PullArgs a) {
     __shared__ int ok;
     if (threadIdx.x == 0) {
         bool good = true;
-        if (a.lo_box) good = wait_flag(a.lo_flag, a.seq, a.timeout_flag) && good;
-        if (a.hi_box) good = wait_flag(a.hi_flag, a.seq, a.timeout_flag) && good;
+        if (a.lo_box) good = wait_flag(a.lo_flag, a.seq, a.timeout_flag, 1) && good;
+        if (a.hi_box) good = wait_flag(a.hi_flag, a.seq, a.timeout_flag, 2) && good;
         ok = good;
     }
     __syncthreads();
@@ -163,7 +165,7 @@ __global__ void __launch_bounds__(32) k_allreduce_peer(ReduceArgs a) {
         st_release_sys(&h->rflag[a.r][buf], a.seq);
     }
     PeerBoxHeader* me = reinterpret_cast<PeerBoxHeader*>(a.box[a.r]);
-    if (t < a.R && !wait_flag(&me->rflag[t][buf], a.seq, a.timeout_flag)) ok = 0;
+    if (t < a.R && !wait_flag(&me->rflag[t][buf], a.seq, a.timeout_flag, 16 + t)) ok = 0;
     __syncwarp();
     if (!ok) return;
     if (t < a.n) {
@@ -177,6 +179,21 @@ __global__ void __launch_bounds__(32) k_allreduce_peer(ReduceArgs a) {
         if (a.op == 2) ((int*)a.vals)[t] = (int)acc;
         else ((double*)a.vals)[t] = acc;
     }
+}
+
+// The waiting kernels ask for the same shared-memory carveout as the TMA stencil kernels (maximum shared memory):
+// with several slabs on ONE GPU (virtual ranks) a stencil kernel of one slab must be able to start on an SM while
+// another slab's waiting kernel is resident elsewhere; measured on B200: with the default carveout the stencil
+// kernel is held back until the waiting kernel exits (SM carveout reconfiguration), i.e. until its time-out.
+void peer_kernel_setup() {
+    static const bool once = [] {
+        cudaFuncSetAttribute(k_halo_push, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(k_halo_pull, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(k_allreduce_peer, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaGetLastError();
+        return true;
+    }();
+    (void)once;
 }
 
 size_t mailbox_offset(const Peer& p, int side, int buf) {
@@ -193,6 +210,7 @@ cfd_status_t peer_alloc_box(cfd_b200_session* s) {
         return CFD_ERROR_UNSUPPORTED;
     }
     CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    peer_kernel_setup();
     p.cnt = s->g.dim3 ? (size_t)s->g.nx * s->g.ny : (size_t)s->g.nx;
     p.box_bytes = sizeof(PeerBoxHeader) + 4 * PEER_MAX_FIELDS * p.cnt * sizeof(double);
     if (cudaMalloc((void**)&p.box, p.box_bytes) != cudaSuccess) {
@@ -290,6 +308,8 @@ cfd_status_t peer_allreduce(cfd_b200_session* s, void* dev, int n, int op) {
     a.n = n;
     a.op = op;
     CFDB_LAUNCH(KK_ALLREDUCE, s->st, k_allreduce_peer<<<1, 32, 0, s->st>>>(a));
+    static const bool hostsync = getenv("CFD_B200_PEER_HOSTSYNC") != nullptr;  // debugging aid
+    if (hostsync) cudaStreamSynchronize(s->st);
     return CFD_SUCCESS;
 }
 

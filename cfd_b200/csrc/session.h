@@ -148,5 +148,7 @@ cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
                             const cfd_b200_poisson_config_t* pc, int nsteps, ns_solver_stats_t* stats);
 cfd_status_t run_rk(cfd_b200_session* s, int order, const ns_solver_params_t* prm, int nsteps,
                     ns_solver_stats_t* stats);
+cfd_status_t prepare_buffers(cfd_b200_session* s, int kind, const ns_solver_params_t* prm,
+                             const cfd_b200_poisson_config_t* pc);
 cfd_status_t validate_common(const flow_field* f, const grid* g, const ns_solver_params_t* prm);
 }  // namespace cfdb

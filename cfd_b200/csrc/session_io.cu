@@ -168,7 +168,17 @@ cfd_status_t comm_check(cfd_b200_session* s) {
     if (rc == CFD_SUCCESS && s->peer.on && s->h_ctl[0].comm_timeout) {
         set_error(CFD_ERROR, "peer transport: rank %d waited too long for a neighbour (lost rank or mismatched call sequence)",
                   s->desc.rank);
-        cudaMemsetAsync(&s->ctl->comm_timeout, 0, sizeof(int), s->st);
+        cudaMemsetAsync(&s->ctl->comm_timeout, 0, 2 * sizeof(int), s->st);
+        if (getenv("CFD_B200_PEER_DEBUG")) {  // which exchange / reduction never arrived
+            PeerBoxHeader h;
+            cudaMemcpy(&h, s->peer.box, sizeof(h), cudaMemcpyDeviceToHost);
+            fprintf(stderr, "[peer] first wait that gave up: code %d seq %d; ", s->h_ctl[0].comm_timeout, s->h_ctl[0].pad[0]);
+            fprintf(stderr, "[peer] rank %d/%d issued halo #%llu reduce #%llu; box: halo flags lo{%llu,%llu} hi{%llu,%llu}; reduce flags",
+                    s->desc.rank, s->desc.nranks, s->peer.hseq, s->peer.rseq, h.hflag[0][0], h.hflag[0][1], h.hflag[1][0],
+                    h.hflag[1][1]);
+            for (int q = 0; q < s->desc.nranks; q++) fprintf(stderr, " r%d{%llu,%llu}", q, h.rflag[q][0], h.rflag[q][1]);
+            fprintf(stderr, "\n");
+        }
         rc = CFD_ERROR;
     }
     return rc;

@@ -84,6 +84,34 @@ static void fill_stats(cfd_b200_session* s, ns_solver_stats_t* stats, int iters)
     stats->max_temperature = s->h_ctl[0].stat[2];
 }
 
+// Every device allocation a run of `kind` will need, made up front.  The drivers below allocate lazily as well
+// (stand-alone session use), but a gang must not allocate while slabs already wait for each other inside kernels:
+// cudaMalloc may synchronise the device, and with several slabs on one GPU (virtual ranks) the allocating thread
+// would then wait for a kernel that waits for that very thread's next launch.
+cfd_status_t prepare_buffers(cfd_b200_session* s, int kind, const ns_solver_params_t* prm,
+                             const cfd_b200_poisson_config_t* pc) {
+    CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    cfd_status_t rc = CFD_SUCCESS;
+    const bool energy = prm->alpha > 0.0, thermo = energy || prm->beta != 0.0;
+    std::vector<double**> need;
+    if (kind == 0) {
+        need = {&s->us, &s->vs, &s->ws, &s->pn, &s->rhs};
+        if (pc->method == POISSON_METHOD_JACOBI || pc->method == POISSON_METHOD_REDBLACK_SOR) need.push_back(&s->xt);
+        const int nk = pc->method == POISSON_METHOD_CG ? 4 : (pc->method == POISSON_METHOD_BICGSTAB ? 8 : 0);
+        for (int q = 0; q < nk; q++) need.push_back(&s->kv[q]);
+    } else {
+        const int nbuf = kind == 1 ? 4 : (kind == 4 ? 12 : 8);
+        for (int q = 0; q < nbuf; q++) need.push_back(&s->rk[q]);
+    }
+    if (thermo) need.push_back(&s->T);
+    if (energy) need.push_back(&s->Tn);
+    for (double** q : need)
+        if ((rc = dalloc(s, q)) != CFD_SUCCESS) return rc;
+    if ((rc = ensure_tables(s, prm)) != CFD_SUCCESS) return rc;
+    CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
+    return CFD_SUCCESS;
+}
+
 cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
                             const cfd_b200_poisson_config_t* pc, int nsteps, ns_solver_stats_t* stats) {
     if (!s || !prm || !pc) return CFD_ERROR_INVALID;

@@ -3,6 +3,14 @@ import sys
 
 import pytest
 
+# Virtual ranks (CFD_B200_VIRTUAL_RANKS=1: several slabs of a gang on ONE GPU, tests/test_gpu_runner.py) wait for each
+# other inside kernels; two of their streams must never share a hardware work queue, or the waiting kernel blocks
+# the one it waits for.  Must be set before the CUDA context exists.  (One rank per GPU needs nothing of the kind.)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+# ... and no kernel may be lazily LOADED while another rank's kernel on the same GPU waits for it: loading a
+# kernel on first launch can synchronise the context (CUDA programming guide, "Lazy Loading: concurrent execution").
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -22,7 +22,7 @@ for stage in "$@"; do
   arg=${stage#*:}; [ "$arg" = "$stage" ] && arg=""
   case ${stage%%:*} in
     tests)
-      if [ -n "$arg" ]; then timeout 1500 python -m pytest tests -m gpu -q -x -k "$arg" > ${O}_pytest.log 2>&1
+      if [ -n "$arg" ]; then timeout 1500 python -m pytest tests -m gpu -q -k "$arg" > ${O}_pytest.log 2>&1
       else timeout 1500 python -m pytest tests -m gpu -q > ${O}_pytest.log 2>&1; fi
       echo "pytest exit $?" >> ${O}_pytest.log; tail -15 ${O}_pytest.log | cut -c1-400 ;;
     smoke)
@@ -49,6 +49,10 @@ for stage in "$@"; do
       run --shape 4096,4096,1 --stepper projection --method rbsor --iters 50
       run --shape 129,129,1 --stepper projection --method jacobi --iters 50
       run --shape 1024,1024,1024 --stepper projection --method rbsor --iters 20 --steps 1
+      for st in "--stepper rk4" "--stepper euler" "--stepper rk2" "--stepper projection --method jacobi --iters 50" \
+                "--stepper projection --method rbsor --iters 50" "--stepper projection --method cg --iters 50 --energy"; do
+        run --shape 512,512,512 $st --fast; done
+      run --shape 128,128,128 --stepper rk4 --steps 20 --fast; run --shape 128,128,128 --stepper rk4 --steps 200 --no-profile
       wc -l $out ;;
     launches)
       timeout 600 python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu > ${O}_launch_bench.json 2>/dev/null &&

@@ -25,10 +25,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--rhs", default="random", choices=["random", "smooth"], help="--stepper poisson: right-hand side")
     ap.add_argument("--energy", action="store_true", help="alpha > 0, beta != 0 (natural-convection kernels)")
+    ap.add_argument("--fast", action="store_true", help="the fast arithmetic build (cfd_b200_set_arithmetic(1))")
+    ap.add_argument("--no-profile", action="store_true", help="no per-launch events: whole-step time only")
     a = ap.parse_args()
     import torch
     from cfd_b200 import abi, api, lib
     nx, ny, nz = (int(v) for v in a.shape.split(","))
+    api.set_arithmetic(1 if a.fast else 0)
     hx, hy, hz = 1.0 / (nx - 1), 1.0 / (ny - 1), (1.0 / (nz - 1) if nz > 1 else 0.0)
     s = api.Session(nx, ny, nz, hx, hy, hz)
     s.init_synthetic(12345, 0, nz)
@@ -70,7 +73,7 @@ def main():
 
     run(a.warmup)
     s.reset_kernel_stats()
-    s.profile(True)
+    s.profile(not a.no_profile)
     st = torch.cuda.ExternalStream(s.stream())
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
@@ -94,7 +97,7 @@ def main():
         gbs = k["bytes_per_cell"] * interior / (avg * 1e-3) / 1e9
         rows.append({"kernel": k["name"], "launches": k["launches"], "avg_us": round(avg * 1e3, 2),
                      "bytes_per_cell": k["bytes_per_cell"], "GBps": round(gbs, 1), "frac_of_measured_peak": round(gbs / peak, 4)})
-    out = {"shape": [nx, ny, nz], "stepper": a.stepper, "method": a.method, "iters": a.iters, "steps": a.steps,
+    out = {"shape": [nx, ny, nz], "arithmetic": "fast" if a.fast else "exact", "stepper": a.stepper, "method": a.method, "iters": a.iters, "steps": a.steps,
            "ms_per_step": ms / a.steps, "MLUPS": nx * ny * nz * a.steps / (ms * 1e-3) / 1e6,
            "field_MB": 8 * nx * ny * nz / 1e6, "cache_resident": 8 * nx * ny * nz * 6 < 126e6, "kernels": rows}
     print(json.dumps(out))
