@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_build")
 LIB = os.path.join(HERE, "libcfd_b200.so")
 SOURCES = ["poisson_kernels.cu", "poisson_mini.cu", "poisson_mg.cu", "ns_kernels.cu", "ns_kernels2.cu", "session.cu", "session_io.cu", "xfer.cu", "tma_host.cu",
-           "poisson_driver.cu", "step_driver.cu", "capi.cu", "capi_vtables.cu", "bc_api.cu", "gang.cu", "host_sync.cu", "peer.cu"]
+           "poisson_driver.cu", "step_driver.cu", "capi.cu", "capi_vtables.cu", "bc_api.cu", "gang.cu", "host_sync.cu", "peer.cu", "no_alloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-fmad=false", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC,-fvisibility=hidden", "-Xptxas", "-v"]

@@ -100,6 +100,9 @@ def load():
     proto("cfd_b200_session_peer_export", i32, [vp, C.c_char_p])
     proto("cfd_b200_session_peer_attach", i32, [vp, C.c_char_p])
     proto("cfd_b200_session_transport", i32, [vp])
+    proto("cfd_b200_noalloc_max_cells", C.c_size_t, [])
+    proto("cfd_b200_poisson_residual_linf_noalloc", i32, [vp, vp, C.c_size_t, C.c_size_t, C.c_size_t, dbl, dbl, dbl,
+                                                          vp, vp])
     proto("cfd_b200_set_arithmetic", i32, [i32])
     proto("cfd_b200_session_arithmetic", i32, [vp])
     proto("cfd_b200_set_device_count", i32, [i32])
@@ -136,6 +139,7 @@ DECLARED_SYMBOLS = [
     "cfd_b200_session_reset_kernel_stats", "cfd_b200_session_stream", "cfd_b200_session_sync",
     "cfd_b200_set_device_count", "cfd_b200_get_device_count", "cfd_b200_session_set_slab",
     "cfd_b200_release_cached_sessions", "cfd_b200_solver_set_host_sync", "cfd_b200_solver_sync_host",
+    "cfd_b200_noalloc_max_cells", "cfd_b200_poisson_residual_linf_noalloc",
     "cfd_b200_set_arithmetic", "cfd_b200_session_arithmetic", "cfd_b200_session_peer_export", "cfd_b200_session_peer_attach", "cfd_b200_session_transport",
 ]
 

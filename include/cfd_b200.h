@@ -602,6 +602,24 @@ typedef enum {
 CFD_B200_API cfd_status_t cfd_b200_solver_set_host_sync(ns_solver_t* solver, int flags);
 CFD_B200_API cfd_status_t cfd_b200_solver_sync_host(ns_solver_t* solver, flow_field* field);
 
+/* ---- An entry point that allocates nothing (csrc/no_alloc.cu) ----
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * L-infinity residual max |lap x - rhs| over the interior cells of a uniform grid -- the quantity of the reference's
+ * poisson_solver_compute_residual (linear_solver.c:304-346), same expression and bits as the initial / final
+ * residual the stationary GPU solvers report.  d_x, d_rhs: DEVICE arrays of nx*ny*nz doubles in the reference layout
+ * (boundary cells included; nz == 1 for 2-D, dz ignored then); d_out: DEVICE pointer to one double, written when the
+ * work queued on `stream` has run (the call does not synchronise).  The per-block partial maxima go through a
+ * file-scope static device array of 524 544 bytes that every GPU loading the library holds until exit: grids of more
+ * than CFD_B200_NOALLOC_MAX_CELLS cells are rejected with CFD_ERROR_LIMIT_EXCEEDED (use a session for those).  The
+ * call makes no cudaMalloc / cudaFree and no allocating library call.  All calls on one GPU share the scratch:
+ * calls that OVERLAP on the GPU (different streams without ordering) race and may return garbage. */
+#define CFD_B200_NOALLOC_MAX_CELLS ((size_t)1 << 24) /* 16 777 216 cells: 256^3, 4096^2 */
+CFD_B200_API size_t cfd_b200_noalloc_max_cells(void);
+CFD_B200_API cfd_status_t cfd_b200_poisson_residual_linf_noalloc(const double* d_x, const double* d_rhs, size_t nx,
+                                                                 size_t ny, size_t nz, double dx, double dy, double dz,
+                                                                 double* d_out, cfd_b200_stream_t stream);
+
 /* ---- Measurement hooks (bench.py): per-kernel CUDA-event timing on the session stream ---- */
 #define CFD_B200_MAX_KERNEL_KINDS 48
 typedef struct {
