@@ -96,6 +96,21 @@ struct KArgs {
     } while (0)
 
 void set_error(cfd_status_t st, const char* fmt, ...);
+
+// Function attributes (dynamic shared-memory opt-in, carveout, cluster size) are PER DEVICE: a process that drives
+// several GPUs -- the in-process gang, or two solver objects on two devices -- must set them on each one.  Runs the
+// statements once per device ordinal (re-running them is harmless, so no lock: two threads may both do it).
+#define CFDB_ONCE_PER_DEVICE(...)                                                   \
+    do {                                                                            \
+        static std::atomic<unsigned long long> done_{0};                            \
+        int dev_ = 0;                                                               \
+        cudaGetDevice(&dev_);                                                       \
+        const unsigned long long bit_ = 1ull << (dev_ & 63);                        \
+        if (!(done_.load(std::memory_order_acquire) & bit_)) {                      \
+            __VA_ARGS__;                                                            \
+            done_.fetch_or(bit_, std::memory_order_release);                        \
+        }                                                                           \
+    } while (0)
 extern std::atomic<unsigned long long> g_launches;  // kernels launched by this library (any thread)
 
 // ---------------------------------------------------------------------------------------

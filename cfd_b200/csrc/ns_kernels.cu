@@ -275,8 +275,7 @@ void launch_predictor(const LaunchCtx& L, const NsConst& c, const double* u, con
         const double* const ops[3] = {u, v, w};
         if (tma_maps2(L, ops, tm)) {
             constexpr size_t SM = DirectPipe<3>::SMEM;
-            static bool once = (tma_optin(k_predictor_tma<true>, SM), tma_optin(k_predictor_tma<false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_predictor_tma<true>, SM), tma_optin(k_predictor_tma<false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_PREDICTOR, L.st, (k_predictor_tma<true><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, T, su_tab, sv_tab, us, vs, ws)));
             else CFDB_LAUNCH(KK_PREDICTOR, L.st, (k_predictor_tma<false><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, T, su_tab, sv_tab, us, vs, ws)));
             CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_carry3<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, us, vs, ws)));
@@ -300,8 +299,7 @@ void launch_divergence(const LaunchCtx& L, const NsConst& c, const double* us, c
         const double* const ops[3] = {us, vs, ws};
         if (tma_maps2(L, ops, tm)) {
             constexpr size_t SM = DirectPipe<3>::SMEM;
-            static bool once = (tma_optin(k_divergence_tma<true>, SM), tma_optin(k_divergence_tma<false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_divergence_tma<true>, SM), tma_optin(k_divergence_tma<false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_DIVERGENCE, L.st, (k_divergence_tma<true><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, rhs)));
             else CFDB_LAUNCH(KK_DIVERGENCE, L.st, (k_divergence_tma<false><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, rhs)));
             return;
@@ -319,8 +317,7 @@ void launch_corrector(const LaunchCtx& L, const NsConst& c, const double* us, co
         const double* const ops[2] = {p, T};
         if (tma_maps2(L, ops, tm)) {
             constexpr size_t SM = DirectPipe<2>::SMEM;
-            static bool once = (tma_optin(k_corrector_tma<true, true>, SM), tma_optin(k_corrector_tma<false, true>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_corrector_tma<true, true>, SM), tma_optin(k_corrector_tma<false, true>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_corrector_tma<true, true><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, us, vs, ws, u, v, w, Tn, L.ctl)));
             else CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_corrector_tma<false, true><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, us, vs, ws, u, v, w, Tn, L.ctl)));
             CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_scan<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, p, T, Tn, L.ctl)));
@@ -331,8 +328,7 @@ void launch_corrector(const LaunchCtx& L, const NsConst& c, const double* us, co
         const double* const ops[1] = {p};
         if (tma_maps2(L, ops, tm)) {
             constexpr size_t SM = DirectPipe<1>::SMEM;
-            static bool once = (tma_optin(k_corrector_tma<true, false>, SM), tma_optin(k_corrector_tma<false, false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_corrector_tma<true, false>, SM), tma_optin(k_corrector_tma<false, false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_corrector_tma<true, false><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, us, vs, ws, u, v, w, Tn, L.ctl)));
             else CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_corrector_tma<false, false><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, us, vs, ws, u, v, w, Tn, L.ctl)));
             CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_scan<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, p, nullptr, nullptr, L.ctl)));
@@ -354,8 +350,7 @@ void launch_energy(const LaunchCtx& L, const NsConst& c, const double* u, const 
         const double* const ops[1] = {T};
         if (tma_maps2(L, ops, tm)) {
             constexpr size_t SM = DirectPipe<1>::SMEM;
-            static bool once = (tma_optin(k_energy_tma<true>, SM), tma_optin(k_energy_tma<false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_energy_tma<true>, SM), tma_optin(k_energy_tma<false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_energy_tma<true><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, u, v, w, Tn, L.ctl)));
             else CFDB_LAUNCH(KK_CORRECTOR, L.st, (k_energy_tma<false><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, u, v, w, Tn, L.ctl)));
             // T carry-over and finiteness on boundary cells (u stands in for p: scanned twice, harmless)

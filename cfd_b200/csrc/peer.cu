@@ -186,14 +186,11 @@ __global__ void __launch_bounds__(32) k_allreduce_peer(ReduceArgs a) {
 // another slab's waiting kernel is resident elsewhere; measured on B200: with the default carveout the stencil
 // kernel is held back until the waiting kernel exits (SM carveout reconfiguration), i.e. until its time-out.
 void peer_kernel_setup() {
-    static const bool once = [] {
+    CFDB_ONCE_PER_DEVICE(
         cudaFuncSetAttribute(k_halo_push, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         cudaFuncSetAttribute(k_halo_pull, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         cudaFuncSetAttribute(k_allreduce_peer, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        cudaGetLastError();
-        return true;
-    }();
-    (void)once;
+        cudaGetLastError());
 }
 
 size_t mailbox_offset(const Peer& p, int side, int buf) {

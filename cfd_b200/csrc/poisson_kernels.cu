@@ -699,9 +699,8 @@ void launch_jacobi(const LaunchCtx& L, const KArgs& a0, const double* xin, doubl
             KArgs at = a0;
             at.zchunk = L.zchunk_tma;
             constexpr size_t SM = DirectPipe<1>::SMEM;
-            static bool once = (tma_optin(k_jacobi_tma<true, true>, SM), tma_optin(k_jacobi_tma<true, false>, SM),
-                                tma_optin(k_jacobi_tma<false, true>, SM), tma_optin(k_jacobi_tma<false, false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_jacobi_tma<true, true>, SM), tma_optin(k_jacobi_tma<true, false>, SM),
+                                tma_optin(k_jacobi_tma<false, true>, SM), tma_optin(k_jacobi_tma<false, false>, SM));
 #define CFDB_JACT(D3, RES) CFDB_LAUNCH(KK_JACOBI, L.st, (k_jacobi_tma<D3, RES><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, xout, rhs, L.ctl, L.rb, at)))
             if (L.g.dim3) { if (res) CFDB_JACT(true, true); else CFDB_JACT(true, false); }
             else { if (res) CFDB_JACT(false, true); else CFDB_JACT(false, false); }
@@ -745,8 +744,7 @@ bool launch_rbsor_fused(const LaunchCtx& L, const KArgs& a0, const double* xin, 
     if ((size_t)grid.x * grid.y * grid.z > L.rb_blocks) return false;
     const bool res = (at.it == 0) || ((at.it - 1) % at.check == 0);
     constexpr size_t SM = RbFused::SMEM;
-    static bool once = (tma_optin(k_rbsor_fused_tma<true>, SM), tma_optin(k_rbsor_fused_tma<false>, SM), true);
-    (void)once;
+    CFDB_ONCE_PER_DEVICE(tma_optin(k_rbsor_fused_tma<true>, SM), tma_optin(k_rbsor_fused_tma<false>, SM));
     if (res) CFDB_LAUNCH(KK_RBSOR_FUSED, L.st, (k_rbsor_fused_tma<true><<<grid, RbFused::THREADS, SM, L.st>>>(tm, L.g, xout, L.ctl, L.rb, at)));
     else CFDB_LAUNCH(KK_RBSOR_FUSED, L.st, (k_rbsor_fused_tma<false><<<grid, RbFused::THREADS, SM, L.st>>>(tm, L.g, xout, L.ctl, L.rb, at)));
     return true;
@@ -760,8 +758,7 @@ void launch_redblack(const LaunchCtx& L, const KArgs& a0, double* x, const doubl
             KArgs at = a0;
             at.zchunk = L.zchunk_tma;
             constexpr size_t SM = DirectPipe<1>::SMEM;
-            static bool once = (tma_optin(k_redblack_tma<true>, SM), tma_optin(k_redblack_tma<false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_redblack_tma<true>, SM), tma_optin(k_redblack_tma<false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_REDBLACK, L.st, (k_redblack_tma<true><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, x, rhs, L.ctl, at, colour, decide)));
             else CFDB_LAUNCH(KK_REDBLACK, L.st, (k_redblack_tma<false><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, x, rhs, L.ctl, at, colour, decide)));
             return;
@@ -779,8 +776,7 @@ void launch_linf_residual(const LaunchCtx& L, const KArgs& a0, const double* x, 
             KArgs at = a0;
             at.zchunk = L.zchunk_tma;
             constexpr size_t SM = DirectPipe<1>::SMEM;
-            static bool once = (tma_optin(k_linf_residual_tma<true>, SM), tma_optin(k_linf_residual_tma<false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_linf_residual_tma<true>, SM), tma_optin(k_linf_residual_tma<false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_LINF, L.st, (k_linf_residual_tma<true><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, rhs, L.ctl, L.rb, at, slot)));
             else CFDB_LAUNCH(KK_LINF, L.st, (k_linf_residual_tma<false><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, rhs, L.ctl, L.rb, at, slot)));
             return;
@@ -802,8 +798,7 @@ void launch_krylov_init(const LaunchCtx& L, const KArgs& a0, const double* x, co
             KArgs at = a0;
             at.zchunk = L.zchunk_tma;
             constexpr size_t SM = DirectPipe<1>::SMEM;
-            static bool once = (tma_optin(k_krylov_init_tma<true>, SM), tma_optin(k_krylov_init_tma<false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_krylov_init_tma<true>, SM), tma_optin(k_krylov_init_tma<false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, (k_krylov_init_tma<true><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, rhs, r, p0, rhat, L.ctl, L.rb, at, precond)));
             else CFDB_LAUNCH(KK_KRYLOV_INIT, L.st, (k_krylov_init_tma<false><<<tma_grid(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, rhs, r, p0, rhat, L.ctl, L.rb, at, precond)));
             return;
@@ -822,8 +817,7 @@ void launch_cg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const d
             KArgs a = a0;
             a.zchunk = L.zchunk_tma;
             constexpr size_t SM = TmaPipe<2>::SMEM;
-            static bool once = (tma_optin(k_cg_dir_tma<true>, SM), tma_optin(k_cg_dir_tma<false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_cg_dir_tma<true>, SM), tma_optin(k_cg_dir_tma<false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_CG_DIR, L.st, (k_cg_dir_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, pnew, Ap, L.ctl, L.rb, a, precond)));
             else CFDB_LAUNCH(KK_CG_DIR, L.st, (k_cg_dir_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, pnew, Ap, L.ctl, L.rb, a, precond)));
             return;
@@ -855,8 +849,7 @@ void launch_bicg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const
             KArgs a = a0;
             a.zchunk = L.zchunk_tma;
             constexpr size_t SM = TmaPipe<3>::SMEM;
-            static bool once = (tma_optin(k_bicg_dir_tma<true>, SM), tma_optin(k_bicg_dir_tma<false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_bicg_dir_tma<true>, SM), tma_optin(k_bicg_dir_tma<false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_BICG_DIR, L.st, (k_bicg_dir_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhat, pnew, vnew, L.ctl, L.rb, a)));
             else CFDB_LAUNCH(KK_BICG_DIR, L.st, (k_bicg_dir_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, rhat, pnew, vnew, L.ctl, L.rb, a)));
             return;
@@ -875,8 +868,7 @@ void launch_bicg_s(const LaunchCtx& L, const KArgs& a0, const double* r, const d
             KArgs a = a0;
             a.zchunk = L.zchunk_tma;
             constexpr size_t SM = TmaPipe<2>::SMEM;
-            static bool once = (tma_optin(k_bicg_s_tma<true>, SM), tma_optin(k_bicg_s_tma<false>, SM), true);
-            (void)once;
+            CFDB_ONCE_PER_DEVICE(tma_optin(k_bicg_s_tma<true>, SM), tma_optin(k_bicg_s_tma<false>, SM));
             if (L.g.dim3) CFDB_LAUNCH(KK_BICG_S, L.st, (k_bicg_s_tma<true><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, s, t, L.ctl, L.rb, a)));
             else CFDB_LAUNCH(KK_BICG_S, L.st, (k_bicg_s_tma<false><<<tma_grid(L), Tile::THREADS, SM, L.st>>>(tm, L.g, s, t, L.ctl, L.rb, a)));
             return;

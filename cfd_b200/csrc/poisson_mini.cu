@@ -630,9 +630,8 @@ bool cg_cluster_available(const LaunchCtx& L) {
 bool launch_cg_cluster(const LaunchCtx& L, const KArgs& a, double* x, const double* rhs, int precond) {
     MiniPlan p;
     if (!mini_plan(L.g, p, true)) return false;
-    static bool optin = (cudaFuncSetAttribute(k_cg_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)MINI_MAX_SMEM) == cudaSuccess);
-    if (!optin) { cudaGetLastError(); return false; }
+    CFDB_ONCE_PER_DEVICE(cudaFuncSetAttribute(k_cg_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MINI_MAX_SMEM));
+    if (cudaGetLastError() != cudaSuccess) return false;
     return launch_cluster(L, p, KK_CG_CLUSTER, k_cg_cluster, L.g, x, rhs, L.ctl, a, p.rows_per, precond);
 }
 
@@ -645,15 +644,13 @@ bool jacobi_cluster_available(const LaunchCtx& L) {
 // Whole solve in one launch; x is updated in place.  false => not launched (use the per-sweep kernels).
 template <int CPT>
 static bool launch_jacobi_cluster_cpt(const LaunchCtx& L, MiniPlan p, const KArgs& a, double* x, const double* rhs) {
-    static bool optin = (cudaFuncSetAttribute(k_jacobi_cluster<CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)MINI_MAX_SMEM) == cudaSuccess);
-    if (!optin) { cudaGetLastError(); return false; }
+    CFDB_ONCE_PER_DEVICE(cudaFuncSetAttribute(k_jacobi_cluster<CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MINI_MAX_SMEM));
+    if (cudaGetLastError() != cudaSuccess) return false;
     p.bx = MINI_THREADS;  // 1-D block: cells are dealt out by linear index
     p.by = 1;
     if (p.nc > 1 && !getenv("CFD_B200_CLUSTER_SYNC")) {  // neighbour-only signalling (default); _SYNC=1: cluster.sync() per sweep
-        static bool optin2 = (cudaFuncSetAttribute(k_jacobi_cluster_async<CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                   (int)MINI_MAX_SMEM) == cudaSuccess);
-        if (!optin2) { cudaGetLastError(); return false; }
+        CFDB_ONCE_PER_DEVICE(cudaFuncSetAttribute(k_jacobi_cluster_async<CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MINI_MAX_SMEM));
+        if (cudaGetLastError() != cudaSuccess) return false;
         return launch_cluster(L, p, KK_JACOBI_CLUSTER, k_jacobi_cluster_async<CPT>, L.g, x, rhs, L.ctl, a, p.rows_per);
     }
     return launch_cluster(L, p, KK_JACOBI_CLUSTER, k_jacobi_cluster<CPT>, L.g, x, rhs, L.ctl, a, p.rows_per);

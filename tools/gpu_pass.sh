@@ -35,9 +35,9 @@ for stage in "$@"; do
       timeout 900 bash -c "$(declare -f torchrun_); torchrun_ $arg tests/multigpu_parity.py" > ${O}_parity_${arg}gpu.log 2>&1
       echo "parity exit $?" >> ${O}_parity_${arg}gpu.log; grep -E "ok|FAIL|PARITY|exit|Error" ${O}_parity_${arg}gpu.log | tail -50 | cut -c1-200 ;;
     scale)
-      n=${arg%% *}; extra=${arg#$n}
-      timeout 1200 bash -c "$(declare -f torchrun_); torchrun_ $n bench.py --gpus $n $extra" > ${O}_bench_${n}gpu.json 2> ${O}_bench_${n}gpu.err
-      echo "scale exit $?"; cut -c1-500 ${O}_bench_${n}gpu.json; tail -3 ${O}_bench_${n}gpu.err | cut -c1-300 ;;
+      n=${arg%% *}; extra=${arg#$n}; tagx=$(echo "$extra" | grep -o "config [a-z0-9]*" | tr -d " ")
+      timeout 1200 bash -c "$(declare -f torchrun_); torchrun_ $n bench.py --gpus $n $extra" > ${O}_bench_${n}gpu${tagx}.json 2> ${O}_bench_${n}gpu${tagx}.err
+      echo "scale exit $?"; cut -c1-500 ${O}_bench_${n}gpu${tagx}.json; grep -v "^\[rank\|^ *File\|^W1\|^E1\|^\*\*\*\|Setting OMP" ${O}_bench_${n}gpu${tagx}.err | tail -4 | cut -c1-300 ;;
     tables)
       out=${O}_kernel_tables.jsonl; : > $out
       run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
