@@ -340,6 +340,7 @@ cfd_status_t gpu_solver_step(gpu_solver_context_t* c, const grid* g, const ns_so
         s->desc.dx = dx; s->desc.dy = dy; s->desc.dz = dz;
         s->desc.xmin = g->xmin; s->desc.ymin = g->ymin;
         set_spacing(s->g, dx, dy, dz);
+        mg_release(s);  // the levels' coefficients and the captured V-cycle graph were built from the old spacing
     }
     session_set_coords(s, g->x, g->y);
     const unsigned long long l0 = g_launches.load();

@@ -49,10 +49,33 @@ struct Geom {
     long long ncell;         // nx*ny*nz
 };
 
+// Peer-memory transport (peer.cu): every rank owns one "box" in its device memory that its neighbours write
+// into over NVLink (cudaDeviceEnablePeerAccess inside one process, cudaIpc handles across processes): halo
+// mailboxes, reduction slots and sequence flags.  No library call on the data path.
+constexpr int PEER_MAX_RANKS = 16;
+constexpr int PEER_MAX_FIELDS = 6;
+constexpr int PEER_RED_WORDS = 8;
+struct PeerBoxHeader {                       // lives at offset 0 of a box; flags are monotone sequence numbers
+    unsigned long long hflag[2][2];          // [side lo/hi][buffer]: halo planes of exchange #seq have landed
+    unsigned long long rflag[PEER_MAX_RANKS][2];  // [source rank][buffer]: its reduction payload #seq has landed
+    double rval[2][PEER_MAX_RANKS][PEER_RED_WORDS];
+    unsigned ticket;                         // last-block detection of the push kernel (self-resetting)
+    unsigned pad[15];
+    // ---- reductions finished INSIDE the producing kernel (block_reduce_finish): the block that completes the local
+    //      reduction publishes it to every box, waits for the others' and combines in rank order ----
+    unsigned long long fseq;                 // fused reductions this rank has issued (device-side counter)
+    unsigned long long fflag[PEER_MAX_RANKS][2];
+    double fval[2][PEER_MAX_RANKS][4];
+    char* boxes[PEER_MAX_RANKS];             // every rank's box as mapped on THIS device (filled at connect time)
+    int* timeout_flag;                       // &Ctl::comm_timeout of this rank
+    int R, r;
+};
+
 // One reduction "slot" : up to 4 simultaneous sums (or maxes) finished by the last block.
 struct RedBuf {
     double* partials;   // [max_blocks][4]
     unsigned* ticket;   // zero-initialised, self-resetting
+    PeerBoxHeader* peer;  // non-null: finish the reduction ACROSS ranks as well (all-reduce fused into the kernel)
 };
 
 // Device-resident control block of an iterative solve: kernels read/derive everything they
@@ -73,6 +96,22 @@ struct Ctl {
     double stat[4];       // max |vel|, max |p|, max T, spare (solver_registry.c:31-62)
 };
 
+// Halo exchange overlapped with interior compute (peer transport): the exchange's PULL half handed to the
+// first kernel that consumes the exchanged field.  The blocks whose chunk touches a halo layer wait for the neighbour's
+// sequence flag and copy their part of the mailbox layer into the field's halo layer before their first load; all
+// other blocks start at once, and the edge chunks are scheduled last (gate_chunk), so the neighbour's push and the
+// NVLink transfer run under the interior of the sweep.  Without a gate the exchange is push + pull kernels.
+struct HaloGate {
+    int on = 0;                                   // 0: nothing pending
+    int nf = 0;                                   // fields in this exchange (<= 2 on the Poisson path)
+    long long cnt = 0;                            // doubles per layer (a plane in 3-D, a row in 2-D)
+    unsigned long long seq = 0;                   // the exchange's sequence number
+    const double* box[2] = {nullptr, nullptr};    // my lo / hi mailbox of this exchange (null: no neighbour there)
+    const unsigned long long* flag[2] = {nullptr, nullptr};
+    double* halo[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [side][field]: where the mailbox layer belongs
+    int* timeout_flag = nullptr;
+};
+
 // Per-launch arguments of the Poisson kernels (everything the host knows at launch time).
 struct KArgs {
     int seq;              // launch sequence number inside this solve (monotone)
@@ -83,6 +122,7 @@ struct KArgs {
     double omega;         // SOR relaxation factor
     double dinv;          // Jacobi preconditioner 1/diag (linear_solver_cg.c:216)
     int zchunk;           // planes marched per block
+    HaloGate gate;        // pending pull of the operand's halo layers (this launch only)
 };
 
 #define CFDB_CUDA_OK(expr)                                                                  \
@@ -189,6 +229,32 @@ struct RhoDiv {
 #endif
 };
 
+// ---- cross-GPU flags (peer transport): system-scope release / acquire, bounded spinning ----
+constexpr long long SPIN_LIMIT_CYCLES = 8000000000LL;  // ~4 s at 2 GHz
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// (timeout_flag[0] = which wait gave up first: 1 halo lo, 2 halo hi, 16 + r reduction from rank r, 48 + r fused
+//  reduction from rank r; [1] = its sequence number)
+__device__ __forceinline__ bool wait_flag(const unsigned long long* p, unsigned long long want, int* timeout_flag,
+                                          int code) {
+    if (*(volatile int*)timeout_flag) return false;  // an earlier wait of this step already gave up
+    const long long t0 = clock64();
+    while (ld_acquire_sys(p) < want) {
+        if (clock64() - t0 > SPIN_LIMIT_CYCLES) {
+            if (atomicCAS(timeout_flag, 0, code) == 0) timeout_flag[1] = (int)want;
+            return false;
+        }
+        __nanosleep(64);
+    }
+    return true;
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -253,13 +319,50 @@ __device__ __forceinline__ void block_reduce_finish(double (&v)[NV], const RedBu
     }
     __syncthreads();
     if (wid == 0) {
+        double loc[NV];
 #pragma unroll
         for (int q = 0; q < NV; q++) {
             double r = (lane < nw) ? sh[q][lane] : (IS_MAX ? -INFINITY : 0.0);
-            r = IS_MAX ? warp_max(r) : warp_sum(r);
-            if (lane == 0) out[q] = r;
+            loc[q] = IS_MAX ? warp_max(r) : warp_sum(r);
+        }
+        if (rb.peer) {
+            // All-reduce fused into the producing kernel: lane t serves rank t.  My local result goes into slot [me] of
+            // every box (NVLink stores + system-scope release of a sequence flag); then the R flags in my own box are
+            // awaited and the R values combined in RANK ORDER -- the same numbers in the same order on every rank, so
+            // all ranks hold the same bits (same result as the stand-alone k_allreduce_peer, minus its launch).
+            PeerBoxHeader* me = rb.peer;
+            const int R = me->R, rk = me->r;
+            unsigned long long seq = 0;
+            if (lane == 0) seq = ++me->fseq;
+            seq = __shfl_sync(0xffffffffu, seq, 0);
+            const int buf = (int)(seq & 1);
+            if (lane < R) {
+                PeerBoxHeader* h = reinterpret_cast<PeerBoxHeader*>(me->boxes[lane]);
+#pragma unroll
+                for (int q = 0; q < NV; q++) h->fval[buf][rk][q] = loc[q];
+                __threadfence_system();
+                st_release_sys(&h->fflag[rk][buf], seq);
+            }
+            bool ok = true;
+            if (lane < R) ok = wait_flag(&me->fflag[lane][buf], seq, me->timeout_flag, 48 + lane);
+            ok = __all_sync(0xffffffffu, ok);
+            if (ok && lane == 0) {
+                const volatile double* fv = &me->fval[buf][0][0];
+#pragma unroll
+                for (int q = 0; q < NV; q++) {
+                    double acc = fv[q];
+                    for (int t = 1; t < R; t++) {
+                        const double x = fv[t * 4 + q];
+                        if (IS_MAX) { if (x > acc) acc = x; }
+                        else acc = acc + x;
+                    }
+                    loc[q] = acc;
+                }
+            }
         }
         if (lane == 0) {
+#pragma unroll
+            for (int q = 0; q < NV; q++) out[q] = loc[q];
             *rb.ticket = 0u;
             __threadfence();
         }

@@ -108,7 +108,7 @@ static bool connect_peers(Runner* r, const std::vector<int>& devs) {
     }
     for (int a = 0; a < G; a++) {
         for (int b = 0; b < G; b++) r->s[a]->peer.peer_box[b] = r->s[b]->peer.box;
-        r->s[a]->peer.on = true;
+        if (peer_connected(r->s[a]) != CFD_SUCCESS) return false;
     }
     return true;
 }
@@ -196,7 +196,10 @@ Runner* runner_create(const flow_field* f, const grid* g, int want) {
         else want_nccl = true;  // no peer mapping between these devices: the library transport
     }
     if (ok && G > 1 && want_nccl) {
-        for (int q = 0; q < G; q++) r->s[q]->peer.on = false;
+        for (int q = 0; q < G; q++) {
+            r->s[q]->peer.on = false;
+            r->s[q]->rb.peer = nullptr;
+        }
         Nccl n;
         ok = load_nccl(n, getenv("CFD_B200_NCCL_LIB")) == CFD_SUCCESS;
         std::vector<void*> comms(G, nullptr);

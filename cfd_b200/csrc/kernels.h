@@ -69,6 +69,9 @@ struct NsConst {            // per-step constants of the projection / RK kernels
     double src_decay;                  // exp(-lambda*iter*dt) (solver_explicit_euler.c:326-331)
 };
 
+// stand-alone pull of a pending halo gate (peer.cu): for a launcher that ends up on a kernel without the in-kernel gate
+void peer_pull_from_gate(cudaStream_t st, const HaloGate& hg);
+
 // launchers of the two arithmetic builds (common.cuh): exact ones in cfdb::, fast twins in cfdb::arith_fast::
 #ifdef CFDB_FAST
 inline namespace arith_fast {

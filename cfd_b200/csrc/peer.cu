@@ -26,31 +26,6 @@ namespace cfdb {
 
 namespace {
 
-constexpr long long SPIN_LIMIT_CYCLES = 8000000000LL;  // ~4 s at 2 GHz
-
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-// (timeout_flag[0] = which wait gave up first: 1 halo lo, 2 halo hi, 16 + r reduction from rank r; [1] = its sequence number)
-__device__ __forceinline__ bool wait_flag(const unsigned long long* p, unsigned long long want, int* timeout_flag,
-                                          int code) {
-    if (*(volatile int*)timeout_flag) return false;  // an earlier wait of this step already gave up
-    const long long t0 = clock64();
-    while (ld_acquire_sys(p) < want) {
-        if (clock64() - t0 > SPIN_LIMIT_CYCLES) {
-            if (atomicCAS(timeout_flag, 0, code) == 0) timeout_flag[1] = (int)want;
-            return false;
-        }
-        __nanosleep(64);
-    }
-    return true;
-}
-
 struct PushArgs {
     const double* lo_src[PEER_MAX_FIELDS];   // my first owned layer of every field
     const double* hi_src[PEER_MAX_FIELDS];   // my last owned layer
@@ -228,14 +203,67 @@ void peer_release(cfd_b200_session* s) {
         if (p.ipc_mapped[q] && p.peer_box[q]) cudaIpcCloseMemHandle(p.peer_box[q]);
     if (p.box) cudaFree(p.box);
     p = Peer();
+    s->rb.peer = nullptr;
 }
 
+cfd_status_t peer_connected(cfd_b200_session* s) {
+    Peer& p = s->peer;
+    CFDB_CUDA_OK(cudaSetDevice(s->dev));
+    PeerBoxHeader h;
+    CFDB_CUDA_OK(cudaMemcpy(&h, p.box, sizeof(h), cudaMemcpyDeviceToHost));
+    for (int q = 0; q < PEER_MAX_RANKS; q++) h.boxes[q] = q < s->desc.nranks ? p.peer_box[q] : nullptr;
+    h.timeout_flag = &s->ctl->comm_timeout;
+    h.R = s->desc.nranks;
+    h.r = s->desc.rank;
+    CFDB_CUDA_OK(cudaMemcpy(p.box, &h, sizeof(h), cudaMemcpyHostToDevice));
+    p.on = true;
+    s->rb.peer = getenv("CFD_B200_NO_FUSED_REDUCE") ? nullptr : reinterpret_cast<PeerBoxHeader*>(p.box);
+    // edge blocks that spin inside a sweep would starve the OTHER slabs' kernels when slabs share one GPU
+    const char* vr = getenv("CFD_B200_VIRTUAL_RANKS");
+    s->gate_enabled = !getenv("CFD_B200_NO_HALO_GATE") && !(vr && vr[0] && vr[0] != '0');
+    return CFD_SUCCESS;
+}
+
+// gate != nullptr: launch the push only and describe the pull in *gate (nf <= 2): the next kernel that reads these
+// fields does it in its edge blocks (stencil_tma.cuh: halo_gate_pull), or peer_pull_from_gate() does it stand-alone.
+static cfd_status_t peer_exchange_impl(cfd_b200_session* s, double* const* fields, int nf, bool ring, HaloGate* gate);
+
 cfd_status_t peer_halo_exchange(cfd_b200_session* s, double* const* fields, int nf, bool ring) {
+    return peer_exchange_impl(s, fields, nf, ring, nullptr);
+}
+cfd_status_t peer_halo_push_gated(cfd_b200_session* s, double* const* fields, int nf, HaloGate* gate) {
+    *gate = HaloGate();
+    if (nf > 2) return peer_exchange_impl(s, fields, nf, false, nullptr);
+    return peer_exchange_impl(s, fields, nf, false, gate);
+}
+void peer_pull_from_gate(cudaStream_t st, const HaloGate& hg) {
+    if (!hg.on) return;
+    PullArgs pl;
+    memset(&pl, 0, sizeof(pl));
+    for (int q = 0; q < hg.nf; q++) {
+        pl.lo_halo[q] = hg.halo[0][q];
+        pl.hi_halo[q] = hg.halo[1][q];
+    }
+    pl.lo_box = hg.box[0];
+    pl.hi_box = hg.box[1];
+    pl.lo_flag = hg.flag[0];
+    pl.hi_flag = hg.flag[1];
+    pl.timeout_flag = hg.timeout_flag;
+    pl.seq = hg.seq;
+    pl.cnt = hg.cnt;
+    pl.nf = hg.nf;
+    const long long work = (long long)hg.nf * hg.cnt / 2;
+    int blocks = (int)((work + 256 * 8 - 1) / (256 * 8));
+    blocks = blocks < 1 ? 1 : (blocks > 148 ? 148 : blocks);
+    CFDB_LAUNCH(KK_HALO, st, k_halo_pull<<<blocks, 256, 0, st>>>(pl));
+}
+
+static cfd_status_t peer_exchange_impl(cfd_b200_session* s, double* const* fields, int nf, bool ring, HaloGate* gate) {
     Peer& p = s->peer;
     const int R = s->desc.nranks, r = s->desc.rank;
     if (nf > PEER_MAX_FIELDS) {
         for (int q = 0; q < nf; q += PEER_MAX_FIELDS) {
-            const cfd_status_t rc = peer_halo_exchange(s, fields + q, nf - q < PEER_MAX_FIELDS ? nf - q : PEER_MAX_FIELDS, ring);
+            const cfd_status_t rc = peer_exchange_impl(s, fields + q, nf - q < PEER_MAX_FIELDS ? nf - q : PEER_MAX_FIELDS, ring, nullptr);
             if (rc != CFD_SUCCESS) return rc;
         }
         return CFD_SUCCESS;
@@ -287,6 +315,22 @@ cfd_status_t peer_halo_exchange(cfd_b200_session* s, double* const* fields, int 
     if (blocks < 1) blocks = 1;
     if (blocks > 148) blocks = 148;
     CFDB_LAUNCH(KK_HALO, s->st, k_halo_push<<<blocks, 256, 0, s->st>>>(pa));
+    if (gate) {
+        gate->on = 1;
+        gate->nf = nf;
+        gate->cnt = st;
+        gate->seq = seq;
+        gate->box[0] = pl.lo_box;
+        gate->box[1] = pl.hi_box;
+        gate->flag[0] = pl.lo_flag;
+        gate->flag[1] = pl.hi_flag;
+        for (int q = 0; q < nf; q++) {
+            gate->halo[0][q] = pl.lo_halo[q];
+            gate->halo[1][q] = pl.hi_halo[q];
+        }
+        gate->timeout_flag = pl.timeout_flag;
+        return CFD_SUCCESS;
+    }
     CFDB_LAUNCH(KK_HALO, s->st, k_halo_pull<<<blocks, 256, 0, s->st>>>(pl));
     return CFD_SUCCESS;
 }
@@ -350,8 +394,7 @@ cfd_status_t cfd_b200_session_peer_attach(cfd_b200_session_t* s, const char* han
         p.peer_box[q] = (char*)ptr;
         p.ipc_mapped[q] = true;
     }
-    p.on = true;
-    return CFD_SUCCESS;
+    return peer_connected(s);
 }
 
 int cfd_b200_session_transport(const cfd_b200_session_t* s) {  // 0 none, 1 NCCL, 2 peer memory

@@ -86,6 +86,21 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         else gny = global_dec_extent(s);
         a.omega = pp.omega > 0.0 ? pp.omega : optimal_omega(s->desc, gnx, gny, gnz);
     }
+    // Halo exchange of <= 2 fields whose PULL half rides in the next sweep's edge blocks (HaloGate) when the transport
+    // (peer memory) and the kernels (TMA engines) allow it: the interior of the sweep then runs under the neighbour's
+    // push.  Otherwise the plain exchange (push + pull kernels, or NCCL send/recv).
+    auto exchange = [&](double* f0, double* f1) {
+        a.gate = HaloGate();
+        if (R <= 1) return;
+        double* f[2] = {f0, f1};
+        const int nf = f1 ? 2 : 1;
+        if (s->peer.on && s->gate_enabled && L.tc && L.tc->usable) peer_halo_push_gated(s, f, nf, &a.gate);
+        else halo_exchange(s, f, nf, false);
+    };
+    auto flush_gate = [&]() {  // before a launch that cannot take the gate
+        if (a.gate.on) peer_pull_from_gate(s->st, a.gate);
+        a.gate = HaloGate();
+    };
     CFDB_KL(s, launch_zero_ctl)(L);
     Poll poll{s};
     const int B = batch_size(s);
@@ -113,15 +128,15 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
             for (int b = 0; b < B && q <= a.max_iter; b++, q++) {
                 a.seq = seq++;
                 a.it = q;
-                CFDB_KL(s, launch_jacobi)(L, a, buf[q & 1], buf[(q + 1) & 1], rhs);
+                CFDB_KL(s, launch_jacobi)(L, a, buf[q & 1], buf[(q + 1) & 1], rhs);  // (pulls the halo of its input)
                 if (R > 1) {
-                    double* f[1] = {buf[(q + 1) & 1]};
-                    halo_exchange(s, f, 1, false);
-                    allreduce(s, &s->ctl->dot[q & 1], 1, true);
+                    exchange(buf[(q + 1) & 1], nullptr);
+                    allreduce_produced(s, &s->ctl->dot[q & 1], 1, true);
                 }
             }
             if (poll.step()) break;
         }
+        flush_gate();
         a.seq = seq++;
         a.it = a.max_iter;
         CFDB_KL(s, launch_stationary_final)(L, a);
@@ -153,25 +168,26 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
     } else if (method == POISSON_METHOD_REDBLACK_SOR) {
         a.seq = seq++;
         CFDB_KL(s, launch_linf_residual)(L, a, x, rhs, 0);
-        if (R > 1) allreduce(s, &s->ctl->dot[0], 1, true);
+        if (R > 1) allreduce_produced(s, &s->ctl->dot[0], 1, true);
         for (int it = 0; it < a.max_iter;) {
             for (int b = 0; b < B && it < a.max_iter; b++, it++) {
                 a.it = it;
-                double* f[1] = {x};
                 a.seq = seq++;
                 CFDB_KL(s, launch_redblack)(L, a, x, rhs, 0, 1);
-                if (R > 1) halo_exchange(s, f, 1, false);
+                exchange(x, nullptr);
                 a.seq = seq++;
                 CFDB_KL(s, launch_redblack)(L, a, x, rhs, 1, 0);
-                if (R > 1) halo_exchange(s, f, 1, false);
+                exchange(x, nullptr);
                 if (it % a.check == 0) {
                     a.seq = seq++;
                     CFDB_KL(s, launch_linf_residual)(L, a, x, rhs, (it + 1) & 1);
-                    if (R > 1) allreduce(s, &s->ctl->dot[(it + 1) & 1], 1, true);
+                    a.gate = HaloGate();
+                    if (R > 1) allreduce_produced(s, &s->ctl->dot[(it + 1) & 1], 1, true);
                 }
             }
             if (poll.step()) break;
         }
+        flush_gate();
         a.seq = seq++;
         a.it = a.max_iter;
         CFDB_KL(s, launch_stationary_final)(L, a);
@@ -193,9 +209,8 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         a.seq = seq++;
         CFDB_KL(s, launch_krylov_init)(L, a, x, rhs, r, pb[0], nullptr, pre);
         if (R > 1) {
-            double* f[2] = {r, pb[0]};
-            halo_exchange(s, f, 2, false);
-            allreduce(s, &s->ctl->dot[0], 2, false);
+            exchange(r, pb[0]);
+            allreduce_produced(s, &s->ctl->dot[0], 2, false);
         }
         for (int it = 0; it < a.max_iter;) {
             for (int b = 0; b < B && it < a.max_iter; b++, it++) {
@@ -204,21 +219,22 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
                 // iteration it: p_it lives in pb[it&1]; it == 0 only applies A to p_0
                 double* pold = (it == 0) ? pb[0] : pb[(it - 1) & 1];
                 double* pnew = pb[it & 1];
-                CFDB_KL(s, launch_cg_dir)(L, a, r, pold, pnew, Ap, pre, 0);
-                if (R > 1) allreduce(s, &s->ctl->dot[4 + (it & 1)], 1, false);
+                CFDB_KL(s, launch_cg_dir)(L, a, r, pold, pnew, Ap, pre, 0);  // (pulls the halo of r -- and of p_0)
+                a.gate = HaloGate();
+                if (R > 1) allreduce_produced(s, &s->ctl->dot[4 + (it & 1)], 1, false);
                 a.seq = seq++;
                 CFDB_KL(s, launch_cg_update)(L, a, x, r, pnew, Ap, pre);
                 if (R > 1) {
-                    double* f[1] = {r};
-                    halo_exchange(s, f, 1, false);
-                    allreduce(s, &s->ctl->dot[2 * ((it + 1) & 1)], 2, false);
+                    exchange(r, nullptr);
+                    allreduce_produced(s, &s->ctl->dot[2 * ((it + 1) & 1)], 2, false);
                 }
             }
             if (poll.step()) break;
         }
         a.seq = seq++;
         a.it = a.max_iter;
-        CFDB_KL(s, launch_cg_dir)(L, a, r, pb[0], pb[1], Ap, pre, 1);
+        CFDB_KL(s, launch_cg_dir)(L, a, r, pb[0], pb[1], Ap, pre, 1);  // (decide only; a pending pull is done stand-alone)
+        a.gate = HaloGate();
         CFDB_KL(s, launch_neumann_fill)(L, x, 0, 1, true);
         (void)poll.final_state();
     } else if (method == POISSON_METHOD_BICGSTAB) {
@@ -230,9 +246,8 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         a.seq = seq++;
         CFDB_KL(s, launch_krylov_init)(L, a, x, rhs, r, nullptr, rh, 0);
         if (R > 1) {
-            double* f[1] = {r};
-            halo_exchange(s, f, 1, false);
-            allreduce(s, &s->ctl->dot[0], 2, false);
+            exchange(r, nullptr);
+            allreduce_produced(s, &s->ctl->dot[0], 2, false);
         }
         for (int it = 0; it < a.max_iter;) {
             for (int b = 0; b < B && it < a.max_iter; b++, it++) {
@@ -240,28 +255,28 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
                 a.seq = seq++;
                 double *pold = pb[(it + 1) & 1], *pnew = pb[it & 1];
                 double *vold = vb[(it + 1) & 1], *vnew = vb[it & 1];
-                CFDB_KL(s, launch_bicg_dir)(L, a, r, pold, vold, rh, pnew, vnew, it == 0, 0);
+                CFDB_KL(s, launch_bicg_dir)(L, a, r, pold, vold, rh, pnew, vnew, it == 0, 0);  // (pulls the halo of r)
                 if (R > 1) {
-                    double* f[1] = {vnew};
-                    halo_exchange(s, f, 1, false);
-                    allreduce(s, &s->ctl->dot[4 + (it & 1)], 1, false);
+                    exchange(vnew, nullptr);
+                    allreduce_produced(s, &s->ctl->dot[4 + (it & 1)], 1, false);
                 }
                 a.seq = seq++;
-                CFDB_KL(s, launch_bicg_s)(L, a, r, vnew, sv, tv);
-                if (R > 1) allreduce(s, &s->ctl->dot[8 + 4 * (it & 1)], 3, false);
+                CFDB_KL(s, launch_bicg_s)(L, a, r, vnew, sv, tv);  // (pulls the halo of v)
+                a.gate = HaloGate();
+                if (R > 1) allreduce_produced(s, &s->ctl->dot[8 + 4 * (it & 1)], 3, false);
                 a.seq = seq++;
                 CFDB_KL(s, launch_bicg_update)(L, a, x, r, pnew, sv, tv, rh);
                 if (R > 1) {
-                    double* f[1] = {r};
-                    halo_exchange(s, f, 1, false);
-                    allreduce(s, &s->ctl->dot[2 * ((it + 1) & 1)], 2, false);
+                    exchange(r, nullptr);
+                    allreduce_produced(s, &s->ctl->dot[2 * ((it + 1) & 1)], 2, false);
                 }
             }
             if (poll.step()) break;
         }
         a.seq = seq++;
         a.it = a.max_iter;
-        CFDB_KL(s, launch_bicg_dir)(L, a, r, pb[0], vb[0], rh, pb[1], vb[1], 0, 1);
+        CFDB_KL(s, launch_bicg_dir)(L, a, r, pb[0], vb[0], rh, pb[1], vb[1], 0, 1);  // (decide only)
+        a.gate = HaloGate();
         CFDB_KL(s, launch_neumann_fill)(L, x, 0, 1, true);
         (void)poll.final_state();
     } else {

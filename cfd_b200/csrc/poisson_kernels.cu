@@ -670,7 +670,12 @@ static inline dim3 blk() { return dim3(TX, TY); }
 static inline dim3 pw_grid(const LaunchCtx& L, int& rpb) {
     const long long xt = (L.g.nx - 2 + PW_THREADS - 1) / PW_THREADS;
     const long long rows = (long long)(L.g.ny - 2) * (L.g.k1 - L.g.k0);
-    long long r = rows * xt / (148LL * 8 * 6);
+    static const int waves = [] {  // tuning knob (default 6 waves of 148 x 8 blocks)
+        const char* e = getenv("CFD_B200_PW_WAVES");
+        const int v = e ? atoi(e) : 6;
+        return v < 1 ? 1 : v;
+    }();
+    long long r = rows * xt / (148LL * 8 * waves);
     if (r < 4) r = 4;
     if (r > 64) r = 64;
     const long long cap = (long long)L.rb_blocks;
@@ -708,6 +713,7 @@ void launch_jacobi(const LaunchCtx& L, const KArgs& a0, const double* xin, doubl
             return;
         }
     }
+    peer_pull_from_gate(L.st, a0.gate);  // no in-kernel gate on this path: pull the pending halo layers first
 #define CFDB_JAC(D3, RES) CFDB_LAUNCH(KK_JACOBI, L.st, (k_jacobi<D3, RES><<<L.grid(), blk(), 0, L.st>>>(L.g, xin, xout, rhs, L.ctl, L.rb, a)))
     if (L.g.dim3) { if (res) CFDB_JAC(true, true); else CFDB_JAC(true, false); }
     else { if (res) CFDB_JAC(false, true); else CFDB_JAC(false, false); }
@@ -764,6 +770,7 @@ void launch_redblack(const LaunchCtx& L, const KArgs& a0, double* x, const doubl
             return;
         }
     }
+    peer_pull_from_gate(L.st, a0.gate);  // no in-kernel gate on this path: pull the pending halo layers first
     const KArgs a = with_chunk(L, a0);
     if (L.g.dim3) CFDB_LAUNCH(KK_REDBLACK, L.st, k_redblack<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, a, colour, decide));
     else CFDB_LAUNCH(KK_REDBLACK, L.st, k_redblack<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, a, colour, decide));
@@ -782,6 +789,7 @@ void launch_linf_residual(const LaunchCtx& L, const KArgs& a0, const double* x, 
             return;
         }
     }
+    peer_pull_from_gate(L.st, a0.gate);  // no in-kernel gate on this path: pull the pending halo layers first
     const KArgs a = with_chunk(L, a0);
     if (L.g.dim3) CFDB_LAUNCH(KK_LINF, L.st, k_linf_residual<true><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, L.rb, a, slot));
     else CFDB_LAUNCH(KK_LINF, L.st, k_linf_residual<false><<<L.grid(), blk(), 0, L.st>>>(L.g, x, rhs, L.ctl, L.rb, a, slot));
@@ -823,6 +831,7 @@ void launch_cg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const d
             return;
         }
     }
+    peer_pull_from_gate(L.st, a0.gate);  // no in-kernel gate on this path: pull the pending halo layers first
     const KArgs a = with_chunk(L, a0);
     const dim3 gr = decide_only ? dim3(1, 1, 1) : L.grid();
     if (L.g.dim3) CFDB_LAUNCH(KK_CG_DIR, L.st, k_cg_dir<true><<<gr, blk(), 0, L.st>>>(L.g, r, pold, pnew, Ap, L.ctl, L.rb, a, precond, decide_only));
@@ -855,6 +864,7 @@ void launch_bicg_dir(const LaunchCtx& L, const KArgs& a0, const double* r, const
             return;
         }
     }
+    peer_pull_from_gate(L.st, a0.gate);  // no in-kernel gate on this path: pull the pending halo layers first
     const KArgs a = with_chunk(L, a0);
     const dim3 gr = decide_only ? dim3(1, 1, 1) : L.grid();
     if (L.g.dim3) CFDB_LAUNCH(KK_BICG_DIR, L.st, k_bicg_dir<true><<<gr, blk(), 0, L.st>>>(L.g, r, pold, vold, rhat, pnew, vnew, L.ctl, L.rb, a, decide_only));
@@ -874,6 +884,7 @@ void launch_bicg_s(const LaunchCtx& L, const KArgs& a0, const double* r, const d
             return;
         }
     }
+    peer_pull_from_gate(L.st, a0.gate);  // no in-kernel gate on this path: pull the pending halo layers first
     const KArgs a = with_chunk(L, a0);
     if (L.g.dim3) CFDB_LAUNCH(KK_BICG_S, L.st, k_bicg_s<true><<<L.grid(), blk(), 0, L.st>>>(L.g, r, v, s, t, L.ctl, L.rb, a));
     else CFDB_LAUNCH(KK_BICG_S, L.st, k_bicg_s<false><<<L.grid(), blk(), 0, L.st>>>(L.g, r, v, s, t, L.ctl, L.rb, a));

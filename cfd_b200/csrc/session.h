@@ -25,19 +25,7 @@ struct Nccl {
     int (*CommInitAll)(void**, int, const int*) = nullptr;
 };
 
-// Peer-memory transport (peer.cu): every rank owns one "box" in its device memory that its neighbours write
-// into over NVLink (cudaDeviceEnablePeerAccess inside one process, cudaIpc handles across processes): halo
-// mailboxes, reduction slots and sequence flags.  No library call on the data path.
-constexpr int PEER_MAX_RANKS = 16;
-constexpr int PEER_MAX_FIELDS = 6;
-constexpr int PEER_RED_WORDS = 8;
-struct PeerBoxHeader {                       // lives at offset 0 of a box; flags are monotone sequence numbers
-    unsigned long long hflag[2][2];          // [side lo/hi][buffer]: halo planes of exchange #seq have landed
-    unsigned long long rflag[PEER_MAX_RANKS][2];  // [source rank][buffer]: its reduction payload #seq has landed
-    double rval[2][PEER_MAX_RANKS][PEER_RED_WORDS];
-    unsigned ticket;                         // last-block detection of the push kernel (self-resetting)
-    unsigned pad[15];
-};
+// (PeerBoxHeader and the PEER_* limits live in common.cuh: the reducing kernels use them)
 struct Peer {
     bool on = false;
     char* box = nullptr;                     // my box (device memory, cudaMalloc)
@@ -94,6 +82,7 @@ struct cfd_b200_session {
     // first failure of a halo exchange / all-reduce since the last check (comm_check): a decomposed solve
     // that lost an exchange must not report success on a per-slab answer
     cfd_status_t comm_err = CFD_SUCCESS;
+    bool gate_enabled = false;  // peer transport: the pull of an exchange may ride in the consuming kernel (HaloGate)
     int kernels_at_create = 0;
 
     cfdb::LaunchCtx L() const {
@@ -137,6 +126,12 @@ cfd_status_t peer_alloc_box(cfd_b200_session* s);
 void peer_release(cfd_b200_session* s);
 cfd_status_t peer_halo_exchange(cfd_b200_session* s, double* const* fields, int nf, bool periodic_ring);
 cfd_status_t peer_allreduce(cfd_b200_session* s, void* dev, int n, int op);  // op 0 sum f64, 1 max f64, 2 max i32
+// after the boxes are mapped: fill the device-side header (box table, rank, time-out flag) and switch the fused
+// reductions of the session on (CFD_B200_NO_FUSED_REDUCE=1: keep the stand-alone all-reduce kernel)
+cfd_status_t peer_connected(cfd_b200_session* s);
+cfd_status_t peer_halo_push_gated(cfd_b200_session* s, double* const* fields, int nf, HaloGate* gate);
+// all-reduce of values a reducing KERNEL has just left in Ctl: nothing to do when the kernel finished it itself
+cfd_status_t allreduce_produced(cfd_b200_session* s, double* dev, int n, bool is_max);
 cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double** x,
                            double** xtmp, const double* rhs, poisson_solver_stats_t* st);
 // geometric multigrid (poisson_mg.cu): x in place, boundary cells filled at the end; one GPU only

@@ -152,6 +152,10 @@ cfd_status_t allreduce(cfd_b200_session* s, double* dev, int cnt, bool is_max) {
     return allreduce_any(s, dev, cnt, 8, is_max ? 2 : 0);
 }
 cfd_status_t allreduce_int_max(cfd_b200_session* s, int* dev, int cnt) { return allreduce_any(s, dev, cnt, 2, 2); }
+cfd_status_t allreduce_produced(cfd_b200_session* s, double* dev, int cnt, bool is_max) {
+    if (s->rb.peer) return CFD_SUCCESS;  // block_reduce_finish of the producing kernel already combined the ranks
+    return allreduce(s, dev, cnt, is_max);
+}
 
 cfd_status_t comm_ready(cfd_b200_session* s) {
     if (s->desc.nranks > 1 && !s->nccl.comm && !s->peer.on) {

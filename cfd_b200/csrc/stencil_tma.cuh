@@ -47,11 +47,56 @@ struct DirectPipe {
 
 #ifdef __CUDACC__
 
+// Chunk a block works on: with a halo gate pending the two edge chunks go LAST (order 1, 2, ..., n-2, 0, n-1), so the
+// blocks that have to wait for a neighbour are scheduled after the interior ones.
+__device__ __forceinline__ int gate_chunk(const HaloGate* hg, int b, int nb) {
+    if (!hg || !hg->on || nb <= 2) return b;
+    return b < nb - 2 ? b + 1 : (b == nb - 2 ? 0 : nb - 1);
+}
+// Called by ALL threads of a block before its first load.  lo / hi: the block's chunk touches the low / high halo
+// layer.  (x0, y0): origin of the block's {HX, HY} box; d3 = false: the layers are ROWS (y-slabs) and the box is a row
+// segment.  Neighbouring blocks copy overlapping cells with identical values (benign).
+__device__ __forceinline__ void halo_gate_pull(const HaloGate* hg, const Geom& g, int x0, int y0, bool lo, bool hi,
+                                               bool d3) {
+    if (!hg || !hg->on) return;
+    const bool need0 = lo && hg->box[0], need1 = hi && hg->box[1];
+    if (!need0 && !need1) return;  // (block-uniform)
+    __shared__ int gate_ok;
+    if (threadIdx.x == 0) {
+        bool ok = true;
+        if (need0) ok = wait_flag(hg->flag[0], hg->seq, hg->timeout_flag, 1) && ok;
+        if (need1) ok = wait_flag(hg->flag[1], hg->seq, hg->timeout_flag, 2) && ok;
+        gate_ok = ok;
+    }
+    __syncthreads();
+    if (gate_ok) {
+        const int w = min(Tile::HX, g.nx - x0);
+        const int h = d3 ? min(Tile::HY, g.ny - y0) : 1;
+        for (int side = 0; side < 2; side++) {
+            if (!(side ? need1 : need0)) continue;
+            for (int f = 0; f < hg->nf; f++) {
+                const double* src = hg->box[side] + (long long)f * hg->cnt;
+                double* dst = hg->halo[side][f];
+                for (int e = threadIdx.x; e < w * h; e += blockDim.x) {
+                    const int r = e / w, c = e - r * w;
+                    const long long off = d3 ? (long long)(y0 + r) * g.nx + x0 + c : (long long)(x0 + c);
+                    dst[off] = __ldcg(src + off);  // written by another GPU: read past L1
+                }
+            }
+        }
+        __threadfence();
+        fence_proxy_async_global();
+    }
+    __syncthreads();
+    fence_proxy_async_global();  // (the thread that issues the TMA loads is one of us)
+}
+
 // 2-D grids (nz == 1): the pipeline marches along y instead -- a block owns `ychunk` consecutive
 // 64 x 16 tiles of one x column of tiles and streams their {66,18,1} boxes through the same ring
 // (each box carries its own y halo; the 2 shared rows per tile come from L2).
 template <class Op>
-__device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, const Geom& g, int ychunk, Op& op) {
+__device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, const Geom& g, int ychunk, Op& op,
+                                                    const HaloGate* hg = nullptr) {
     constexpr int NF = Op::NF, NPW = Op::NPW, ST = DirectPipe<NF>::ST;
     constexpr int PP = Tile::PLANE_PAD;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -60,7 +105,7 @@ __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, co
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * Tile::BX;
     const int tiles_y = (g.ny - 2 + Tile::BY - 1) / Tile::BY;
-    const int ty0 = blockIdx.y * ychunk;
+    const int ty0 = gate_chunk(hg, blockIdx.y, gridDim.y) * ychunk;
     const int nt = min(ychunk, tiles_y - ty0);
     uint64_t* empty = full + ST;
     if (tid == 0) {
@@ -72,6 +117,7 @@ __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, co
         mbar_fence_init();
     }
     __syncthreads();
+    halo_gate_pull(hg, g, x0, 0, ty0 == 0, ty0 + nt == tiles_y, false);
     constexpr bool PWARP = Op::PRODUCER_WARP;
     int next_q = 0;
     auto issue = [&](int q) {
@@ -146,9 +192,10 @@ __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, co
 }
 
 template <bool D3, class Op>
-__device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const Geom& g, int zchunk, Op& op) {
+__device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const Geom& g, int zchunk, Op& op,
+                                                 const HaloGate* hg = nullptr) {
     if (!D3) {
-        tma_direct_sweep_2d(tm, g, zchunk, op);
+        tma_direct_sweep_2d(tm, g, zchunk, op, hg);
         return;
     }
     constexpr int NF = Op::NF, NPW = Op::NPW, ST = DirectPipe<NF>::ST;
@@ -158,7 +205,7 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
     uint64_t* full = reinterpret_cast<uint64_t*>(ring + DirectPipe<NF>::RING);  // [ST]
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * Tile::BX, y0 = blockIdx.y * Tile::BY;
-    const int kb = g.k0 + blockIdx.z * zchunk, ke = min(kb + zchunk, g.k1);
+    const int kb = g.k0 + gate_chunk(hg, blockIdx.z, gridDim.z) * zchunk, ke = min(kb + zchunk, g.k1);
     const int np = ke - kb + 2;  // planes kb-1 .. ke
     const int pz0 = kb - 1;
     uint64_t* empty = full + ST;
@@ -171,6 +218,7 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
         mbar_fence_init();
     }
     __syncthreads();
+    halo_gate_pull(hg, g, x0, y0, kb == g.k0, ke == g.k1, true);
     constexpr bool PWARP = Op::PRODUCER_WARP;  // false: 512 threads, thread 0 refills after a block barrier
     int next_q = 0;
     auto issue = [&](int q) {

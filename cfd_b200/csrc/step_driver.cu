@@ -75,7 +75,7 @@ static cfd_status_t read_flags(cfd_b200_session* s, int* nonfinite) {
 static void fill_stats(cfd_b200_session* s, ns_solver_stats_t* stats, int iters) {
     if (!stats) return;
     CFDB_KL(s, launch_field_stats)(s->L(), s->u, s->v, s->w, s->p, s->T);
-    if (s->desc.nranks > 1) allreduce(s, &s->ctl->stat[0], 3, true);
+    if (s->desc.nranks > 1) allreduce_produced(s, &s->ctl->stat[0], 3, true);
     cudaMemcpyAsync(&s->h_ctl[0], s->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s->st);
     cudaStreamSynchronize(s->st);
     stats->iterations = iters;

@@ -86,6 +86,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void fence_proxy_async() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
+// generic-proxy WRITES to global memory (halo layers copied out of a mailbox) before TMA loads of the same addresses
+__device__ __forceinline__ void fence_proxy_async_global() {
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+}
 // one {HX, HY, 1} box of `map` at (x0, y0, z) -> smem dst; completion counted in bytes on bar
 __device__ __forceinline__ void tma_load_plane(void* dst, const CUtensorMap* map, int x0, int y0, int z,
                                                uint64_t* bar) {

@@ -13,6 +13,7 @@
 #   launches     ncu launch list (gpu__time_duration.sum) of the default bench command + share summary
 #   ncu          ncu --set full of the headline kernels -> profiles-ready CSV (tools/ncu_summary.py)
 #   ncu512       ncu --set full of the 512^3 kernels that are not part of the headline
+#   c4waves      2-D pointwise kernels: blocks per launch (CFD_B200_PW_WAVES) at the C4 slab sizes
 #   sass         SASS opcode histogram of the shipped cubins (runs anywhere)
 TAG=$1; shift
 mkdir -p gpurun_out
@@ -87,6 +88,12 @@ PY
       python tools/ncu_summary.py "ncu --set full --clock-control none, tools/kernel_table.py --shape 512,512,512 (jacobi, rbsor, cg, rk4, euler); $(date -u +%F) $TAG" \
           ${O}_ncu_512.csv ${O}_ncu_512.ncu-rep
       if [ $(stat -c %s ${O}_ncu_512.ncu-rep) -gt 40000000 ]; then rm ${O}_ncu_512.ncu-rep; fi ;;
+    c4waves)
+      out=${O}_c4_pw_waves.jsonl; : > $out
+      for w in 6 3 2 1; do for shape in 4096,4096,1 4096,2050,1 4096,1026,1; do
+        CFD_B200_PW_WAVES=$w timeout 150 python tools/kernel_table.py --shape $shape --stepper projection --method pcg --iters 50 --energy 2>/dev/null | tail -1 |
+          python -c "import json,sys; d=json.loads(sys.stdin.read()); print(json.dumps({'pw_waves': $w, 'shape': d['shape'], 'ms_per_step': round(d['ms_per_step'],3), 'kernels': {k['kernel']: [k['avg_us'], k['frac_of_measured_peak']] for k in d['kernels'][:3]}}))" >> $out
+      done; done; cat $out ;;
     sass)
       python tools/sass_histogram.py > ${O}_sass_histogram.md; head -30 ${O}_sass_histogram.md ;;
     *) echo "unknown stage $stage" ;;
