@@ -28,6 +28,7 @@ class Ctx:
         self.orc = oracle.Oracle()
         self.fails = []
         self.results = []
+        self.transport = "?"
 
 
 def global_case(kind, nx, ny, nzg):
@@ -72,6 +73,7 @@ def run_case(cx, name, kind, shape, stepper, method=None, nsteps=2, tol=0.0, poi
     s = api.Session(lg.nx, lg.ny, lg.nz, dx, dy, dz, float(lg.x[0]), float(lg.y[0]),
                     float(lg.z[0]) if nzg > 1 else 0.0, rank=rank, nranks=world, device=local)
     dist.attach_comm(s, rank, world)
+    cx.transport = s.transport()
     # bit-identical coordinates on every rank: the slice of the GLOBAL grid arrays
     if nzg > 1:
         s.set_coords(g.x, g.y)
@@ -206,7 +208,7 @@ def main():
         if fails:
             print("MULTIGPU PARITY FAILED:", fails)
             sys.exit(1)
-        print("MULTIGPU PARITY OK")
+        print("MULTIGPU PARITY OK (world=%d transport=%s)" % (world, cx.transport))
 
 
 if __name__ == "__main__":

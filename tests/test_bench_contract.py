@@ -36,3 +36,36 @@ def test_reference_arm_prints_one_contract_line():
 
 def test_reference_arm_other_ranks_exit_quietly():
     assert _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}) == []
+
+
+def test_slab_partition_matches_the_gangs_rule():
+    """bench.py --config c4 cuts the FIXED grid like csrc/gang.cu does: interior layers dealt out as evenly as
+    possible, the first (interior % G) ranks one layer more, one boundary / halo layer each side."""
+    sys.path.insert(0, ROOT)
+    import bench
+    for layers, world in ((4096, 1), (4096, 2), (4096, 4), (131, 3), (29, 4), (1024, 8)):
+        parts = bench.slab_partition(layers, world)
+        assert len(parts) == world and parts[0][0] == 0
+        own = [n - 2 for _, n in parts]
+        assert sum(own) == layers - 2 and max(own) - min(own) <= 1 and own == sorted(own, reverse=True)
+        for (lo, n), (lo2, _) in zip(parts, parts[1:]):
+            assert lo2 == lo + n - 2  # the next slab starts on my last owned layer's successor minus its halo
+        assert parts[-1][0] + parts[-1][1] == layers
+
+
+def test_roofline_traffic_comes_from_the_committed_ncu_summary():
+    """roofline.traffic is read from profiles/ncu_headline_latest.csv (no number typed into bench.py): the file
+    parses, names its box, and the DRAM traffic of the dominant kernel is within 0.9 .. 1.3 of its algorithmic bytes."""
+    sys.path.insert(0, ROOT)
+    import bench
+    if not os.path.exists(bench.NCU_LATEST):
+        pytest.skip("no committed ncu summary yet")
+    with open(bench.NCU_LATEST) as fh:
+        title = fh.readline()
+    assert "box=" in title and "ncu --set full" in title
+    n = int(title.split("box=")[1].split(";")[0].split()[0])
+    got, src = bench.ncu_traffic("bicg_update", n)
+    assert got and src and "ncu_headline_latest.csv" in src
+    algorithmic = 56.0 * (n - 2) ** 3
+    assert 0.9 * algorithmic <= got <= 1.3 * algorithmic, (got, algorithmic)
+    assert bench.ncu_traffic("bicg_update", n + 2) [0] is None  # another box: not applicable

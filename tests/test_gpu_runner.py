@@ -229,6 +229,34 @@ def test_gang_behind_the_stateless_symbols_equals_the_undecomposed_oracle(clean,
         close(f, fo, tol, "%s G=%d" % (name, G))
 
 
+@pytest.mark.parametrize("case", [c for c in GANG_CASES if c[0] in ("jacobi z-slabs uneven", "rbsor y-slabs uneven",
+                                                                     "multi-tile bicgstab x12", "pcg y-slabs", "rk4 z-slabs uneven")],
+                         ids=lambda c: c[0].replace(" ", "_"))
+def test_gang_over_the_nccl_fallback(clean, orc, monkeypatch, case):
+    """The library transport (ncclCommInitAll, ncclSend/Recv, ncclAllReduce) behind the same gang: what runs where
+    devices cannot map each other's memory.  Needs two real GPUs (NCCL cannot put two ranks on one device)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    monkeypatch.setenv("CFD_B200_GANG_TRANSPORT", "nccl")
+    name, kind, method, shape, tol, pkw = case
+    g, f = cases.random_field(*shape, seed=21, scale=0.05)
+    f.rho[...] = 1.0 + 0.1 * np.random.default_rng(2).random(f.rho.shape)
+    p = cases.params(dt=1e-3, amp=(0.1, 0.05))
+    p.max_iter = 2
+    fo = f.copy()
+    pc = abi.poisson_config(method or "cg", on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE, **pkw)
+    api.set_poisson(pc)
+    api.set_device_count(2)
+    rc = api.solve_method_gpu(kind, f, g, p)
+    rco = orc.projection(fo, g, p, pc, 2)[0] if kind == "projection" else orc.rk(fo, g, p, int(kind[2]), 2)
+    assert rc == rco == 0, api.last_error()
+    if tol == 0.0:
+        bitwise(f, fo, "%s over NCCL" % name)
+    else:
+        close(f, fo, tol, "%s over NCCL" % name)
+
+
 @pytest.mark.parametrize("G", [2, 4])
 def test_gang_natural_convection_y_slabs(clean, orc, monkeypatch, G):
     """C4 shape: energy + buoyancy + thermal BCs, PCG, y-slabs, persistent solver object with stats."""

@@ -64,11 +64,14 @@ for stage in "$@"; do
       timeout 600 python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu > /dev/null 2>&1 &&
       timeout 1200 ncu --set full --clock-control none --import-source on \
           -k regex:'bicg_dir_tma|bicg_s_tma|bicg_update|predictor_tma|divergence_tma|corrector_tma|krylov_init' \
-          --launch-skip 12 -c 14 -o ${O}_ncu_headline -f python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu > ${O}_ncu_full.log 2>&1
+          --launch-skip 0 -c 16 -o ${O}_ncu_headline -f python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu > ${O}_ncu_full.log 2>&1
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:'corrector_tma' -c 1 \
+          -o ${O}_ncu_corrector -f python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu >> ${O}_ncu_full.log 2>&1
       box=$(python -c "import json;print(json.load(open('${O}_launch_bench.json'))['config']['grid_global'][0])" 2>/dev/null || echo 1024)
       python tools/ncu_summary.py "ncu --set full --clock-control none, python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu; box=$box; $(date -u +%F) $TAG" \
-          ${O}_ncu_headline.csv ${O}_ncu_headline.ncu-rep
-      if [ $(stat -c %s ${O}_ncu_headline.ncu-rep) -gt 40000000 ]; then rm ${O}_ncu_headline.ncu-rep; fi ;;
+          ${O}_ncu_headline.csv ${O}_ncu_headline.ncu-rep ${O}_ncu_corrector.ncu-rep
+      tail -3 ${O}_ncu_full.log | cut -c1-200
+      for f in ${O}_ncu_headline.ncu-rep ${O}_ncu_corrector.ncu-rep; do if [ $(stat -c %s $f) -gt 25000000 ]; then rm $f; fi; done ;;
     ncu512)
       cat > /tmp/prof512.py <<'PY'
 import subprocess, sys
