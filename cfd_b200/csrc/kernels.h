@@ -28,6 +28,7 @@ struct LaunchCtx {
     int zchunk;     // planes marched per block
     TmaCache* tc;   // may be null
     int zchunk_tma; // planes marched per block of the TMA kernels
+    int zchunk_tma1; // ... of those that run one block per SM (small grids: one wave of 148 blocks)
     size_t rb_blocks;  // rows of the partial-sum buffer (upper bound on reducing grids)
     dim3 grid() const;   // tile grid over (nx, ny, z-chunks)
 };

@@ -276,8 +276,10 @@ void launch_predictor(const LaunchCtx& L, const NsConst& c, const double* u, con
         if (tma_maps2(L, ops, tm)) {
             constexpr size_t SM = DirectPipe<3>::SMEM;
             CFDB_ONCE_PER_DEVICE(tma_optin(k_predictor_tma<true>, SM), tma_optin(k_predictor_tma<false>, SM));
-            if (L.g.dim3) CFDB_LAUNCH(KK_PREDICTOR, L.st, (k_predictor_tma<true><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, T, su_tab, sv_tab, us, vs, ws)));
-            else CFDB_LAUNCH(KK_PREDICTOR, L.st, (k_predictor_tma<false><<<tma_grid2(L), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L.zchunk_tma, T, su_tab, sv_tab, us, vs, ws)));
+            LaunchCtx L1 = L;  // one block per SM (93 registers x 544 threads): its own chunk length
+            L1.zchunk_tma = L.zchunk_tma1;
+            if (L.g.dim3) CFDB_LAUNCH(KK_PREDICTOR, L.st, (k_predictor_tma<true><<<tma_grid2(L1), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L1.zchunk_tma, T, su_tab, sv_tab, us, vs, ws)));
+            else CFDB_LAUNCH(KK_PREDICTOR, L.st, (k_predictor_tma<false><<<tma_grid2(L1), Tile::THREADS_PW, SM, L.st>>>(tm, L.g, c, L1.zchunk_tma, T, su_tab, sv_tab, us, vs, ws)));
             CFDB_LAUNCH(KK_BOUNDARY, L.st, (k_boundary_carry3<<<face_blocks(L.g), 256, 0, L.st>>>(L.g, u, v, w, us, vs, ws)));
             return;
         }

@@ -224,7 +224,30 @@ cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
         if (zc > 32) zc = 32;
         if (zc < 4) zc = 4;
         if (zc > nzi) zc = nzi;
+        // Cache-resident 3-D grids (fewer than ~3 waves of blocks): wave quantisation and the per-block pipeline fill
+        // decide, not L2 locality.  Measured at 128^3 (profiles/r2l_zchunk_sweep.jsonl): 4-plane chunks = 512 blocks;
+        // 7-plane chunks = 288 blocks (two per SM) take the Jacobi step from 1.31 to 1.09 ms, 14-plane chunks = 144
+        // blocks (one per SM) take RK4 from 0.405 to 0.333 ms per step.  Cost model: waves x (planes + prologue + fill);
+        // kernels that run one block per SM (rk_stage, euler, predictor) get their own chunk length.
+        const bool small_grid = ttiles * ((nzi + zc - 1) / zc) < 3 * 148 * 2;  // (a property of the grid, not of a kernel)
+        auto small_grid_chunk = [&](long long slots, long long zc_now) -> long long {
+            if (!small_grid) return zc_now;
+            long long best = zc_now;
+            double best_cost = 1e300;
+            for (long long z = 4; z <= 32 && z <= nzi; z++) {
+                const long long blocks = ttiles * ((nzi + z - 1) / z);
+                const double cost = (double)((blocks + slots - 1) / slots) * (double)(z + 5);
+                if (cost < best_cost) {
+                    best_cost = cost;
+                    best = z;
+                }
+            }
+            return best;
+        };
+        const long long zc1 = s->g.dim3 ? small_grid_chunk(148, zc) : zc;
+        if (s->g.dim3) zc = small_grid_chunk(148 * 2, zc);
         s->zchunk_tma = (int)(zc < 1 ? 1 : zc);
+        s->zchunk_tma1 = (int)(zc1 < 1 ? 1 : zc1);
         if (!s->g.dim3) {
             // 2-D: the TMA kernels march along y; zchunk_tma = tiles of 16 rows per block
             const long long tx = (s->g.nx - 2 + Tile::BX - 1) / Tile::BX, ty = (s->g.ny - 2 + Tile::BY - 1) / Tile::BY;
@@ -233,10 +256,11 @@ cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
             if (yc > 32) yc = 32;
             if (yc < 1) yc = 1;
             s->zchunk_tma = (int)yc;
+            s->zchunk_tma1 = (int)yc;
         }
         if (const char* e = getenv("CFD_B200_ZCHUNK_TMA")) {  // tuning knob
             const int v = atoi(e);
-            if (v >= 1) s->zchunk_tma = v > nzi ? nzi : v;
+            if (v >= 1) s->zchunk_tma = s->zchunk_tma1 = v > nzi ? nzi : v;
         }
         const size_t tma_blocks = s->g.dim3 ? (size_t)ttiles * (size_t)((nzi + s->zchunk_tma - 1) / s->zchunk_tma)
                                             : (size_t)ttiles;

@@ -71,6 +71,7 @@ struct cfd_b200_session {
     cfdb::Profiler prof;
     cfdb::TmaCache tma;
     int zchunk_tma = 1;
+    int zchunk_tma1 = 1;      // ... of the TMA kernels that run ONE block per SM (rk_stage, euler, predictor)
     cfdb::Nccl nccl;
     cfdb::Peer peer;
     poisson_solver_stats_t last_ps = {};
@@ -94,6 +95,7 @@ struct cfd_b200_session {
         l.zchunk = zchunk;
         l.tc = const_cast<cfdb::TmaCache*>(&tma);
         l.zchunk_tma = zchunk_tma;
+        l.zchunk_tma1 = zchunk_tma1;
         l.rb_blocks = rb_blocks;
         return l;
     }
