@@ -184,7 +184,9 @@ cfd_status_t peer_alloc_box(cfd_b200_session* s) {
     CFDB_CUDA_OK(cudaSetDevice(s->dev));
     peer_kernel_setup();
     p.cnt = s->g.dim3 ? (size_t)s->g.nx * s->g.ny : (size_t)s->g.nx;
-    p.box_bytes = sizeof(PeerBoxHeader) + 4 * PEER_MAX_FIELDS * p.cnt * sizeof(double);
+    const size_t mail_bytes = sizeof(PeerBoxHeader) + 4 * PEER_MAX_FIELDS * p.cnt * sizeof(double);
+    const size_t halo2_off = (mail_bytes + 255) / 256 * 256;
+    p.box_bytes = halo2_off + 2 * p.cnt * sizeof(double);
     if (cudaMalloc((void**)&p.box, p.box_bytes) != cudaSuccess) {
         cudaGetLastError();
         p.box = nullptr;
@@ -192,6 +194,9 @@ cfd_status_t peer_alloc_box(cfd_b200_session* s) {
         return CFD_ERROR_NOMEM;
     }
     CFDB_CUDA_OK(cudaMemset(p.box, 0, sizeof(PeerBoxHeader)));
+    p.halo2[0] = reinterpret_cast<double*>(p.box + halo2_off);
+    p.halo2[1] = p.halo2[0] + p.cnt;
+    CFDB_CUDA_OK(cudaMemset(p.halo2[0], 0, 2 * p.cnt * sizeof(double)));
     s->bytes_allocated += p.box_bytes;
     p.peer_box[s->desc.rank] = p.box;
     return CFD_SUCCESS;
@@ -226,10 +231,17 @@ cfd_status_t peer_connected(cfd_b200_session* s) {
 
 // gate != nullptr: launch the push only and describe the pull in *gate (nf <= 2): the next kernel that reads these
 // fields does it in its edge blocks (stencil_tma.cuh: halo_gate_pull), or peer_pull_from_gate() does it stand-alone.
-static cfd_status_t peer_exchange_impl(cfd_b200_session* s, double* const* fields, int nf, bool ring, HaloGate* gate);
+// deep2: ONE field, two layers per side (the second one lands in Peer::halo2), sent as two "fields" of one exchange.
+static cfd_status_t peer_exchange_impl(cfd_b200_session* s, double* const* fields, int nf, bool ring, HaloGate* gate,
+                                       bool deep2 = false);
 
 cfd_status_t peer_halo_exchange(cfd_b200_session* s, double* const* fields, int nf, bool ring) {
     return peer_exchange_impl(s, fields, nf, ring, nullptr);
+}
+cfd_status_t peer_halo_exchange2(cfd_b200_session* s, double* field, HaloGate* gate) {
+    if (gate) *gate = HaloGate();
+    double* f[1] = {field};
+    return peer_exchange_impl(s, f, 1, false, gate, true);
 }
 cfd_status_t peer_halo_push_gated(cfd_b200_session* s, double* const* fields, int nf, HaloGate* gate) {
     *gate = HaloGate();
@@ -258,7 +270,8 @@ void peer_pull_from_gate(cudaStream_t st, const HaloGate& hg) {
     CFDB_LAUNCH(KK_HALO, st, k_halo_pull<<<blocks, 256, 0, st>>>(pl));
 }
 
-static cfd_status_t peer_exchange_impl(cfd_b200_session* s, double* const* fields, int nf, bool ring, HaloGate* gate) {
+static cfd_status_t peer_exchange_impl(cfd_b200_session* s, double* const* fields, int nf, bool ring, HaloGate* gate,
+                                       bool deep2) {
     Peer& p = s->peer;
     const int R = s->desc.nranks, r = s->desc.rank;
     if (nf > PEER_MAX_FIELDS) {
@@ -289,6 +302,14 @@ static cfd_status_t peer_exchange_impl(cfd_b200_session* s, double* const* field
         pa.hi_src[q] = fields[q] + (n_ax - 2) * st;
         pl.lo_halo[q] = fields[q];
         pl.hi_halo[q] = fields[q] + (n_ax - 1) * st;
+    }
+    if (deep2) {
+        if (nf != 1 || n_ax < 4 || !p.halo2[0]) return CFD_ERROR_INVALID;
+        pa.lo_src[1] = fields[0] + 2 * st;
+        pa.hi_src[1] = fields[0] + (n_ax - 3) * st;
+        pl.lo_halo[1] = p.halo2[0];
+        pl.hi_halo[1] = p.halo2[1];
+        nf = 2;
     }
     if (has_lo) {  // my low edge is the lo neighbour's HIGH halo
         PeerBoxHeader* h = reinterpret_cast<PeerBoxHeader*>(p.peer_box[lo]);

@@ -101,19 +101,34 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
         if (a.gate.on) peer_pull_from_gate(s->st, a.gate);
         a.gate = HaloGate();
     };
+    // One-pass Red-Black SOR on z-slabs: peer transport (its box holds the second halo layer) and >= 2 own planes on
+    // EVERY rank -- agreed once per slab layout with an all-reduce, since ranks that took different paths would wait
+    // for exchanges the others never issue.
+    const int method = cfg->method;
+    double* const* halo2 = nullptr;
+    if (method == POISSON_METHOD_REDBLACK_SOR && R > 1 && s->g.dim3 && s->peer.on && s->peer.halo2[0]) {
+        if (s->rb_slab_ok < 0) {
+            CFDB_CUDA_OK(cudaMemsetAsync(&s->ctl->pad[0], s->g.nz >= 4 ? 0 : 1, sizeof(int), s->st));
+            if (allreduce_int_max(s, &s->ctl->pad[0], 1) != CFD_SUCCESS) return CFD_ERROR;
+            int bad = 1;
+            CFDB_CUDA_OK(cudaMemcpyAsync(&bad, &s->ctl->pad[0], sizeof(int), cudaMemcpyDeviceToHost, s->st));
+            CFDB_CUDA_OK(cudaStreamSynchronize(s->st));
+            s->rb_slab_ok = bad ? 0 : 1;
+        }
+        if (s->rb_slab_ok == 1) halo2 = s->peer.halo2;
+    }
+    const bool rb_fused = method == POISSON_METHOD_REDBLACK_SOR && (R == 1 || halo2) &&
+                          CFDB_KL(s, rbsor_fused_available)(L, halo2);
     CFDB_KL(s, launch_zero_ctl)(L);
     Poll poll{s};
     const int B = batch_size(s);
     double* x = *px;
     int seq = 1;
-    const int method = cfg->method;
     cfd_status_t rc = CFD_SUCCESS;
 
     // the one-pass Red-Black SOR iteration is out of place: it needs the ping-pong partner as well
     // (no memory for it => the in-place half-sweeps below)
-    if (method == POISSON_METHOD_REDBLACK_SOR && R == 1 && pxt && !*pxt && CFDB_KL(s, rbsor_fused_available)(L) &&
-        dalloc(s, pxt) != CFD_SUCCESS)
-        *pxt = nullptr;
+    if (rb_fused && pxt && !*pxt && dalloc(s, pxt) != CFD_SUCCESS) *pxt = nullptr;
 
     if (method == POISSON_METHOD_JACOBI && R == 1 && a.max_iter >= 1 && jacobi_cluster_available(L) &&
         (a.seq = seq, launch_jacobi_cluster(L, a, x, rhs))) {
@@ -145,18 +160,35 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
             *px = buf[1];
             *pxt = buf[0];
         }
-    } else if (method == POISSON_METHOD_REDBLACK_SOR && R == 1 && pxt && *pxt && CFDB_KL(s, rbsor_fused_available)(L) &&
-               L.tc->get_wide(x) && L.tc->get_wide(*pxt) && L.tc->get(rhs)) {
+    } else if (rb_fused && pxt && *pxt && L.tc->get_wide(x) && L.tc->get_wide(*pxt) && L.tc->get(rhs) &&
+               (!halo2 || (L.tc->get_wide(halo2[0]) && L.tc->get_wide(halo2[1])))) {
         // one pass per iteration, same protocol as Jacobi: sweep q reads x_q, writes x_{q+1}, leaves res(x_q)
         double* buf[2] = {x, *pxt};
+        // slabs: x travels two layers deep, once per iteration; the pull rides in the next sweep's edge blocks
+        auto exchange2 = [&](double* f) {
+            a.gate = HaloGate();
+            if (peer_halo_exchange2(s, f, s->gate_enabled ? &a.gate : nullptr) != CFD_SUCCESS && s->comm_err == CFD_SUCCESS)
+                s->comm_err = CFD_ERROR;
+        };
+        if (halo2) {
+            // the first half-sweep on the neighbour's edge plane reads its right-hand side
+            double* fr[1] = {const_cast<double*>(rhs)};
+            if ((rc = halo_exchange(s, fr, 1, false)) != CFD_SUCCESS) return rc;
+            exchange2(x);
+        }
         for (int q = 0; q <= a.max_iter;) {
             for (int b = 0; b < B && q <= a.max_iter; b++, q++) {
                 a.seq = seq++;
                 a.it = q;
-                if (!CFDB_KL(s, launch_rbsor_fused)(L, a, buf[q & 1], buf[(q + 1) & 1], rhs)) return CFD_ERROR;
+                if (!CFDB_KL(s, launch_rbsor_fused)(L, a, buf[q & 1], buf[(q + 1) & 1], rhs, halo2)) return CFD_ERROR;
+                if (halo2) {
+                    exchange2(buf[(q + 1) & 1]);
+                    allreduce_produced(s, &s->ctl->dot[q & 1], 1, true);
+                }
             }
             if (poll.step()) break;
         }
+        flush_gate();
         a.seq = seq++;
         a.it = a.max_iter;
         CFDB_KL(s, launch_stationary_final)(L, a);

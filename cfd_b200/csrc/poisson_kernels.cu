@@ -652,6 +652,7 @@ k_bicg_update(Geom g, double* __restrict__ x, double* __restrict__ r, const doub
 #include "poisson_tma.inc"
 #include "poisson_tma2.inc"
 #include "poisson_tma3.inc"
+#include "poisson_tma4.inc"
 
 // =======================================================================================
 // Host launchers
@@ -719,10 +720,45 @@ void launch_jacobi(const LaunchCtx& L, const KArgs& a0, const double* xin, doubl
     else { if (res) CFDB_JAC(false, true); else CFDB_JAC(false, false); }
 #undef CFDB_JAC
 }
-// One-pass Red-Black SOR iteration (poisson_tma3.inc): 3-D, TMA-capable grids (nx even), single rank.
-bool rbsor_fused_available(const LaunchCtx& L) {
+// One-pass Red-Black SOR iteration, TMA-capable grids (nx even).  3-D (poisson_tma3.inc): a single rank, or z-slabs
+// with a second halo layer (>= 2 own planes, so that the layer behind a rank's edge plane is its own).  2-D
+// (poisson_tma4.inc): a single rank.
+bool rbsor_fused_available(const LaunchCtx& L, double* const* halo2) {
     const bool off = getenv("CFD_B200_NO_RB_FUSED") != nullptr;  // read per solve: tests toggle it
-    return !off && L.g.dim3 && L.tc && L.tc->usable && L.g.glo[2] && L.g.ghi[2];
+    if (off || !L.tc || !L.tc->usable) return false;
+    if (!L.g.dim3) return L.g.glo[1] && L.g.ghi[1];
+    if (L.g.glo[2] && L.g.ghi[2]) return true;
+    return halo2 && halo2[0] && halo2[1] && L.g.nz >= 4;
+}
+// 2-D: x tiles times chunks of `yc` consecutive 64 x 16 tiles; two blocks per SM, aim at >= 8 waves, 4..64 tiles
+// per block (a block's pipeline fill is one tile's load latency)
+static int rbsor_fused2d_ychunk(const LaunchCtx& L, dim3& grid) {
+    const int gx = (L.g.nx - 2 + Tile::BX - 1) / Tile::BX, ty = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
+    static const int forced = getenv("CFD_B200_YCHUNK_RB") ? atoi(getenv("CFD_B200_YCHUNK_RB")) : 0;
+    int nch = (148 * 2 * 8 + gx - 1) / gx;
+    int yc = (ty + nch - 1) / nch;
+    yc = yc < 4 ? 4 : (yc > 64 ? 64 : yc);
+    if (forced > 0) yc = forced;
+    if (yc > ty) yc = ty;
+    grid = dim3(gx, (ty + yc - 1) / yc, 1);
+    return yc;
+}
+static bool launch_rbsor_fused2d(const LaunchCtx& L, const KArgs& a0, const double* xin, double* xout, const double* rhs) {
+    const CUtensorMap *mx = L.tc->get_wide(xin), *mr = L.tc->get(rhs);
+    if (!mx || !mr) return false;
+    TmaSet<2> tm;
+    tm.m[0] = *mx;
+    tm.m[1] = *mr;
+    KArgs at = a0;
+    dim3 grid;
+    at.zchunk = rbsor_fused2d_ychunk(L, grid);
+    if ((size_t)grid.x * grid.y > L.rb_blocks) return false;
+    const bool res = (at.it == 0) || ((at.it - 1) % at.check == 0);
+    constexpr size_t SM = RbFused2D::SMEM;
+    CFDB_ONCE_PER_DEVICE(tma_optin(k_rbsor_fused2d_tma<true>, SM), tma_optin(k_rbsor_fused2d_tma<false>, SM));
+    if (res) CFDB_LAUNCH(KK_RBSOR_FUSED, L.st, (k_rbsor_fused2d_tma<true><<<grid, RbFused::THREADS, SM, L.st>>>(tm, L.g, xout, L.ctl, L.rb, at)));
+    else CFDB_LAUNCH(KK_RBSOR_FUSED, L.st, (k_rbsor_fused2d_tma<false><<<grid, RbFused::THREADS, SM, L.st>>>(tm, L.g, xout, L.ctl, L.rb, at)));
+    return true;
 }
 static int rbsor_fused_zchunk(const LaunchCtx& L, dim3& grid) {
     const int nzi = L.g.k1 - L.g.k0;
@@ -737,13 +773,22 @@ static int rbsor_fused_zchunk(const LaunchCtx& L, dim3& grid) {
     grid = dim3(gx, gy, (nzi + zc - 1) / zc);
     return zc;
 }
-bool launch_rbsor_fused(const LaunchCtx& L, const KArgs& a0, const double* xin, double* xout, const double* rhs) {
-    if (!rbsor_fused_available(L)) return false;
+bool launch_rbsor_fused(const LaunchCtx& L, const KArgs& a0, const double* xin, double* xout, const double* rhs,
+                        double* const* halo2) {
+    if (!rbsor_fused_available(L, halo2)) return false;
+    if (!L.g.dim3) return launch_rbsor_fused2d(L, a0, xin, xout, rhs);
     const CUtensorMap *mx = L.tc->get_wide(xin), *mr = L.tc->get(rhs);
     if (!mx || !mr) return false;
-    TmaSet<2> tm;
+    TmaSet<4> tm;
     tm.m[0] = *mx;
     tm.m[1] = *mr;
+    tm.m[2] = tm.m[3] = *mx;  // (never dereferenced on a side with a physical boundary)
+    for (int side = 0; side < 2; side++) {
+        if (side ? L.g.ghi[2] : L.g.glo[2]) continue;
+        const CUtensorMap* mh = L.tc->get_wide(halo2[side]);  // only plane 0 of this map exists
+        if (!mh) return false;
+        tm.m[2 + side] = *mh;
+    }
     KArgs at = a0;
     dim3 grid;
     at.zchunk = rbsor_fused_zchunk(L, grid);

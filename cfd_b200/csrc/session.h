@@ -32,6 +32,8 @@ struct Peer {
     char* peer_box[PEER_MAX_RANKS] = {};     // every rank's box as mapped here (peer_box[rank] == box)
     bool ipc_mapped[PEER_MAX_RANKS] = {};    // opened with cudaIpcOpenMemHandle (to be closed)
     size_t cnt = 0;                          // doubles per halo layer
+    double* halo2[2] = {};                   // SECOND halo layer (lo, hi) of the one-pass Red-Black SOR sweep on slabs:
+                                             // two planes at the end of the box (poisson_tma3.inc)
     size_t box_bytes = 0;
     unsigned long long hseq = 0, rseq = 0;   // exchanges / reductions issued so far (identical on every rank)
 };
@@ -83,6 +85,7 @@ struct cfd_b200_session {
     // first failure of a halo exchange / all-reduce since the last check (comm_check): a decomposed solve
     // that lost an exchange must not report success on a per-slab answer
     cfd_status_t comm_err = CFD_SUCCESS;
+    int rb_slab_ok = -1;        // one-pass Red-Black SOR on slabs: every rank has >= 2 own planes (-1: not agreed yet)
     bool gate_enabled = false;  // peer transport: the pull of an exchange may ride in the consuming kernel (HaloGate)
     int kernels_at_create = 0;
 
@@ -132,6 +135,9 @@ cfd_status_t peer_allreduce(cfd_b200_session* s, void* dev, int n, int op);  // 
 // reductions of the session on (CFD_B200_NO_FUSED_REDUCE=1: keep the stand-alone all-reduce kernel)
 cfd_status_t peer_connected(cfd_b200_session* s);
 cfd_status_t peer_halo_push_gated(cfd_b200_session* s, double* const* fields, int nf, HaloGate* gate);
+// TWO layers of one field per side: the outer one into the field's own halo layer, the one behind it into
+// Peer::halo2 (gate may be null: push + stand-alone pull)
+cfd_status_t peer_halo_exchange2(cfd_b200_session* s, double* field, HaloGate* gate);
 // all-reduce of values a reducing KERNEL has just left in Ctl: nothing to do when the kernel finished it itself
 cfd_status_t allreduce_produced(cfd_b200_session* s, double* dev, int n, bool is_max);
 cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double** x,

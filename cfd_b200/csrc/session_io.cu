@@ -232,6 +232,7 @@ cfd_status_t cfd_b200_session_set_slab(cfd_b200_session_t* s, size_t global_laye
         return CFD_ERROR_INVALID;
     }
     s->gdec = global_layers;
+    s->rb_slab_ok = -1;
     if (s->g.dim3) s->g.gk0 = (long long)global_lo;
     else s->g.gj0 = (long long)global_lo;
     // physical faces follow from the position, not from the rank number

@@ -53,11 +53,12 @@ __device__ __forceinline__ int gate_chunk(const HaloGate* hg, int b, int nb) {
     if (!hg || !hg->on || nb <= 2) return b;
     return b < nb - 2 ? b + 1 : (b == nb - 2 ? 0 : nb - 1);
 }
-// Called by ALL threads of a block before its first load.  lo / hi: the block's chunk touches the low / high halo
-// layer.  (x0, y0): origin of the block's {HX, HY} box; d3 = false: the layers are ROWS (y-slabs) and the box is a row
-// segment.  Neighbouring blocks copy overlapping cells with identical values (benign).
-__device__ __forceinline__ void halo_gate_pull(const HaloGate* hg, const Geom& g, int x0, int y0, bool lo, bool hi,
-                                               bool d3) {
+// Called by ALL threads of a block before its first load.  lo / hi: the block reads the low / high halo layer.
+// (xa, ya), bw x bh: the block's box in the layer (clipped to the grid here; the origin may be negative);
+// d3 = false: the layers are ROWS (y-slabs) and the box is a row segment.  Neighbouring blocks copy overlapping cells
+// with identical values (benign).
+__device__ __forceinline__ void halo_gate_pull_box(const HaloGate* hg, const Geom& g, int xa, int ya, int bw, int bh,
+                                                   bool lo, bool hi, bool d3) {
     if (!hg || !hg->on) return;
     const bool need0 = lo && hg->box[0], need1 = hi && hg->box[1];
     if (!need0 && !need1) return;  // (block-uniform)
@@ -70,8 +71,9 @@ __device__ __forceinline__ void halo_gate_pull(const HaloGate* hg, const Geom& g
     }
     __syncthreads();
     if (gate_ok) {
-        const int w = min(Tile::HX, g.nx - x0);
-        const int h = d3 ? min(Tile::HY, g.ny - y0) : 1;
+        const int x0 = max(xa, 0), y0 = d3 ? max(ya, 0) : 0;
+        const int w = min(xa + bw, g.nx) - x0;
+        const int h = d3 ? min(ya + bh, g.ny) - y0 : 1;
         for (int side = 0; side < 2; side++) {
             if (!(side ? need1 : need0)) continue;
             for (int f = 0; f < hg->nf; f++) {
@@ -89,6 +91,11 @@ __device__ __forceinline__ void halo_gate_pull(const HaloGate* hg, const Geom& g
     }
     __syncthreads();
     fence_proxy_async_global();  // (the thread that issues the TMA loads is one of us)
+}
+// ... for the {HX, HY} box of a tile with origin (x0, y0)
+__device__ __forceinline__ void halo_gate_pull(const HaloGate* hg, const Geom& g, int x0, int y0, bool lo, bool hi,
+                                               bool d3) {
+    halo_gate_pull_box(hg, g, x0, y0, Tile::HX, Tile::HY, lo, hi, d3);
 }
 
 // 2-D grids (nz == 1): the pipeline marches along y instead -- a block owns `ychunk` consecutive

@@ -106,6 +106,41 @@ def test_rbsor_one_pass_iteration_is_bit_exact(orc, shape, check, fused, monkeyp
     assert np.array_equal(x, xo)
 
 
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("check,cap", [(1, 24), (3, 25), (1, 3000)])
+@pytest.mark.parametrize("shape", [(130, 40), (66, 18), (200, 300), (64, 150), (258, 1030), (4, 3), (1026, 70)])
+def test_rbsor_one_pass_iteration_2d_is_bit_exact(orc, shape, check, cap, fused, monkeypatch):
+    """2-D Red-Black SOR on TMA-capable grids (nx even): one fused pass per iteration over y-chunks of 64 x 16 tiles
+    (poisson_tma4.inc) -- single-tile, multi-tile and multi-chunk shapes, capped solves and the reference's own
+    stopping rule (cap 3000: converges or not exactly as the oracle does), caller-set ghost values.  fused=False
+    forces the half-sweep kernels on the same grids."""
+    if not fused:
+        monkeypatch.setenv("CFD_B200_NO_RB_FUSED", "1")
+    else:
+        monkeypatch.delenv("CFD_B200_NO_RB_FUSED", raising=False)
+    nx, ny = shape
+    if cap > 1000 and nx * ny > 100000:
+        pytest.skip("the oracle's converging solve on this grid takes too long for the suite")
+    g, x, rhs = cases.poisson_problem(nx, ny, 1, seed=17)
+    x[0, 0, :] = 0.3  # caller-set ghost values enter the first residual and the first sweep as they are
+    kw = dict(tolerance=1e-30, absolute_tolerance=1e-300) if cap < 1000 else {}
+    pp = pparams("rbsor", max_iterations=cap, check_interval=check, **kw)
+    xo = x.copy()
+    dx, dy, dz = g.spacing
+    rc_o, st_o = orc.poisson(METH["rbsor"], nx, ny, 1, dx, dy, dz, pp, xo, rhs, np.zeros_like(x))
+    L = api.load()
+    n0 = L.cfd_b200_kernel_launch_count()
+    rc_g, st_g = gpu_solve("rbsor", g, x, rhs, pp)
+    launches = L.cfd_b200_kernel_launch_count() - n0
+    assert (rc_g, st_g.status, st_g.iterations) == (rc_o, st_o.status, st_o.iterations)
+    assert st_g.initial_residual == st_o.initial_residual and st_g.final_residual == st_o.final_residual
+    assert np.array_equal(x, xo)
+    if fused and cap < 1000:
+        assert launches <= cap + 8, launches  # one kernel per iteration (+ control block, final decision)
+    elif cap < 1000:
+        assert launches >= 2 * cap
+
+
 @pytest.mark.parametrize("cluster", ["async16", "sync8", "sync16", "async2", False])
 @pytest.mark.parametrize("check,cap", [(10, 2000), (1, 37), (3, 50), (7, 1)])
 @pytest.mark.parametrize("shape", [(129, 129), (33, 33), (130, 40), (17, 15), (3, 3), (5, 4), (200, 11), (24, 150)])

@@ -187,6 +187,12 @@ GANG_CASES = [
     ("jacobi z-slabs uneven", "projection", "jacobi", (34, 22, 29), 0.0, dict(max_iterations=30)),
     ("rbsor z-slabs uneven", "projection", "rbsor", (34, 22, 31), 0.0, dict(max_iterations=25)),
     ("rbsor y-slabs uneven", "projection", "rbsor", (36, 41, 1), 0.0, dict(max_iterations=25)),
+    # one-pass sweep on slabs (second halo layer): two own planes per rank at G = 4; 2 + 1 + 1 + 1 own planes (the
+    # ranks agree on the half-sweeps instead); the reference's own stopping rule
+    ("rbsor z-slabs two planes each", "projection", "rbsor", (34, 22, 10), 0.0, dict(max_iterations=25)),
+    ("rbsor z-slabs too thin", "projection", "rbsor", (34, 22, 7), 0.0, dict(max_iterations=25)),
+    ("rbsor z-slabs reference rule", "projection", "rbsor", (34, 22, 31), 0.0, dict(max_iterations=400)),
+    ("multi-tile rbsor z-slabs", "projection", "rbsor", (130, 34, 83), 0.0, dict(max_iterations=12)),
     ("cg z-slabs uneven", "projection", "cg", (34, 22, 29), 1e-8, dict(max_iterations=60)),
     ("pcg y-slabs", "projection", "pcg", (36, 42, 1), 1e-8, dict(max_iterations=60)),
     ("bicgstab x12 z-slabs", "projection", "bicgstab", (34, 22, 27), 1e-8, dict(max_iterations=12)),
@@ -229,7 +235,37 @@ def test_gang_behind_the_stateless_symbols_equals_the_undecomposed_oracle(clean,
         close(f, fo, tol, "%s G=%d" % (name, G))
 
 
+@pytest.mark.parametrize("G", [2, 3])
+@pytest.mark.parametrize("n,steps", [(64, 3)])
+def test_gang_c3_cavity_rbsor_one_pass_and_half_sweeps(clean, orc, monkeypatch, G, n, steps):
+    """C3 shape on slabs: lid-driven cavity, Red-Black SOR x 30, bitwise per step against the undecomposed oracle --
+    with the one-pass sweep (two-layer exchange, poisson_tma3.inc) and with the half-sweeps it replaces."""
+    _gang_or_skip(G, monkeypatch)
+    pc = abi.poisson_config("rbsor", max_iterations=30, on_nonconvergence=abi.CFD_B200_NONCONV_CONTINUE)
+    api.set_poisson(pc)
+    api.set_device_count(G)
+    for path in ("one_pass", "half_sweeps"):
+        if path == "half_sweeps":
+            monkeypatch.setenv("CFD_B200_NO_RB_FUSED", "1")
+        else:
+            monkeypatch.delenv("CFD_B200_NO_RB_FUSED", raising=False)
+        g, f, p = cases.cavity(n, n, dt=1e-4)
+        fo = f.copy()
+        slv = api.GpuSolver("projection_gpu")
+        try:
+            for step in range(steps):
+                cases.apply_cavity_bc(f)
+                cases.apply_cavity_bc(fo)
+                rc, _ = slv.step(f, g, p)
+                rco, _ = orc.projection(fo, g, p, pc, 1)
+                assert rc == rco == 0, api.last_error()
+                bitwise(f, fo, "C3 %d^3 G=%d %s step %d" % (n, G, path, step))
+        finally:
+            slv.close()
+
+
 @pytest.mark.parametrize("case", [c for c in GANG_CASES if c[0] in ("jacobi z-slabs uneven", "rbsor y-slabs uneven",
+                                                                     "rbsor z-slabs uneven",
                                                                      "multi-tile bicgstab x12", "pcg y-slabs", "rk4 z-slabs uneven")],
                          ids=lambda c: c[0].replace(" ", "_"))
 def test_gang_over_the_nccl_fallback(clean, orc, monkeypatch, case):

@@ -13,7 +13,9 @@
 #   launches     ncu launch list (gpu__time_duration.sum) of the default bench command + share summary
 #   ncu          ncu --set full of the headline kernels -> profiles-ready CSV (tools/ncu_summary.py)
 #   ncu512       ncu --set full of the 512^3 kernels that are not part of the headline
+#   ncurb        ncu --set full of the one-pass Red-Black SOR sweeps (4096^2, 256^3)
 #   c4waves      2-D pointwise kernels: blocks per launch (CFD_B200_PW_WAVES) at the C4 slab sizes
+#   rbtables     Red-Black SOR: one-pass sweeps (3-D, 2-D) against the half-sweeps, 2-D tiles per block
 #   sass         SASS opcode histogram of the shipped cubins (runs anywhere)
 TAG=$1; shift
 mkdir -p gpurun_out
@@ -39,6 +41,24 @@ for stage in "$@"; do
       n=${arg%% *}; extra=${arg#$n}; tagx=$(echo "$extra" | grep -o "config [a-z0-9]*" | tr -d " ")
       timeout 1200 bash -c "$(declare -f torchrun_); torchrun_ $n bench.py --gpus $n $extra" > ${O}_bench_${n}gpu${tagx}.json 2> ${O}_bench_${n}gpu${tagx}.err
       echo "scale exit $?"; cut -c1-500 ${O}_bench_${n}gpu${tagx}.json; grep -v "^\[rank\|^ *File\|^W1\|^E1\|^\*\*\*\|Setting OMP" ${O}_bench_${n}gpu${tagx}.err | tail -4 | cut -c1-300 ;;
+    rbtables)
+      out=${O}_rb_tables.jsonl; : > $out
+      run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
+      for shp in 4096,4096,1 1024,1024,1 256,256,256; do
+        run --shape $shp --stepper projection --method rbsor --iters 50
+        CFD_B200_NO_RB_FUSED=1 run --shape $shp --stepper projection --method rbsor --iters 50
+      done
+      for yc in 4 16 32 64; do CFD_B200_YCHUNK_RB=$yc run --shape 4096,4096,1 --stepper projection --method rbsor --iters 50; done
+      run --shape 4096,4096,1 --stepper projection --method rbsor --iters 50 --fast
+      python - $out <<'PY'
+import json, sys
+for l in open(sys.argv[1]):
+    try: d = json.loads(l)
+    except Exception: print(l[:200]); continue
+    ks = {k["kernel"]: (k["launches"], k["avg_us"], k["frac_of_measured_peak"]) for k in d.get("kernels", []) if "rb" in k["kernel"] or "redblack" in k["kernel"] or "linf" in k["kernel"]}
+    print(d.get("shape"), d.get("arithmetic"), d.get("env", ""), round(d.get("ms_per_step", 0), 3), ks)
+PY
+      ;;
     tables)
       out=${O}_kernel_tables.jsonl; : > $out
       run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
@@ -91,6 +111,21 @@ PY
       python tools/ncu_summary.py "ncu --set full --clock-control none, tools/kernel_table.py --shape 512,512,512 (jacobi, rbsor, cg, rk4, euler); $(date -u +%F) $TAG" \
           ${O}_ncu_512.csv ${O}_ncu_512.ncu-rep
       if [ $(stat -c %s ${O}_ncu_512.ncu-rep) -gt 40000000 ]; then rm ${O}_ncu_512.ncu-rep; fi ;;
+    ncurb)
+      cat > gpurun_out/prof_rb.py <<'PY'
+import subprocess, sys
+for shape in ("4096,4096,1", "256,256,256"):
+    r = subprocess.run([sys.executable, "tools/kernel_table.py", "--shape", shape, "--steps", "1", "--warmup", "1",
+                        "--stepper", "projection", "--method", "rbsor", "--iters", "4"], capture_output=True, text=True)
+    if r.returncode != 0:
+        print(r.stdout[-2000:], r.stderr[-2000:]); sys.exit(1)
+PY
+      timeout 300 python gpurun_out/prof_rb.py &&
+      timeout 900 ncu --set full --clock-control none --import-source on --target-processes all \
+          -k regex:'rbsor_fused' --launch-skip 2 -c 12 -o ${O}_ncu_rb -f python gpurun_out/prof_rb.py > ${O}_ncu_rb.log 2>&1
+      python tools/ncu_summary.py "ncu --set full --clock-control none, tools/kernel_table.py --method rbsor at 4096^2 and 256^3; $(date -u +%F) $TAG" \
+          ${O}_ncu_rb.csv ${O}_ncu_rb.ncu-rep
+      if [ $(stat -c %s ${O}_ncu_rb.ncu-rep) -gt 40000000 ]; then rm ${O}_ncu_rb.ncu-rep; fi ;;
     c4waves)
       out=${O}_c4_pw_waves.jsonl; : > $out
       for w in 6 3 2 1; do for shape in 4096,4096,1 4096,2050,1 4096,1026,1; do

@@ -99,6 +99,7 @@ def main():
                      "bytes_per_cell": k["bytes_per_cell"], "GBps": round(gbs, 1), "frac_of_measured_peak": round(gbs / peak, 4)})
     out = {"shape": [nx, ny, nz], "arithmetic": "fast" if a.fast else "exact", "stepper": a.stepper, "method": a.method, "iters": a.iters, "steps": a.steps,
            "ms_per_step": ms / a.steps, "MLUPS": nx * ny * nz * a.steps / (ms * 1e-3) / 1e6,
+           "env": {k: v for k, v in os.environ.items() if k.startswith("CFD_B200_")},
            "field_MB": 8 * nx * ny * nz / 1e6, "cache_resident": 8 * nx * ny * nz * 6 < 126e6, "kernels": rows}
     print(json.dumps(out))
 
