@@ -15,6 +15,7 @@
 #   ncu512       ncu --set full of the 512^3 kernels that are not part of the headline
 #   ncurb        ncu --set full of the one-pass Red-Black SOR sweeps (4096^2, 256^3)
 #   c4waves      2-D pointwise kernels: blocks per launch (CFD_B200_PW_WAVES) at the C4 slab sizes
+#   c3slabs:N    tools/c3_slabs.py on 1 and N GPUs: one-pass Red-Black SOR on slabs against the half-sweeps
 #   rbtables     Red-Black SOR: one-pass sweeps (3-D, 2-D) against the half-sweeps, 2-D tiles per block
 #   sass         SASS opcode histogram of the shipped cubins (runs anywhere)
 TAG=$1; shift
@@ -41,6 +42,17 @@ for stage in "$@"; do
       n=${arg%% *}; extra=${arg#$n}; tagx=$(echo "$extra" | grep -o "config [a-z0-9]*" | tr -d " ")
       timeout 1200 bash -c "$(declare -f torchrun_); torchrun_ $n bench.py --gpus $n $extra" > ${O}_bench_${n}gpu${tagx}.json 2> ${O}_bench_${n}gpu${tagx}.err
       echo "scale exit $?"; cut -c1-500 ${O}_bench_${n}gpu${tagx}.json; grep -v "^\[rank\|^ *File\|^W1\|^E1\|^\*\*\*\|Setting OMP" ${O}_bench_${n}gpu${tagx}.err | tail -4 | cut -c1-300 ;;
+    c3slabs)
+      out=${O}_c3_slabs.jsonl; : > $out
+      timeout 300 python tools/c3_slabs.py 2>/dev/null | grep '^{' >> $out
+      if [ -n "$arg" ] && [ "$arg" != "1" ]; then
+        timeout 600 bash -c "$(declare -f torchrun_); torchrun_ $arg tools/c3_slabs.py" 2>/dev/null | grep '^{' >> $out
+        timeout 600 bash -c "$(declare -f torchrun_); torchrun_ $arg tools/c3_slabs.py --n 512 --steps 5" 2>/dev/null | grep '^{' >> $out
+      fi
+      python -c "
+import json,sys
+for l in open('$out'):
+    d=json.loads(l); print(d['workload'][:22], d['n_gpus'], d['path'], d['transport'], d['ms_per_step'], [(k['kernel'],k['launches'],k['avg_us']) for k in d['kernels'][:4]])" ;;
     rbtables)
       out=${O}_rb_tables.jsonl; : > $out
       run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
