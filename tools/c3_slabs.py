@@ -97,7 +97,7 @@ def main():
         s.close()
         if rank == 0:
             print(json.dumps({"workload": "C3-shaped: %d^3 box, projection + rbsor x %d" % (n, a.iters), "path": path,
-                              "n_gpus": world, "transport": {0: "none", 1: "nccl", 2: "peer"}.get(transport),
+                              "n_gpus": world, "transport": transport,
                               "slab_planes": nloc - 2, "steps": a.steps, "ms_per_step": round(ms / a.steps, 4),
                               "MLUPS": round(n ** 3 * a.steps / (ms * 1e-3) / 1e6, 1), "kernels": rows[:6]}), flush=True)
     if td is not None:

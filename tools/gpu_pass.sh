@@ -21,7 +21,8 @@
 TAG=$1; shift
 mkdir -p gpurun_out
 O=gpurun_out/$TAG
-torchrun_() { n=$1; shift; python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500 + n)) "$@"; }
+PORT_BASE=29500
+torchrun_() { n=$1; shift; PORT_BASE=$((PORT_BASE + 17)); python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((PORT_BASE + n)) "$@"; }
 for stage in "$@"; do
   arg=${stage#*:}; [ "$arg" = "$stage" ] && arg=""
   case ${stage%%:*} in
@@ -46,8 +47,8 @@ for stage in "$@"; do
       out=${O}_c3_slabs.jsonl; : > $out
       timeout 300 python tools/c3_slabs.py 2>/dev/null | grep '^{' >> $out
       if [ -n "$arg" ] && [ "$arg" != "1" ]; then
-        timeout 600 bash -c "$(declare -f torchrun_); torchrun_ $arg tools/c3_slabs.py" 2>/dev/null | grep '^{' >> $out
-        timeout 600 bash -c "$(declare -f torchrun_); torchrun_ $arg tools/c3_slabs.py --n 512 --steps 5" 2>/dev/null | grep '^{' >> $out
+        timeout 600 bash -c "$(declare -f torchrun_); PORT_BASE=29600; torchrun_ $arg tools/c3_slabs.py" 2>/dev/null | grep '^{' >> $out
+        timeout 600 bash -c "$(declare -f torchrun_); PORT_BASE=29700; torchrun_ $arg tools/c3_slabs.py --n 512 --steps 5" 2> ${O}_c3_512.err | grep '^{' >> $out
       fi
       python -c "
 import json,sys
