@@ -730,12 +730,13 @@ bool rbsor_fused_available(const LaunchCtx& L, double* const* halo2) {
     if (L.g.glo[2] && L.g.ghi[2]) return true;
     return halo2 && halo2[0] && halo2[1] && L.g.nz >= 4;
 }
-// 2-D: x tiles times chunks of `yc` consecutive 64 x 16 tiles; two blocks per SM, aim at >= 8 waves, 4..64 tiles
-// per block (a block's pipeline fill is one tile's load latency)
+// 2-D: x tiles times chunks of `yc` consecutive 64 x 16 tiles; two blocks per SM, aim at >= 4 waves, 4..64 tiles
+// per block (a block's pipeline fill is one tile's load latency; 4096^2: 143 / 122 / 113 / 124 / 128 us per sweep
+// with 4 / 7 / 16 / 32 / 64 tiles per block)
 static int rbsor_fused2d_ychunk(const LaunchCtx& L, dim3& grid) {
     const int gx = (L.g.nx - 2 + Tile::BX - 1) / Tile::BX, ty = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
     static const int forced = getenv("CFD_B200_YCHUNK_RB") ? atoi(getenv("CFD_B200_YCHUNK_RB")) : 0;
-    int nch = (148 * 2 * 8 + gx - 1) / gx;
+    int nch = (148 * 2 * 4 + gx - 1) / gx;
     int yc = (ty + nch - 1) / nch;
     yc = yc < 4 ? 4 : (yc > 64 ? 64 : yc);
     if (forced > 0) yc = forced;
@@ -764,10 +765,29 @@ static int rbsor_fused_zchunk(const LaunchCtx& L, dim3& grid) {
     const int nzi = L.g.k1 - L.g.k0;
     const int gx = (L.g.nx - 2 + Tile::BX - 1) / Tile::BX, gy = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
     static const int forced = getenv("CFD_B200_ZCHUNK_RB") ? atoi(getenv("CFD_B200_ZCHUNK_RB")) : 0;
-    // one block per SM (154 KB of shared memory): aim at >= 10 waves (measured flat between 64 and 128 planes), 16..128 planes per block
-    int nch = (148 * 10 + gx * gy - 1) / (gx * gy);
-    int zc = (nzi + nch - 1) / nch;
-    zc = zc < 16 ? 16 : (zc > 128 ? 128 : zc);
+    // One block per SM (154 KB of shared memory).  A block of zc planes runs zc + 4 pipeline steps after ~1 step of
+    // load latency, and the last wave of blocks is rarely full: choose the chunk count (16..128 planes per block)
+    // that maximises  blocks / (waves * 148)  *  zc / (zc + 5).  256^3: 9 chunks of 29 planes (measured 166 us per
+    // sweep against 176 with 16 chunks of 16); 512^3 and up: 128 planes (measured flat between 64 and 128).
+    int zc = nzi;
+    {
+        const int tiles = gx * gy;
+        const int n_lo = (nzi + 127) / 128, n_hi = nzi / 16 > n_lo ? nzi / 16 : n_lo;
+        double best = -1.0;
+        // (from many short chunks to few long ones; a longer chunk must win by 2 %: neighbouring blocks of short
+        // chunks stay within a few planes of each other and share their halo rows in L2)
+        for (int nch = n_hi; nch >= n_lo; nch--) {
+            const int c = (nzi + nch - 1) / nch;
+            const int real = (nzi + c - 1) / c;  // chunks that length gives
+            const long long blocks = (long long)tiles * real;
+            const long long waves = (blocks + 147) / 148;
+            const double eff = (double)blocks / (double)(waves * 148) * (double)c / (double)(c + 5);
+            if (eff > best + 0.02) {
+                best = eff;
+                zc = c;
+            }
+        }
+    }
     if (forced > 0) zc = forced;
     if (zc > nzi) zc = nzi;
     grid = dim3(gx, gy, (nzi + zc - 1) / zc);

@@ -54,6 +54,17 @@ for stage in "$@"; do
 import json,sys
 for l in open('$out'):
     d=json.loads(l); print(d['workload'][:22], d['n_gpus'], d['path'], d['transport'], d['ms_per_step'], [(k['kernel'],k['launches'],k['avg_us']) for k in d['kernels'][:4]])" ;;
+    rbzc)
+      out=${O}_rb_zchunk.jsonl; : > $out
+      run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
+      for shp in 256,256,129 256,256,256 512,512,257; do
+        run --shape $shp --stepper projection --method rbsor --iters 50
+        for zc in 16 19 22 26 32 43 64 127; do CFD_B200_ZCHUNK_RB=$zc run --shape $shp --stepper projection --method rbsor --iters 50; done
+      done
+      python -c "
+import json
+for l in open('$out'):
+    d=json.loads(l); k=[k for k in d['kernels'] if 'rbsor' in k['kernel']][0]; print(d['shape'], d['env'].get('CFD_B200_ZCHUNK_RB','default'), k['avg_us'], k['frac_of_measured_peak'])" ;;
     rbtables)
       out=${O}_rb_tables.jsonl; : > $out
       run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
@@ -61,8 +72,10 @@ for l in open('$out'):
         run --shape $shp --stepper projection --method rbsor --iters 50
         CFD_B200_NO_RB_FUSED=1 run --shape $shp --stepper projection --method rbsor --iters 50
       done
-      for yc in 4 16 32 64; do CFD_B200_YCHUNK_RB=$yc run --shape 4096,4096,1 --stepper projection --method rbsor --iters 50; done
+      for yc in 16; do CFD_B200_YCHUNK_RB=$yc run --shape 4096,4096,1 --stepper projection --method rbsor --iters 50; done
       run --shape 4096,4096,1 --stepper projection --method rbsor --iters 50 --fast
+      for zc in 29; do CFD_B200_ZCHUNK_RB=$zc run --shape 256,256,256 --stepper projection --method rbsor --iters 50; done
+      run --shape 512,512,512 --stepper projection --method rbsor --iters 50
       python - $out <<'PY'
 import json, sys
 for l in open(sys.argv[1]):
