@@ -185,3 +185,36 @@ def host_halo_exchange(arr, rank, nranks, periodic_ring=False):
             w.wait()
     for i, r in recv:
         arr[layer(i)] = r.numpy()
+
+
+def host_halo_exchange2(arr, rank, nranks):
+    """CPU restatement of peer_halo_exchange2 (csrc/peer.cu): the usual one-layer exchange of `arr` plus the layer
+    BEHIND each neighbour's edge layer, returned as (lo2, hi2) -- None on a side without a neighbour.  The one-pass
+    Red-Black SOR sweep on slabs reads x two layers deep (csrc/poisson_tma3.inc)."""
+    import torch
+    import torch.distributed as td
+    ax = dec_axis(arr.shape[0])
+    n = arr.shape[ax]
+
+    def layer(i):
+        sl = [slice(None)] * 3
+        sl[ax] = i
+        return tuple(sl)
+
+    host_halo_exchange(arr, rank, nranks)
+    lo, hi = rank - 1, rank + 1
+    ops, got = [], {}
+    if 0 <= lo < nranks:
+        ops.append(td.P2POp(td.isend, torch.from_numpy(np.ascontiguousarray(arr[layer(2)])), lo))
+    if 0 <= hi < nranks:
+        ops.append(td.P2POp(td.isend, torch.from_numpy(np.ascontiguousarray(arr[layer(n - 3)])), hi))
+        got["hi"] = torch.empty_like(torch.from_numpy(np.ascontiguousarray(arr[layer(0)])))
+        ops.append(td.P2POp(td.irecv, got["hi"], hi))
+    if 0 <= lo < nranks:
+        got["lo"] = torch.empty_like(torch.from_numpy(np.ascontiguousarray(arr[layer(0)])))
+        ops.append(td.P2POp(td.irecv, got["lo"], lo))
+    if ops:
+        for w in td.batch_isend_irecv(ops):
+            w.wait()
+    return (got["lo"].numpy() if "lo" in got else None, got["hi"].numpy() if "hi" in got else None)
+

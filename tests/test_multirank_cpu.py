@@ -47,6 +47,63 @@ def _jacobi_sweep(x, rhs, dx, dy, dz, phys_lo, phys_hi):
     return new
 
 
+def _rb_relax(x, rhs, mask, dx, dy, dz, omega):
+    """x + omega (pn - x) on the interior cells selected by `mask` (cpu/linear_solver_redblack.c:107-121)."""
+    ix, iy, iz = 1.0 / (dx * dx), 1.0 / (dy * dy), 1.0 / (dz * dz)
+    inv = 1.0 / (2.0 * (ix + iy + iz))
+    c = (slice(1, -1), slice(1, -1), slice(1, -1))
+    pn = -(rhs[c] - (x[1:-1, 1:-1, 2:] + x[1:-1, 1:-1, :-2]) * ix - (x[1:-1, 2:, 1:-1] + x[1:-1, :-2, 1:-1]) * iy
+           - (x[2:, 1:-1, 1:-1] + x[:-2, 1:-1, 1:-1]) * iz) * inv
+    new = x.copy()
+    new[c] = np.where(mask[c], x[c] + omega * (pn - x[c]), x[c])
+    return new
+
+
+def _colour(shape, k0):
+    """(i + j + k) & 1 with GLOBAL k = k0 + local k."""
+    nz, ny, nx = shape
+    return ((np.arange(nz)[:, None, None] + k0 + np.arange(ny)[None, :, None] + np.arange(nx)[None, None, :]) & 1)
+
+
+def _neumann_xy(x):
+    x[:, :, 0], x[:, :, -1] = x[:, :, 1], x[:, :, -2]
+    x[:, 0, :], x[:, -1, :] = x[:, 1, :], x[:, -2, :]
+
+
+def _rb_global(x, rhs, dx, dy, dz, omega):
+    """The reference's iteration: odd half-sweep, even half-sweep (in place), then the Neumann ghosts."""
+    col = _colour(x.shape, 0)
+    x = _rb_relax(x, rhs, col == 1, dx, dy, dz, omega)
+    x = _rb_relax(x, rhs, col == 0, dx, dy, dz, omega)
+    _neumann_xy(x)
+    x[0], x[-1] = x[1], x[-2]
+    return x
+
+
+def _rb_slab_one_pass(x, rhs, lo2, hi2, k0, dx, dy, dz, omega):
+    """The one-pass sweep on a z-slab as poisson_tma3.inc does it: stage A (odd cells) on the own planes AND on the
+    neighbour's edge plane (the halo layer), which needs the layer behind it (lo2 / hi2); stage B (even cells) on
+    the own planes from stage A's results; ghosts; out of place.  Halo layers of the result come from the exchange."""
+    zero = np.zeros_like(x[0])
+    ext = np.concatenate([(lo2 if lo2 is not None else zero)[None], x, (hi2 if hi2 is not None else zero)[None]])
+    rext = np.concatenate([zero[None], rhs, zero[None]])
+    col = _colour(ext.shape, k0 - 1)
+    a_planes = np.zeros(ext.shape, bool)
+    a_planes[2:-2] = True                 # own planes
+    a_planes[1] = lo2 is not None         # the lo neighbour's edge plane (my halo layer)
+    a_planes[-2] = hi2 is not None
+    R = _rb_relax(ext, rext, (col == 1) & a_planes, dx, dy, dz, omega)
+    b_planes = np.zeros(ext.shape, bool)
+    b_planes[2:-2] = True
+    new = _rb_relax(R, rext, (col == 0) & b_planes, dx, dy, dz, omega)[1:-1]
+    _neumann_xy(new)
+    if lo2 is None:
+        new[0] = new[1]
+    if hi2 is None:
+        new[-1] = new[-2]
+    return new
+
+
 def _worker(rank, world, port, shape, out):
     import torch.distributed as td
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -114,6 +171,27 @@ def _worker(rank, world, port, shape, out):
         inner = [slice(None)] * 3
         inner[ax] = slice(1, -1)
         assert float(t) == np.max(np.abs(xg[tuple(inner)]))
+        # 7. one-pass Red-Black SOR on slabs (two-layer exchange once per iteration) == the reference's two half-sweeps
+        #    on the undecomposed grid, bitwise
+        if ax == 0:
+            omega = 1.6
+            xg, xl = gf.p.copy(), loc.p.copy()
+            _neumann_xy(xg)
+            xg[0], xg[-1] = xg[1], xg[-2]
+            xl = xg[lo:hi].copy()
+            for _ in range(3):
+                lo2, hi2 = dist.host_halo_exchange2(xl, rank, world)
+                if rank > 0:
+                    np.testing.assert_array_equal(lo2, xg[lo - 1])
+                if rank < world - 1:
+                    np.testing.assert_array_equal(hi2, xg[hi])
+                xg_new = _rb_global(xg.copy(), rg, dx, dy, dz, omega)
+                xl = _rb_slab_one_pass(xl, rl, lo2, hi2, lo, dx, dy, dz, omega)
+                own = slice(1, -1)
+                np.testing.assert_array_equal(xl[own], xg_new[lo:hi][own])
+                xg = xg_new
+            dist.host_halo_exchange(xl, rank, world)
+            np.testing.assert_array_equal(xl, xg[lo:hi])
         out.put((rank, "ok"))
     except Exception as e:  # pragma: no cover - reported to the parent
         import traceback
