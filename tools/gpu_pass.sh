@@ -13,6 +13,8 @@
 #   launches     ncu launch list (gpu__time_duration.sum) of the default bench command + share summary
 #   ncu          ncu --set full of the headline kernels -> profiles-ready CSV (tools/ncu_summary.py)
 #   ncu512       ncu --set full of the 512^3 kernels that are not part of the headline
+#   c4tables     kernel tables of the CG / PCG paths at 4096^2 and 512^3
+#   ncuc4        ncu --set full of the C4 kernels (4096^2, PCG + energy)
 #   ncurb        ncu --set full of the one-pass Red-Black SOR sweeps (4096^2, 256^3)
 #   c4waves      2-D pointwise kernels: blocks per launch (CFD_B200_PW_WAVES) at the C4 slab sizes
 #   c3slabs:N    tools/c3_slabs.py on 1 and N GPUs: one-pass Red-Black SOR on slabs against the half-sweeps
@@ -54,6 +56,17 @@ for stage in "$@"; do
 import json,sys
 for l in open('$out'):
     d=json.loads(l); print(d['workload'][:22], d['n_gpus'], d['path'], d['transport'], d['ms_per_step'], [(k['kernel'],k['launches'],k['avg_us']) for k in d['kernels'][:4]])" ;;
+    c4tables)
+      out=${O}_c4_tables.jsonl; : > $out
+      run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
+      run --shape 4096,4096,1 --stepper projection --method pcg --iters 50 --energy
+      run --shape 4096,4096,1 --stepper projection --method cg --iters 50
+      run --shape 512,512,512 --stepper projection --method cg --iters 50
+      run --shape 512,512,512 --stepper projection --method pcg --iters 50
+      python -c "
+import json
+for l in open('$out'):
+    d=json.loads(l); print(d['shape'], d['method'], round(d['ms_per_step'],3), [(k['kernel'],k['avg_us'],k['frac_of_measured_peak']) for k in d['kernels'][:3]])" ;;
     rbzc)
       out=${O}_rb_zchunk.jsonl; : > $out
       run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
@@ -137,6 +150,20 @@ PY
       python tools/ncu_summary.py "ncu --set full --clock-control none, tools/kernel_table.py --shape 512,512,512 (jacobi, rbsor, cg, rk4, euler); $(date -u +%F) $TAG" \
           ${O}_ncu_512.csv ${O}_ncu_512.ncu-rep
       if [ $(stat -c %s ${O}_ncu_512.ncu-rep) -gt 40000000 ]; then rm ${O}_ncu_512.ncu-rep; fi ;;
+    ncuc4)
+      cat > gpurun_out/prof_c4.py <<'PY'
+import subprocess, sys
+r = subprocess.run([sys.executable, "tools/kernel_table.py", "--shape", "4096,4096,1", "--steps", "1", "--warmup", "1",
+                    "--stepper", "projection", "--method", "pcg", "--iters", "4", "--energy"], capture_output=True, text=True)
+if r.returncode != 0:
+    print(r.stdout[-2000:], r.stderr[-2000:]); sys.exit(1)
+PY
+      timeout 300 python gpurun_out/prof_c4.py &&
+      timeout 900 ncu --set full --clock-control none --import-source on --target-processes all \
+          -k regex:'cg_update|cg_dir_tma|predictor_tma|corrector_tma|krylov_init|k_copy|field_stats' --launch-skip 4 -c 14 -o ${O}_ncu_c4 -f python gpurun_out/prof_c4.py > ${O}_ncu_c4.log 2>&1
+      python tools/ncu_summary.py "ncu --set full --clock-control none, tools/kernel_table.py --shape 4096,4096,1 --method pcg --energy (C4 kernels); $(date -u +%F) $TAG" \
+          ${O}_ncu_c4.csv ${O}_ncu_c4.ncu-rep
+      if [ $(stat -c %s ${O}_ncu_c4.ncu-rep) -gt 40000000 ]; then rm ${O}_ncu_c4.ncu-rep; fi ;;
     ncurb)
       cat > gpurun_out/prof_rb.py <<'PY'
 import subprocess, sys
