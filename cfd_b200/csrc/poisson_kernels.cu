@@ -16,6 +16,7 @@
 #include "stencil_tma.cuh"
 
 #include <limits.h>
+#include <type_traits>
 
 namespace cfdb {
 CFDB_ARITH_BEGIN
