@@ -253,8 +253,8 @@ static inline dim3 blk2() { return dim3(TX, TY); }
 static inline dim3 tma_grid2(const LaunchCtx& L) {
     const int nzi = L.g.k1 - L.g.k0, ty = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
     if (!L.g.dim3)  // 2-D: zchunk_tma counts tiles along y
-        return dim3((L.g.nx - 2 + Tile::BX - 1) / Tile::BX, (ty + L.zchunk_tma - 1) / L.zchunk_tma, 1);
-    return dim3((L.g.nx - 2 + Tile::BX - 1) / Tile::BX, ty, (nzi + L.zchunk_tma - 1) / L.zchunk_tma);
+        return dim3(Tile::GX(L.g.nx), (ty + L.zchunk_tma - 1) / L.zchunk_tma, 1);
+    return dim3(Tile::GX(L.g.nx), ty, (nzi + L.zchunk_tma - 1) / L.zchunk_tma);
 }
 template <int N>
 static inline bool tma_maps2(const LaunchCtx& L, const double* const (&ptr)[N], TmaSet<N>& out) {

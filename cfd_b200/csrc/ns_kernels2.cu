@@ -247,12 +247,12 @@ k_rk_stage_tma(const __grid_constant__ TmaSet<4> tm, Geom g, NsConst c, RkArgs r
                const double* __restrict__ su_tab, const double* __restrict__ sv_tab, Ctl* ctl) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int tid = threadIdx.x;
-    const int i = blockIdx.x * Tile::BX + 1 + (tid & (Tile::BX - 1)), y0 = blockIdx.y * Tile::BY;
+    const int i = Tile::X0(blockIdx.x) + Tile::XO + (tid & (Tile::BX - 1)), y0 = blockIdx.y * Tile::BY;
     const int j0 = y0 + 1 + (tid >> 6);
     RkOp<D3> op{g, c, ra, q0, acc, qout, rho, T, su_tab, sv_tab,
                 reinterpret_cast<double*>(smem_raw + RkStage::OFFSET) + tid,
                 min(g.k0 + ((int)blockIdx.z + 1) * zchunk, g.k1), y0,
-                (i < g.nx - 1) && (j0 + 8 < g.ny - 1), false};
+                (i >= 1) && (i < g.nx - 1) && (j0 + 8 < g.ny - 1), false};
     tma_direct_sweep<D3>(tm, g, zchunk, op);
     if (op.bad && ra.last) ctl->nonfinite = 1;
 }

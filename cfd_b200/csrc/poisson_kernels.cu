@@ -252,12 +252,15 @@ k_linf_residual(Geom g, const double* __restrict__ x, const double* __restrict__
 constexpr int PW_THREADS = 256;
 template <class F>
 __device__ __forceinline__ void pointwise_rows(const Geom& g, int rpb, F f) {
-    const int i = 1 + blockIdx.x * PW_THREADS + threadIdx.x;
+    // x tiles start at i = 0 (thread 0 of the first tile idles on the boundary cell): a warp's 256-byte accesses then
+    // start on a 256-byte boundary.  Stores that start one element off it run at 0.6 of the aligned rate on this GPU
+    // (tools/copy_probe.cu, profiles/r2z_copy_probe.jsonl).
+    const int i = blockIdx.x * PW_THREADS + threadIdx.x;
     const int nyi = g.ny - 2;
     const long long rows = (long long)nyi * (g.k1 - g.k0);
     const long long r0 = (long long)blockIdx.y * rpb;
     const long long r1 = r0 + rpb < rows ? r0 + rpb : rows;
-    if (i >= g.nx - 1) return;
+    if (i < 1 || i >= g.nx - 1) return;
     int j = 1 + (int)(r0 % nyi), k = g.k0 + (int)(r0 / nyi);
     long long n = (long long)k * g.sz + (long long)j * g.sy + i;
 #pragma unroll 4
@@ -304,10 +307,10 @@ __device__ __forceinline__ void pointwise_cells_batched(const Geom& g, int chunk
         stride = g.sz;
         count = ke - kb;
     } else {  // (2-D grids only: the rows of a chunk are consecutive rows of the one plane)
-        const int i = 1 + blockIdx.x * PW_THREADS + threadIdx.x;
+        const int i = blockIdx.x * PW_THREADS + threadIdx.x;  // (aligned x tiles, see pointwise_rows)
         const int nyi = g.ny - 2;
         const int r0 = blockIdx.y * chunk, r1 = min(r0 + chunk, nyi);
-        if (i >= g.nx - 1 || r0 >= r1) return;
+        if (i < 1 || i >= g.nx - 1 || r0 >= r1) return;
         n = (long long)(1 + r0) * g.sy + i;
         stride = g.sy;
         count = r1 - r0;
@@ -711,7 +714,7 @@ static inline dim3 blk() { return dim3(TX, TY); }
 // grid of the pointwise sweeps: x tiles of PW_THREADS cells, row chunks sized for ~6 waves of
 // 148 x 8 blocks, never more blocks than the partial-sum buffer has rows
 static inline dim3 pw_grid(const LaunchCtx& L, int& rpb) {
-    const long long xt = (L.g.nx - 2 + PW_THREADS - 1) / PW_THREADS;
+    const long long xt = (L.g.nx - 1 + PW_THREADS - 1) / PW_THREADS;  // tiles from i = 0 up to i = nx - 2
     const long long rows = (long long)(L.g.ny - 2) * (L.g.k1 - L.g.k0);
     static const int waves = [] {  // tuning knob (default 6 waves of 148 x 8 blocks)
         const char* e = getenv("CFD_B200_PW_WAVES");
@@ -777,7 +780,7 @@ bool rbsor_fused_available(const LaunchCtx& L, double* const* halo2) {
 // per block (a block's pipeline fill is one tile's load latency; 4096^2: 143 / 122 / 113 / 124 / 128 us per sweep
 // with 4 / 7 / 16 / 32 / 64 tiles per block)
 static int rbsor_fused2d_ychunk(const LaunchCtx& L, dim3& grid) {
-    const int gx = (L.g.nx - 2 + Tile::BX - 1) / Tile::BX, ty = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
+    const int gx = Tile::GX(L.g.nx), ty = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
     static const int forced = getenv("CFD_B200_YCHUNK_RB") ? atoi(getenv("CFD_B200_YCHUNK_RB")) : 0;
     int nch = (148 * 2 * 4 + gx - 1) / gx;
     int yc = (ty + nch - 1) / nch;
@@ -806,7 +809,7 @@ static bool launch_rbsor_fused2d(const LaunchCtx& L, const KArgs& a0, const doub
 }
 static int rbsor_fused_zchunk(const LaunchCtx& L, dim3& grid) {
     const int nzi = L.g.k1 - L.g.k0;
-    const int gx = (L.g.nx - 2 + Tile::BX - 1) / Tile::BX, gy = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
+    const int gx = Tile::GX(L.g.nx), gy = (L.g.ny - 2 + Tile::BY - 1) / Tile::BY;
     static const int forced = getenv("CFD_B200_ZCHUNK_RB") ? atoi(getenv("CFD_B200_ZCHUNK_RB")) : 0;
     // One block per SM (154 KB of shared memory).  A block of zc planes runs zc + 4 pipeline steps after ~1 step of
     // load latency, and the last wave of blocks is rarely full: choose the chunk count (16..128 planes per block)

@@ -214,7 +214,7 @@ cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
         if (s->rb_blocks < 148 * 16) s->rb_blocks = 148 * 16;
         // TMA kernels: 64x16 tiles, 2 blocks per SM; aim at >= 8 waves but keep chunks >= 32 planes
         // (each chunk re-reads 2 planes in its prologue)
-        const long long ttiles = (long long)((s->g.nx - 2 + Tile::BX - 1) / Tile::BX) * ((s->g.ny - 2 + Tile::BY - 1) / Tile::BY);
+        const long long ttiles = (long long)(Tile::GX(s->g.nx)) * ((s->g.ny - 2 + Tile::BY - 1) / Tile::BY);
         // Short chunks win (measured at 1024^3: 32 planes -> 1.03 of the copy peak for bicg_dir, 341
         // planes -> 0.85): blocks of one x-y neighbourhood stay within a few planes of each other, so
         // the halo rows they share are still in L2.  32 planes cost 6 % prologue re-reads; small grids
@@ -250,7 +250,7 @@ cfd_b200_session_t* cfd_b200_session_create(const cfd_b200_session_desc_t* d) {
         s->zchunk_tma1 = (int)(zc1 < 1 ? 1 : zc1);
         if (!s->g.dim3) {
             // 2-D: the TMA kernels march along y; zchunk_tma = tiles of 16 rows per block
-            const long long tx = (s->g.nx - 2 + Tile::BX - 1) / Tile::BX, ty = (s->g.ny - 2 + Tile::BY - 1) / Tile::BY;
+            const long long tx = Tile::GX(s->g.nx), ty = (s->g.ny - 2 + Tile::BY - 1) / Tile::BY;
             const long long nch2 = (148LL * 2 * 4 + tx - 1) / tx;
             long long yc = (ty + nch2 - 1) / nch2;
             if (yc > 32) yc = 32;

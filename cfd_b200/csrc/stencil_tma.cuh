@@ -110,7 +110,7 @@ __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, co
     double* ring = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(ring + DirectPipe<NF>::RING);
     const int tid = threadIdx.x;
-    const int x0 = blockIdx.x * Tile::BX;
+    const int x0 = Tile::X0(blockIdx.x);  // box origin; own cells start XO columns to the right
     const int tiles_y = (g.ny - 2 + Tile::BY - 1) / Tile::BY;
     const int ty0 = gate_chunk(hg, blockIdx.y, gridDim.y) * ychunk;
     const int nt = min(ychunk, tiles_y - ty0);
@@ -149,8 +149,8 @@ __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, co
     }
     const int lane = tid & 31;
     const int lx = tid & (Tile::BX - 1), ly = tid >> 6;
-    const int i = x0 + 1 + lx;
-    const bool actx = i < g.nx - 1;
+    const int i = x0 + Tile::XO + lx;
+    const bool actx = (i >= 1) && (i < g.nx - 1);
     int o[2];
 #pragma unroll
     for (int c = 0; c < 2; c++) o[c] = Tile::OWN0(lx, ly + 8 * c);
@@ -211,7 +211,7 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
     double* ring = reinterpret_cast<double*>(smem_raw);                          // [ST][NF][PP]
     uint64_t* full = reinterpret_cast<uint64_t*>(ring + DirectPipe<NF>::RING);  // [ST]
     const int tid = threadIdx.x;
-    const int x0 = blockIdx.x * Tile::BX, y0 = blockIdx.y * Tile::BY;
+    const int x0 = Tile::X0(blockIdx.x), y0 = blockIdx.y * Tile::BY;  // box origin
     const int kb = g.k0 + gate_chunk(hg, blockIdx.z, gridDim.z) * zchunk, ke = min(kb + zchunk, g.k1);
     const int np = ke - kb + 2;  // planes kb-1 .. ke
     const int pz0 = kb - 1;
@@ -250,7 +250,7 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
     }
     const int lane = tid & 31;
     const int lx = tid & (Tile::BX - 1), ly = tid >> 6;
-    const int i = x0 + 1 + lx;
+    const int i = x0 + Tile::XO + lx;
     int o[2], j[2];
     bool act[2];
     long long n[2];
@@ -258,7 +258,7 @@ __device__ __forceinline__ void tma_direct_sweep(const TmaSet<Op::NF>& tm, const
     for (int c = 0; c < 2; c++) {
         o[c] = Tile::OWN0(lx, ly + 8 * c);
         j[c] = y0 + 1 + ly + 8 * c;
-        act[c] = (i < g.nx - 1) && (j[c] < g.ny - 1);
+        act[c] = (i >= 1) && (i < g.nx - 1) && (j[c] < g.ny - 1);
         n[c] = (long long)kb * g.sz + (long long)j[c] * g.sy + i;
     }
     double zm[2][NF], zc[2][NF];  // z-1 and centre values of the own cells, carried in registers

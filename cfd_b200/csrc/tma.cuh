@@ -14,31 +14,48 @@
 
 namespace cfdb {
 
+// Where a tile's own cells start.  I0 = 0 (default): tile b owns the columns i = b*BX .. b*BX+BX-1, so the 256 bytes a
+// warp stores per row start on a 256-byte boundary (the thread on the boundary column i = 0 idles).  A write-only
+// stream whose warps start ONE element off that boundary runs at 0.6 of the aligned rate on this GPU
+// (tools/copy_probe.cu, profiles/r2z_copy_probe.jsonl: 3.9 against 6.3 TB/s for the tile-row pattern of these
+// kernels).  The price: the box has to start on an even column (TMA coordinate rule, below), i.e. two columns left
+// of the own cells, and is one column wider than the stencil needs.  I0 = 1 is the round-1 geometry (own cells
+// start at b*BX + 1, the first interior column; box = tile + one halo column each side), kept for A/B builds.
+#ifndef CFDB_TILE_I0
+#define CFDB_TILE_I0 0
+#endif
 struct Tile {
     static constexpr int BX = 64, BY = 16;            // interior cells per block and plane
-    static constexpr int HX = BX + 2, HY = BY + 2;    // box with halo
-    static constexpr int PLANE = HX * HY;             // doubles per operand plane (1188)
-    static constexpr int PLANE_PAD = 1200;            // padded so every plane starts 128-B aligned
+    static constexpr int I0 = CFDB_TILE_I0;           // own column 0 of tile b is global column b*BX + I0
+    static constexpr int XO = 2 - I0;                 // ... and sits in column XO of the box
+    static constexpr int HX = BX + 2 * XO, HY = BY + 2;  // box with halo
+    static constexpr int PLANE = HX * HY;             // doubles per operand plane
+    static constexpr int PLANE_PAD = (PLANE + 15) / 16 * 16;  // padded so every plane starts 128-B aligned
     static constexpr int PLANE_BYTES = PLANE * 8;     // bytes the TMA delivers per operand plane
     static constexpr int THREADS = 512;               // 2 cells per thread: rows ly and ly + 8
     static constexpr int WARPS = THREADS / 32;
     static constexpr int THREADS_PW = THREADS + 32;   // + one producer warp (stencil_tma.cuh)
-    __host__ __device__ static constexpr int OWN0(int lx, int ly) { return (ly + 1) * HX + lx + 1; }
+    __host__ __device__ static constexpr int OWN0(int lx, int ly) { return (ly + 1) * HX + lx + XO; }
+    __host__ __device__ static constexpr int X0(int b) { return b * BX + I0 - XO; }   // box origin (even)
+    __host__ __device__ static constexpr int GX(int nx) { return (nx - 1 - I0 + BX - 1) / BX; }  // tiles along x
+    __host__ __device__ static constexpr int GY(int ny) { return (ny - 2 + BY - 1) / BY; }
 };
 static_assert((Tile::HX * 8) % 16 == 0, "TMA box rows must be a multiple of 16 bytes");
 static_assert((Tile::PLANE_PAD * 8) % 128 == 0, "TMA destinations must stay 128-byte aligned");
+static_assert((Tile::I0 - Tile::XO) % 2 == 0, "box origins must be even columns");
 
 // Box with a TWO-cell halo, for sweeps that apply two dependent stencil stages per pass
-// (poisson_tma3.inc): stage 1 is evaluated on the HX x HY ring-extended tile, stage 2 on the tile.
+// (poisson_tma3.inc): stage 1 is evaluated on the tile plus a one-cell ring, stage 2 on the tile.
 // The innermost start coordinate of a TMA box must be 16-byte aligned (FP64: EVEN -- an odd x
-// start raises "illegal instruction" on sm_100a, measured; negative starts are fine), so the box
-// starts THREE cells left of the first own cell and is BX + 6 wide.
+// start raises "illegal instruction" on sm_100a, measured; negative starts are fine), so the box starts at the
+// even column b*BX - 2: XOFF = 2 + I0 cells left of the first own cell.
 struct WideTile {
-    static constexpr int WX = Tile::BX + 6, WY = Tile::BY + 4;
-    static constexpr int XOFF = 3, YOFF = 2;       // own cell (lx, ly) sits at (ly + YOFF) * WX + lx + XOFF
-    static constexpr int PLANE = WX * WY;          // 1400 doubles
-    static constexpr int PLANE_PAD = 1408;         // 88 * 128 bytes
+    static constexpr int XOFF = 2 + Tile::I0, YOFF = 2;   // own cell (lx, ly) sits at (ly + YOFF) * WX + lx + XOFF
+    static constexpr int WX = Tile::BX + 2 * XOFF, WY = Tile::BY + 4;
+    static constexpr int PLANE = WX * WY;
+    static constexpr int PLANE_PAD = (PLANE + 15) / 16 * 16;
     static constexpr int PLANE_BYTES = PLANE * 8;
+    __host__ __device__ static constexpr int X0(int b) { return b * Tile::BX + Tile::I0 - XOFF; }
 };
 static_assert((WideTile::WX * 8) % 16 == 0 && (WideTile::PLANE_PAD * 8) % 128 == 0, "wide box alignment");
 

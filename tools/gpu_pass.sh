@@ -13,6 +13,7 @@
 #   launches     ncu launch list (gpu__time_duration.sum) of the default bench command + share summary
 #   ncu          ncu --set full of the headline kernels -> profiles-ready CSV (tools/ncu_summary.py)
 #   ncu512       ncu --set full of the 512^3 kernels that are not part of the headline
+#   abtile       kernel tables with the shipped library and with the legacy tile geometry (libcfd_b200_legacy.so)
 #   c4tables     kernel tables of the CG / PCG paths at 4096^2 and 512^3
 #   ncuc4        ncu --set full of the C4 kernels (4096^2, PCG + energy)
 #   ncurb        ncu --set full of the one-pass Red-Black SOR sweeps (4096^2, 256^3)
@@ -56,6 +57,42 @@ for stage in "$@"; do
 import json,sys
 for l in open('$out'):
     d=json.loads(l); print(d['workload'][:22], d['n_gpus'], d['path'], d['transport'], d['ms_per_step'], [(k['kernel'],k['launches'],k['avg_us']) for k in d['kernels'][:4]])" ;;
+    abtile)
+      # A/B of the tile geometry: the shipped library (own cells of a tile start on a 512-byte boundary) against
+      # cfd_b200/libcfd_b200_legacy.so (built with -DCFDB_TILE_I0=1: the round-1 geometry, one element off it)
+      out=${O}_ab_tile.jsonl; : > $out
+      run() { timeout 200 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
+      cp cfd_b200/libcfd_b200.so gpurun_out/_new.so
+      for which in aligned legacy; do
+        if [ $which = legacy ]; then cp cfd_b200/libcfd_b200_legacy.so cfd_b200/libcfd_b200.so; fi
+        echo "{\"library\": \"$which\"}" >> $out
+        run --shape 1024,1024,1024 --stepper projection --method bicgstab --iters 10 --steps 1 --warmup 1
+        run --shape 512,512,512 --stepper rk4
+        run --shape 512,512,512 --stepper projection --method jacobi --iters 50
+        run --shape 512,512,512 --stepper projection --method rbsor --iters 50
+        run --shape 512,512,512 --stepper projection --method cg --iters 50 --energy
+        run --shape 4096,4096,1 --stepper projection --method pcg --iters 50 --energy
+        run --shape 256,256,256 --stepper projection --method rbsor --iters 50
+        run --shape 128,128,128 --stepper rk4 --steps 20
+      done
+      cp gpurun_out/_new.so cfd_b200/libcfd_b200.so; rm gpurun_out/_new.so
+      python - $out <<'PY'
+import json, sys
+lib = None; rows = {}
+for l in open(sys.argv[1]):
+    d = json.loads(l)
+    if "library" in d: lib = d["library"]; continue
+    key = (tuple(d["shape"]), d["stepper"], d["method"] if d["stepper"] == "projection" else "")
+    rows.setdefault(key, {})[lib] = d
+for key, v in rows.items():
+    if "aligned" not in v or "legacy" not in v: print(key, "incomplete"); continue
+    a, b = v["aligned"], v["legacy"]
+    print(key, "ms/step %.3f vs %.3f (legacy)" % (a["ms_per_step"], b["ms_per_step"]))
+    kb = {k["kernel"]: k for k in b["kernels"]}
+    for k in a["kernels"][:6]:
+        if k["kernel"] in kb: print("    %-24s %9.2f us %.3f   legacy %9.2f us %.3f" % (k["kernel"], k["avg_us"], k["frac_of_measured_peak"], kb[k["kernel"]]["avg_us"], kb[k["kernel"]]["frac_of_measured_peak"]))
+PY
+      ;;
     c4tables)
       out=${O}_c4_tables.jsonl; : > $out
       run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
