@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """C3 on z-slabs: n^3 box, projection + Red-Black SOR x iters, strong scaling over the ranks of one node.
 
-    python tools/c3_slabs.py --n 256                                        # 1 GPU
+    python tools/c3_slabs.py --size 256                                        # 1 GPU
     python -m torch.distributed.run --nproc-per-node 2 tools/c3_slabs.py    # 2 GPUs (peer transport)
 
 Runs the same steps twice -- with the one-pass sweep (poisson_tma3.inc; on slabs: two-layer exchange once per
@@ -20,7 +20,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=256)
+    ap.add_argument("--size", dest="n", type=int, default=256)
     ap.add_argument("--iters", type=int, default=30)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)

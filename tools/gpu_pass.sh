@@ -51,7 +51,7 @@ for stage in "$@"; do
       timeout 300 python tools/c3_slabs.py 2>/dev/null | grep '^{' >> $out
       if [ -n "$arg" ] && [ "$arg" != "1" ]; then
         timeout 600 bash -c "$(declare -f torchrun_); PORT_BASE=29600; torchrun_ $arg tools/c3_slabs.py" 2>/dev/null | grep '^{' >> $out
-        timeout 600 bash -c "$(declare -f torchrun_); PORT_BASE=29700; torchrun_ $arg tools/c3_slabs.py --n 512 --steps 5" 2> ${O}_c3_512.err | grep '^{' >> $out
+        timeout 600 bash -c "$(declare -f torchrun_); PORT_BASE=29700; torchrun_ $arg tools/c3_slabs.py --size 512 --steps 5" 2> ${O}_c3_512.err | grep '^{' >> $out
       fi
       python -c "
 import json,sys
