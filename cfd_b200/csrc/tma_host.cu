@@ -5,6 +5,7 @@
 #include "tma.cuh"
 
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 
 namespace cfdb {
 
@@ -53,9 +54,18 @@ static const CUtensorMap* lookup(TmaCache& tc, std::unordered_map<const double*,
     const cuuint64_t strides[2] = {(cuuint64_t)nx * 8, (cuuint64_t)nx * ny * 8};
     const cuuint32_t box[3] = {(cuuint32_t)bx, (cuuint32_t)by, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
+    // L2 promotion of the box rows (544 bytes starting 16 bytes before a 512-byte boundary): 256-byte lines by
+    // default; CFD_B200_TMA_L2PROMO=128|64|0 for experiments
+    static const CUtensorMapL2promotion promo = [] {
+        const char* e = getenv("CFD_B200_TMA_L2PROMO");
+        const int v = e ? atoi(e) : 256;
+        return v == 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B
+                        : (v == 64 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                   : (v == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE : CU_TENSOR_MAP_L2_PROMOTION_L2_256B));
+    }();
     CUresult r = encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, (void*)p, dims, strides, box, estr,
-                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, promo,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         usable = false;  // never retry: every later launch takes the direct kernels
         return nullptr;
