@@ -16,7 +16,7 @@ struct TmaCache {
     std::unordered_map<const double*, CUtensorMap> maps, wide_maps;
     void configure(const Geom& g);
     const CUtensorMap* get(const double* p);   // nullptr => take the direct (non-TMA) kernel
-    const CUtensorMap* get_wide(const double* p);  // {BX+6, BY+4, 1} box (two-cell halo, even x start) for the fused sweeps
+    const CUtensorMap* get_wide(const double* p);  // {BX+4, BY+4, 1} box (two-cell halo) for the fused sweeps
 };
 
 // Everything a launcher needs besides the per-kernel operands.

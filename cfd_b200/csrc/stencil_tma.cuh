@@ -1,6 +1,6 @@
 // stencil_tma.cuh -- generic TMA plane pipeline for 7-point stencils on NF fields (sm_100a).
 //
-// One block = one 64 x 16 tile of interior cells marched along z (tma.cuh).  The {66,18,1} boxes
+// One block = one 64 x 16 tile of cells marched along z (tma.cuh: Tile).  The {HX,HY,1} = {68,18,1} boxes
 // of the NF stencil fields arrive in a ring of ST stages (one mbarrier per stage, bytes counted
 // by the TMA unit).  For plane k a thread takes the in-plane neighbours of its 2 cells from the
 // shared plane k, the z neighbours from registers (plane k-1, k) and from the freshly landed
@@ -99,7 +99,7 @@ __device__ __forceinline__ void halo_gate_pull(const HaloGate* hg, const Geom& g
 }
 
 // 2-D grids (nz == 1): the pipeline marches along y instead -- a block owns `ychunk` consecutive
-// 64 x 16 tiles of one x column of tiles and streams their {66,18,1} boxes through the same ring
+// 64 x 16 tiles of one x column of tiles and streams their {68,18,1} boxes through the same ring
 // (each box carries its own y halo; the 2 shared rows per tile come from L2).
 template <class Op>
 __device__ __forceinline__ void tma_direct_sweep_2d(const TmaSet<Op::NF>& tm, const Geom& g, int ychunk, Op& op,
