@@ -10,6 +10,8 @@
 #   parity:N     tests/multigpu_parity.py under torchrun, N ranks (needs gpurun --gpus N)
 #   scale:N      torchrun bench.py --gpus N
 #   tables       tools/kernel_table.py over the BASELINE.json shapes
+#   (box time on one B200: tests 4 min; smoke + bench 1.5 min; launches + ncu 20 min -- the two ncu stages replay
+#    9-ms kernels ~40 times each; every table stage 1-2 min)
 #   launches     ncu launch list (gpu__time_duration.sum) of the default bench command + share summary
 #   ncu          ncu --set full of the headline kernels -> profiles-ready CSV (tools/ncu_summary.py)
 #   ncu512       ncu --set full of the 512^3 kernels that are not part of the headline
