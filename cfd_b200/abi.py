@@ -33,6 +33,7 @@ POISSON_BACKEND_AUTO, POISSON_BACKEND_SCALAR, POISSON_BACKEND_OMP = 0, 1, 2
 POISSON_BACKEND_SIMD, POISSON_BACKEND_GPU = 3, 4
 POISSON_CONVERGED, POISSON_MAX_ITER, POISSON_DIVERGED, POISSON_STAGNATED, POISSON_ERROR = 0, 1, 2, 3, -1
 POISSON_PRECOND_NONE, POISSON_PRECOND_JACOBI = 0, 1
+CFD_B200_PRECOND_MULTIGRID = 100  # extension: CG preconditioned by a multigrid cycle (csrc/poisson_mgpc.cu)
 
 CFD_B200_NONCONV_ERROR, CFD_B200_NONCONV_CONTINUE = 0, 1
 
@@ -299,10 +300,10 @@ def poisson_params_default():
 
 
 def poisson_config(method="cg", **kw):
-    """Build a cfd_b200_poisson_config_t. method in {jacobi, rbsor, cg, pcg, bicgstab, multigrid}."""
+    """Build a cfd_b200_poisson_config_t. method in {jacobi, rbsor, cg, pcg, mgpcg, bicgstab, multigrid}."""
     names = {"jacobi": POISSON_METHOD_JACOBI, "rbsor": POISSON_METHOD_REDBLACK_SOR,
-             "cg": POISSON_METHOD_CG, "pcg": POISSON_METHOD_CG, "bicgstab": POISSON_METHOD_BICGSTAB,
-             "multigrid": POISSON_METHOD_MULTIGRID}
+             "cg": POISSON_METHOD_CG, "pcg": POISSON_METHOD_CG, "mgpcg": POISSON_METHOD_CG,
+             "bicgstab": POISSON_METHOD_BICGSTAB, "multigrid": POISSON_METHOD_MULTIGRID}
     cfg = PoissonConfig()
     cfg.method = names[method]
     cfg.params = poisson_params_default()
@@ -312,6 +313,8 @@ def poisson_config(method="cg", **kw):
         cfg.params.max_iterations = 100  # V-cycles
     if method == "pcg":
         cfg.params.preconditioner = POISSON_PRECOND_JACOBI
+    if method == "mgpcg":
+        cfg.params.preconditioner = CFD_B200_PRECOND_MULTIGRID
     cfg.on_nonconvergence = CFD_B200_NONCONV_ERROR
     for k, v in kw.items():
         if k == "on_nonconvergence":

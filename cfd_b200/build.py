@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 _OUT = os.environ.get("CFD_B200_LIB_OUT", "libcfd_b200.so")
 OBJ = os.path.join(HERE, "_build" if _OUT == "libcfd_b200.so" else "_build_" + _OUT.replace(".so", ""))
 LIB = os.path.join(HERE, _OUT)
-SOURCES = ["poisson_kernels.cu", "poisson_mini.cu", "poisson_mg.cu", "ns_kernels.cu", "ns_kernels2.cu", "session.cu", "session_io.cu", "xfer.cu", "tma_host.cu",
+SOURCES = ["poisson_kernels.cu", "poisson_mini.cu", "poisson_mg.cu", "poisson_mgpc.cu", "ns_kernels.cu", "ns_kernels2.cu", "session.cu", "session_io.cu", "xfer.cu", "tma_host.cu",
            "poisson_driver.cu", "step_driver.cu", "capi.cu", "capi_vtables.cu", "bc_api.cu", "gang.cu", "host_sync.cu", "peer.cu", "no_alloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-fmad=false", "-lineinfo", "-std=c++17",

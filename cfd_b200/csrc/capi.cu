@@ -38,6 +38,7 @@ void init_pcfg_locked() {
         if (!strcmp(e, "jacobi")) { g_pcfg.method = POISSON_METHOD_JACOBI; g_pcfg.params.max_iterations = 2000; }
         else if (!strcmp(e, "rbsor")) g_pcfg.method = POISSON_METHOD_REDBLACK_SOR;
         else if (!strcmp(e, "pcg")) g_pcfg.params.preconditioner = POISSON_PRECOND_JACOBI;
+        else if (!strcmp(e, "mgpcg")) g_pcfg.params.preconditioner = CFD_B200_PRECOND_MULTIGRID;
         else if (!strcmp(e, "bicgstab")) g_pcfg.method = POISSON_METHOD_BICGSTAB;
         else if (!strcmp(e, "multigrid")) { g_pcfg.method = POISSON_METHOD_MULTIGRID; g_pcfg.params.max_iterations = 100; }
     }

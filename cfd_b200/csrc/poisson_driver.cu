@@ -63,6 +63,8 @@ double optimal_omega(const cfd_b200_session_desc_t& d, size_t gnx, size_t gny, s
 cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double** px,
                            double** pxt, const double* rhs, poisson_solver_stats_t* out) {
     if (cfg->method == POISSON_METHOD_MULTIGRID) return mg_solve(s, cfg, *px, rhs, out);
+    if (cfg->method == POISSON_METHOD_CG && (int)cfg->params.preconditioner == (int)CFD_B200_PRECOND_MULTIGRID)
+        return mgpcg_solve(s, cfg, *px, rhs, out);
     {
         const cfd_status_t cr = comm_ready(s);
         if (cr != CFD_SUCCESS) return cr;

@@ -305,6 +305,7 @@ void cfd_b200_session_destroy(cfd_b200_session_t* s) {
     for (double* q : s->kv) if (q) cudaFree(q);
     for (double* q : s->rk) if (q) cudaFree(q);
     mg_release(s);
+    mgpc_release(s);
     if (s->ctl) cudaFree(s->ctl);
     if (s->rb.partials) cudaFree(s->rb.partials);
     if (s->rb.ticket) cudaFree(s->rb.ticket);

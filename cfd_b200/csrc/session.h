@@ -58,6 +58,7 @@ struct cfd_b200_session {
     double* xt = nullptr;     // Jacobi ping-pong buffer
     double* kv[8] = {};       // Krylov work vectors
     cfdb::MgState* mg = nullptr;  // multigrid levels, built on the first POISSON_METHOD_MULTIGRID solve
+    void* mgpc = nullptr;         // levels of the multigrid PRECONDITIONER of CG (poisson_mgpc.cu), built on first use
     double* rk[12] = {};      // RK: B[4], C[4], ACC[4]
     double *su_tab = nullptr, *sv_tab = nullptr;  // device source tables [ny], [nx]
     std::vector<double> xs, ys;                   // host coordinates of local i, j
@@ -146,6 +147,10 @@ cfd_status_t poisson_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t*
 cfd_status_t mg_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double* x, const double* rhs,
                       poisson_solver_stats_t* st);
 void mg_release(cfd_b200_session* s);
+// CG preconditioned by a multigrid cycle for the Krylov operator (poisson_mgpc.cu): x in place; one GPU only
+cfd_status_t mgpcg_solve(cfd_b200_session* s, const cfd_b200_poisson_config_t* cfg, double* x, const double* rhs,
+                         poisson_solver_stats_t* st);
+void mgpc_release(cfd_b200_session* s);
 int mg_level_count(cfd_b200_session* s);
 cfd_status_t run_projection(cfd_b200_session* s, const ns_solver_params_t* prm,
                             const cfd_b200_poisson_config_t* pc, int nsteps, ns_solver_stats_t* stats);

@@ -276,6 +276,11 @@ typedef enum {
 } poisson_solver_status_t;
 
 typedef enum { POISSON_PRECOND_NONE = 0, POISSON_PRECOND_JACOBI = 1 } poisson_precond_type_t;
+/* No counterpart in the reference (its roadmap item ROADMAP.md:190-194): POISSON_METHOD_CG preconditioned by one
+ * multigrid V(1,1) cycle built for the Krylov operator itself (zero boundary cells, csrc/poisson_mgpc.cu).  Same
+ * system and stopping rule as the reference's CG, 7-8 iterations instead of hundreds; the iterates differ, the
+ * answers agree to the tolerance asked for.  One GPU. */
+#define CFD_B200_PRECOND_MULTIGRID ((poisson_precond_type_t)100)
 
 typedef struct {
     double tolerance;

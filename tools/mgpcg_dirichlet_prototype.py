@@ -70,7 +70,7 @@ class Level:
     pass
 
 
-def build(ns, kind, min_nodes=3):
+def build(ns, kind, min_nodes=3, coarse_sweeps=0):
     """Hierarchy for a box of ns = (nx, ny[, nz]) cells incl. boundary cells, unit box, h = 1 / (n - 1) per axis.
     The reference operator is the point-wise stencil (sum over axes of (2u - u- - u+) / h^2) = M^-1 K per axis on the
     uniform fine grid; the symmetric form K_total = sum_axes K_a (x) M_others is what the hierarchy works with
@@ -90,9 +90,10 @@ def build(ns, kind, min_nodes=3):
                 terms.append(kron_all([L.K1[b] if b == a else L.M1[b] for b in range(dims)]))
             L.A = sum(terms[1:], terms[0]).tocsr()
         levels.append(L)
-        if min(len(x) for x in xs) <= min_nodes:
+        if max(len(x) for x in xs) <= min_nodes:
             break
-        xc = [x[1::2] if len(x) > min_nodes else x for x in xs]   # keep the even cells (index 2, 4, ... of 1..n-2)
+        # keep the even cells (index 2, 4, ... of 1..n-2) of every axis that still has more than min_nodes of them
+        xc = [x[1::2] if len(x) > min_nodes else x for x in xs]
         L.P = kron_all([interp1d(xs[a], xc[a], 0.0, 1.0) if len(xc[a]) != len(xs[a]) else sp.identity(len(xs[a]), format="csr")
                         for a in range(dims)])
         xs = xc
@@ -102,7 +103,17 @@ def build(ns, kind, min_nodes=3):
             levels[l].A = (P.T @ levels[l - 1].A @ P).tocsr()
     for L in levels:
         L.dinv = 1.0 / L.A.diagonal()
-    levels[-1].solve = spla.factorized(levels[-1].A.tocsc())
+    if coarse_sweeps:   # what a GPU block would do: a fixed number of damped-Jacobi sweeps (a symmetric operator)
+        Lc = levels[-1]
+
+        def sweeps(b, Lc=Lc):
+            x = 0.85 * Lc.dinv * b
+            for _ in range(coarse_sweeps - 1):
+                x += 0.85 * Lc.dinv * (b - Lc.A @ x)
+            return x
+        Lc.solve = sweeps
+    else:
+        levels[-1].solve = spla.factorized(levels[-1].A.tocsc())
     return levels
 
 
