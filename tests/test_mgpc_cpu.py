@@ -109,3 +109,32 @@ def test_level_plan():
     assert all(r[6] == 0.25 for r in rows)  # even counts keep the wall distance of the fine grid
     assert [int(r[2]) for r in rows] == [1] * 7
     assert rows[-1][7] == 0 and rows[-1][8] == 0
+
+
+@pytest.mark.parametrize("ns", [(34, 23), (33, 33), (18, 15, 13), (17, 17, 17)])
+def test_cycle_is_a_symmetric_positive_operator(host, ns):
+    """PCG needs M^-1 symmetric positive definite: <M^-1 a, b> = <a, M^-1 b> and <M^-1 a, a> > 0 -- which the
+    damped-Jacobi pre / post smoothing, R = P^T and the symmetric wall rows are there for."""
+    d3 = len(ns) == 3
+    nx, ny = ns[0], ns[1]
+    nz = ns[2] if d3 else 1
+    h = [0.7 / (nx - 1), 1.0 / (ny - 1), (1.3 / (nz - 1)) if d3 else 0.0]
+    rng = np.random.default_rng(4)
+    inner = (slice(1, -1) if d3 else slice(None), slice(1, -1), slice(1, -1))
+
+    def rand():
+        a = np.zeros((nz, ny, nx))
+        a[inner] = rng.standard_normal(a[inner].shape)
+        return a
+
+    def apply(a):
+        z = np.zeros_like(a)
+        host.mgpc_host_apply(nx, ny, nz, h[0], h[1], h[2], ptr(a), ptr(z))
+        return z
+
+    for _ in range(3):
+        a, b = rand(), rand()
+        za, zb = apply(a), apply(b)
+        lhs, rhs = float(np.sum(za * b)), float(np.sum(a * zb))
+        assert abs(lhs - rhs) <= 1e-11 * max(abs(lhs), abs(rhs), 1e-30), (lhs, rhs)
+        assert float(np.sum(za * a)) > 0.0
