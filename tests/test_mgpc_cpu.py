@@ -49,7 +49,7 @@ def test_cycle_equals_the_numpy_prototype(host, ns):
     r[inner] = rin
     z = np.full((nz, ny, nx), 7.0)
     nl = host.mgpc_host_apply(nx, ny, nz, h[0], h[1], h[2] if d3 else 0.0, ptr(r), ptr(z))
-    levels = mp.build(ns, "rediscr", coarse_sweeps=40)
+    levels = mp.build(ns, "rediscr", coarse_sweeps=40, coupling=0.5)
     assert nl == len(levels)
     vec = np.transpose(rin, (2, 1, 0)).ravel() if d3 else rin[0].T.ravel()  # the prototype orders (x, y[, z])
     zp = mp.vcycle(levels, 0, vec, 1, 0.85 if d3 else 0.8)
@@ -61,8 +61,8 @@ def test_cycle_equals_the_numpy_prototype(host, ns):
     assert not zb.any()  # boundary cells of the result are zero
 
 
-@pytest.mark.parametrize("shape", [(33, 33, 1), (64, 40, 1), (129, 129, 1), (130, 130, 1), (34, 20, 18), (33, 33, 33),
-                                   (34, 34, 34)])
+@pytest.mark.parametrize("shape", [(33, 33, 1), (64, 40, 1), (129, 129, 1), (130, 130, 1), (258, 66, 1), (34, 20, 18),
+                                   (33, 33, 33), (34, 34, 34), (66, 18, 21)])
 def test_solve_against_the_reference_cg(host, orc, shape):
     """Same system, same stopping rule: the initial residual is the reference's, a tight solve lands on the reference
     CG's answer (<= 1e-8), and the iteration count is a handful where the reference needs tens to hundreds."""
@@ -83,16 +83,15 @@ def test_solve_against_the_reference_cg(host, orc, shape):
         assert out[2] < tol * out[1]
         l2, li = cases.rel_err(xm, xo)
         assert l2 <= gate and li <= gate, (tol, l2, li)
-        iso = max(dx, dy, dz if nz > 1 else dx) / min(dx, dy, dz if nz > 1 else dx) < 1.01
-        if tol == 1e-6:
-            assert out[0] <= (9 if iso else 14), out[0]
+        if tol == 1e-6:  # isotropic or not (semi-coarsening by coupling strength)
+            assert out[0] <= 9, out[0]
             assert st_o.iterations >= 4 * out[0]
 
 
 def test_level_plan():
     """Odd node counts move the wall away from the last coarse node; axes stop at three nodes."""
     r = subprocess.run(["g++", "-std=c++17", "-x", "c++", "-", "-o", os.path.join(ROOT, "oracle", "_mgpc_plan_probe")],
-                       input='#include "%s/cfd_b200/csrc/mgpc_cell.h"\n#include <stdio.h>\nint main(){cfdb::MgpcLv lv[16];'
+                       input='#include "%s/cfd_b200/csrc/mgpc_cell.h"\n#include <stdio.h>\nint main(){cfdb::MgpcLv lv[32];'
                              'int nl=cfdb::mgpc_plan(131,66,1,0.5,0.25,0.0,lv);for(int l=0;l<nl;l++)'
                              'printf("%%d %%d %%d %%g %%g %%g %%g %%d %%d\\n",lv[l].n[0],lv[l].n[1],lv[l].n[2],lv[l].H[0],lv[l].d[0],'
                              'lv[l].H[1],lv[l].d[1],lv[l].coarsen[0],lv[l].coarsen[1]);}' % ROOT,
@@ -101,13 +100,15 @@ def test_level_plan():
     out = subprocess.run([os.path.join(ROOT, "oracle", "_mgpc_plan_probe")], capture_output=True, text=True).stdout
     os.remove(os.path.join(ROOT, "oracle", "_mgpc_plan_probe"))
     rows = [[float(v) for v in line.split()] for line in out.strip().splitlines()]
-    # x: 129 nodes, h = 0.5: 129 -> 64 (odd: d = h + h = 1.0, H = 1.0) -> 32 -> 16 -> 8 -> 4 -> 2
-    assert [int(r[0]) for r in rows] == [129, 64, 32, 16, 8, 4, 2]
-    assert rows[1][3] == 1.0 and rows[1][4] == 1.0 and rows[2][3] == 2.0 and rows[2][4] == 1.0
-    # y: 64 nodes, h = 0.25: 64 -> 32 -> 16 -> 8 -> 4 -> 2 -> 2 (not coarsened below 3)
-    assert [int(r[1]) for r in rows] == [64, 32, 16, 8, 4, 2, 2]
+    # y (h = 0.25) is coupled 4 x more strongly than x (h = 0.5): it is halved alone until the spacings meet
+    # x: 129 nodes: 129, 129 -> 64 (odd: d = h + h = 1.0, H = 1.0) -> 32 -> 16 -> 8 -> 4 -> 2
+    assert [int(r[0]) for r in rows] == [129, 129, 64, 32, 16, 8, 4, 2]
+    assert rows[2][3] == 1.0 and rows[2][4] == 1.0 and rows[3][3] == 2.0 and rows[3][4] == 1.0
+    # y: 64 nodes: 64 -> 32 -> 16 -> 8 -> 4 -> 2 -> 2 -> 2 (not coarsened below 3)
+    assert [int(r[1]) for r in rows] == [64, 32, 16, 8, 4, 2, 2, 2]
     assert all(r[6] == 0.25 for r in rows)  # even counts keep the wall distance of the fine grid
-    assert [int(r[2]) for r in rows] == [1] * 7
+    assert [int(r[2]) for r in rows] == [1] * 8
+    assert (rows[0][7], rows[0][8]) == (0, 1) and (rows[1][7], rows[1][8]) == (1, 1)
     assert rows[-1][7] == 0 and rows[-1][8] == 0
 
 

@@ -70,7 +70,7 @@ class Level:
     pass
 
 
-def build(ns, kind, min_nodes=3, coarse_sweeps=0):
+def build(ns, kind, min_nodes=3, coarse_sweeps=0, coupling=0.0):
     """Hierarchy for a box of ns = (nx, ny[, nz]) cells incl. boundary cells, unit box, h = 1 / (n - 1) per axis.
     The reference operator is the point-wise stencil (sum over axes of (2u - u- - u+) / h^2) = M^-1 K per axis on the
     uniform fine grid; the symmetric form K_total = sum_axes K_a (x) M_others is what the hierarchy works with
@@ -92,8 +92,13 @@ def build(ns, kind, min_nodes=3, coarse_sweeps=0):
         levels.append(L)
         if max(len(x) for x in xs) <= min_nodes:
             break
-        # keep the even cells (index 2, 4, ... of 1..n-2) of every axis that still has more than min_nodes of them
-        xc = [x[1::2] if len(x) > min_nodes else x for x in xs]
+        # keep the even cells (index 2, 4, ... of 1..n-2) of every axis that still has more than min_nodes of them --
+        # with coupling > 0 (semi-coarsening, what csrc/mgpc_cell.h does with 0.5) only of the axes whose 1 / H^2 is
+        # at least that share of the strongest coarsenable one
+        can = [len(x) > min_nodes for x in xs]
+        strength = [1.0 / (x[1] - x[0]) ** 2 if len(x) > 1 else 0.0 for x in xs]
+        cmax = max(s_ for s_, c in zip(strength, can) if c)
+        xc = [x[1::2] if (c and s_ >= coupling * cmax) else x for x, c, s_ in zip(xs, can, strength)]
         L.P = kron_all([interp1d(xs[a], xc[a], 0.0, 1.0) if len(xc[a]) != len(xs[a]) else sp.identity(len(xs[a]), format="csr")
                         for a in range(dims)])
         xs = xc
