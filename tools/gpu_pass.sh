@@ -16,6 +16,7 @@
 #   ncu          ncu --set full of the headline kernels -> profiles-ready CSV (tools/ncu_summary.py)
 #   ncu512       ncu --set full of the 512^3 kernels that are not part of the headline
 #   abtile       kernel tables with the shipped library and with the legacy tile geometry (libcfd_b200_legacy.so)
+#   mgpcg        time to solution of mgpcg / pcg / multigrid at 4096^2, 1024^2, 256^3, 512^3 (not run in round 2: no budget left)
 #   c4tables     kernel tables of the CG / PCG paths at 4096^2 and 512^3
 #   ncuc4        ncu --set full of the C4 kernels (4096^2, PCG + energy)
 #   ncurb        ncu --set full of the one-pass Red-Black SOR sweeps (4096^2, 256^3)
@@ -95,6 +96,18 @@ for key, v in rows.items():
         if k["kernel"] in kb: print("    %-24s %9.2f us %.3f   legacy %9.2f us %.3f" % (k["kernel"], k["avg_us"], k["frac_of_measured_peak"], kb[k["kernel"]]["avg_us"], kb[k["kernel"]]["frac_of_measured_peak"]))
 PY
       ;;
+    mgpcg)
+      # time to solution (relative residual 1e-6) of the stand-alone Poisson solve: multigrid-preconditioned CG against
+      # the reference's Jacobi-PCG and against the stationary-system multigrid, random zero-mean rhs
+      out=${O}_mgpcg.jsonl; : > $out
+      run() { timeout 280 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
+      for shp in 4096,4096,1 1024,1024,1 256,256,256 512,512,512; do
+        for m in mgpcg pcg multigrid; do run --shape $shp --stepper poisson --method $m --tol 1e-6 --iters 20000 --steps 1 --warmup 1; done
+      done
+      python -c "
+import json
+for l in open('$out'):
+    d=json.loads(l); print(d['shape'], d['method'], 'iterations', d['poisson_iterations'], 'ms', round(d['ms_per_step'],2))" ;;
     c4tables)
       out=${O}_c4_tables.jsonl; : > $out
       run() { timeout 150 python tools/kernel_table.py "$@" 2>/dev/null | tail -1 >> $out; }
